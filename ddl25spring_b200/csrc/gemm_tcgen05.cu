@@ -1,0 +1,403 @@
+// K10 / K3: grouped GEMM on the 5th-generation tensor cores.
+//
+//   C[g] (M x N, fp32) = epilogue( A[g] (M x K) * B[g]^T (N x K) )          g = 0 .. G-1
+//
+// * operands are fp32 in HBM and are consumed as TF32 by `tcgen05.mma.kind::tf32` (bf16 operands
+//   use kind::f16); each operand can be K-major ([rows, K], K contiguous) or MN-major
+//   ([K, rows], rows contiguous), so forward (X W^T), input-gradient (dY W) and weight-gradient
+//   (dY^T X) GEMMs of a Linear layer all map onto this kernel without a transpose pass;
+// * operand tiles are staged by TMA (cp.async.bulk.tensor, 128-byte swizzle) into a multi-stage
+//   shared-memory ring, accumulators live in TMEM, one elected thread issues the MMAs, four
+//   epilogue warps read the accumulator back with tcgen05.ld;
+// * PRECISE mode ("3xTF32"): the epilogue warps, idle during the main loop, split every landed
+//   fp32 tile in shared memory into hi = tf32(x) and lo = x - hi; the MMA thread then issues
+//   hi*hi + hi*lo + lo*hi, which recovers fp32-grade products (the reference's nn.Linear runs in
+//   true fp32, lab/tutorial_1a/hfl_complete.py:58-61) while staying on the tensor cores;
+// * split-K writes per-split partial tiles to a scratch buffer; `splitk_reduce` sums them in a
+//   fixed order (deterministic: Krum's selection must not depend on atomics ordering) and applies
+//   bias + activation.  The Gram matrix G = U U^T of K3 is this kernel with A = B = U.
+//
+// Replaces (reference): every nn.Linear and, via ops/gemm.py: gram(), the
+// pairwise-distance computation of Krum [north star].
+#include "common.cuh"
+#include "ddl25_kernels.h"
+#include "tc05.cuh"
+#include "tmap.h"
+
+namespace {
+
+using namespace tc05;
+
+constexpr int BM = 128;
+constexpr int ROW_BYTES = 128;          // one swizzle row: 32 tf32 or 64 bf16 along the contiguous dim
+constexpr int kEpiWarps = 4;
+constexpr int kThreads = 32 * (2 + kEpiWarps);
+
+struct Epilogue {
+  float* C;             // output (or partials scratch when n_split > 1)
+  int64_t ldc;
+  int64_t c_group_stride;
+  const float* bias;    // per-N bias or null
+  int64_t bias_group_stride;
+  int act;              // 0 none, 1 relu, 2 leaky relu
+  float slope;
+  float alpha;
+  int n_split;          // > 1: write raw partial tiles to C = scratch[split][g][M][N] (ldc = N)
+};
+
+__device__ __forceinline__ float apply_act(float v, int act, float slope) {
+  if (act == 1) return fmaxf(v, 0.f);
+  if (act == 2) return v > 0.f ? v : v * slope;
+  return v;
+}
+
+template <int BN, int EB /*element bytes*/, bool SPLIT3>
+struct SmemPlan {
+  static constexpr int A_BYTES = BM * ROW_BYTES;
+  static constexpr int B_BYTES = BN * ROW_BYTES;
+  static constexpr int STAGE_BYTES = (A_BYTES + B_BYTES) * (SPLIT3 ? 2 : 1);
+  static constexpr int BUDGET = 200 * 1024;
+  static constexpr int RAW_STAGES = BUDGET / STAGE_BYTES;
+  static constexpr int STAGES = RAW_STAGES > 8 ? 8 : RAW_STAGES;
+  static constexpr int BAR_BYTES = 1024;
+  static constexpr int TOTAL = STAGES * STAGE_BYTES + BAR_BYTES + 1024 /*alignment slack*/;
+};
+
+template <int BN, int EB, bool A_MN, bool B_MN, bool SPLIT3>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                    const Epilogue epi, const int M, const int N, const int K, const int kblocks_per_split) {
+  using Plan = SmemPlan<BN, EB, SPLIT3>;
+  constexpr int STAGES = Plan::STAGES;
+  constexpr int BK = ROW_BYTES / EB;         // elements per k-block (32 tf32 / 64 bf16)
+  constexpr int UMMA_K = 32 / EB;            // elements per MMA instruction along K (8 tf32 / 16 bf16)
+  constexpr int KSTEPS = BK / UMMA_K;        // 4
+  static_assert(!SPLIT3 || EB == 4, "3xTF32 split applies to fp32 operands only");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* stage_base = smem;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Plan::STAGE_BYTES);
+  uint64_t* full_bar = bars;                  // TMA bytes landed
+  uint64_t* empty_bar = bars + STAGES;        // MMAs that read the stage have completed
+  uint64_t* split_bar = bars + 2 * STAGES;    // hi/lo split written (SPLIT3 only)
+  uint64_t* accum_bar = bars + 3 * STAGES;    // accumulator complete
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * STAGES + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM;
+  const int n0 = blockIdx.y * BN;
+  const int n_split = epi.n_split > 1 ? epi.n_split : 1;
+  const int g = blockIdx.z / n_split;
+  const int split = blockIdx.z % n_split;
+  const int total_kblocks = (K + BK - 1) / BK;
+  const int kb_begin = split * kblocks_per_split;
+  int kb_end = kb_begin + kblocks_per_split;
+  if (kb_end > total_kblocks) kb_end = total_kblocks;
+  const int num_kb = kb_end > kb_begin ? kb_end - kb_begin : 0;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+      mbar_init(&split_bar[s], kEpiWarps);
+    }
+    mbar_init(accum_bar, 1);
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc<BN>(tmem_slot);
+  fence_before_thread_sync();
+  __syncthreads();
+  fence_after_thread_sync();
+  const uint32_t tmem_acc = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      uint32_t phase = 0;
+      int s = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[s], phase ^ 1);
+        uint8_t* a_dst = stage_base + s * Plan::STAGE_BYTES;
+        uint8_t* b_dst = a_dst + Plan::A_BYTES;
+        mbar_arrive_expect_tx(&full_bar[s], Plan::A_BYTES + Plan::B_BYTES);
+        const int k0 = (kb_begin + kb) * BK;
+        if constexpr (A_MN) tma_load_4d(a_dst, &tma_a, &full_bar[s], 0, k0, m0 / BK, g);
+        else tma_load_3d(a_dst, &tma_a, &full_bar[s], k0, m0, g);
+        if constexpr (B_MN) tma_load_4d(b_dst, &tma_b, &full_bar[s], 0, k0, n0 / BK, g);
+        else tma_load_3d(b_dst, &tma_b, &full_bar[s], k0, n0, g);
+        if (++s == STAGES) { s = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = make_idesc(EB == 4 ? FMT_TF32 : FMT_BF16, BM, BN, A_MN, B_MN);
+    uint32_t phase = 0;
+    int s = 0;
+    for (int kb = 0; kb < num_kb; ++kb) {
+      mbar_wait(SPLIT3 ? &split_bar[s] : &full_bar[s], phase);
+      fence_after_thread_sync();
+      if (elect_one()) {
+        const uint32_t a_hi = smem_u32(stage_base + s * Plan::STAGE_BYTES);
+        const uint32_t b_hi = a_hi + Plan::A_BYTES;
+        const uint32_t a_lo = b_hi + Plan::B_BYTES;
+        const uint32_t b_lo = a_lo + Plan::A_BYTES;
+#pragma unroll
+        for (int kk = 0; kk < KSTEPS; ++kk) {
+          // K-major : advance 32 B inside the 128 B swizzle row; 8-row groups are 1024 B apart
+          // MN-major: one k-step = UMMA_K k-rows of 128 B (8-row swizzle atoms 1024 B apart); MN atoms BK*128 B apart
+          const uint32_t a_off = A_MN ? kk * UMMA_K * ROW_BYTES : kk * 32;
+          const uint32_t b_off = B_MN ? kk * UMMA_K * ROW_BYTES : kk * 32;
+          const uint32_t a_lbo = A_MN ? BK * ROW_BYTES : 16, b_lbo = B_MN ? BK * ROW_BYTES : 16;
+          const bool acc = (kb > 0) || (kk > 0);
+          // 32-bit MN-major operands must use the 128B swizzle with 32B atoms (pattern period 4 k-rows)
+          constexpr uint32_t a_lay = (A_MN && EB == 4) ? LAYOUT_SW128_BASE32B : LAYOUT_SW128;
+          constexpr uint32_t b_lay = (B_MN && EB == 4) ? LAYOUT_SW128_BASE32B : LAYOUT_SW128;
+          constexpr uint32_t a_sbo = (A_MN && EB == 4) ? 512 : 1024, b_sbo = (B_MN && EB == 4) ? 512 : 1024;
+          const uint64_t da_hi = smem_desc_sw128(a_hi + a_off, a_lbo, a_sbo, a_lay);
+          const uint64_t db_hi = smem_desc_sw128(b_hi + b_off, b_lbo, b_sbo, b_lay);
+          if constexpr (SPLIT3) {
+            const uint64_t da_lo = smem_desc_sw128(a_lo + a_off, a_lbo, a_sbo, a_lay);
+            const uint64_t db_lo = smem_desc_sw128(b_lo + b_off, b_lbo, b_sbo, b_lay);
+            mma_tf32(tmem_acc, da_lo, db_hi, idesc, acc);
+            mma_tf32(tmem_acc, da_hi, db_lo, idesc, true);
+            mma_tf32(tmem_acc, da_hi, db_hi, idesc, true);
+          } else if constexpr (EB == 4) {
+            mma_tf32(tmem_acc, da_hi, db_hi, idesc, acc);
+          } else {
+            mma_f16(tmem_acc, da_hi, db_hi, idesc, acc);
+          }
+        }
+        mma_commit(&empty_bar[s]);                       // stage reusable once these MMAs retire
+        if (kb == num_kb - 1) mma_commit(accum_bar);     // accumulator complete
+      }
+      __syncwarp();
+      if (++s == STAGES) { s = 0; phase ^= 1; }
+    }
+  } else {
+    // ===================== splitter (PRECISE) + epilogue warps =====================
+    const int ew = warp - 2;                 // 0..3
+    const int et = ew * 32 + lane;           // 0..127
+    if constexpr (SPLIT3) {
+      uint32_t phase = 0;
+      int s = 0;
+      constexpr int NV = (Plan::A_BYTES + Plan::B_BYTES) / 16;   // float4 count of A|B (contiguous)
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[s], phase);
+        float4* hi = reinterpret_cast<float4*>(stage_base + s * Plan::STAGE_BYTES);
+        float4* lo = hi + NV;
+#pragma unroll 4
+        for (int i = et; i < NV; i += 32 * kEpiWarps) {
+          float4 x = hi[i], h, l;
+          h.x = __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u); l.x = x.x - h.x;
+          h.y = __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u); l.y = x.y - h.y;
+          h.z = __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u); l.z = x.z - h.z;
+          h.w = __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u); l.w = x.w - h.w;
+          hi[i] = h;
+          lo[i] = l;
+        }
+        fence_proxy_async_smem();            // make the generic-proxy stores visible to the tensor core
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&split_bar[s]);
+        if (++s == STAGES) { s = 0; phase ^= 1; }
+      }
+    }
+    // ---- epilogue: TMEM -> registers -> global
+    const int quarter = warp & 3;            // TMEM lane quarter this warp may read
+    const int row = quarter * 32 + lane;     // accumulator row == TMEM lane
+    const int m = m0 + row;
+    if (num_kb > 0) {
+      mbar_wait(accum_bar, 0);
+      fence_after_thread_sync();
+    }
+    float* Cg;
+    int64_t ldc;
+    if (n_split > 1) {
+      Cg = epi.C + ((int64_t)split * gridDim.z / n_split + g) * (int64_t)M * N;
+      ldc = N;
+    } else {
+      Cg = epi.C + (int64_t)g * epi.c_group_stride;
+      ldc = epi.ldc;
+    }
+    const float* bias = (epi.bias && n_split == 1) ? epi.bias + (int64_t)g * epi.bias_group_stride : nullptr;
+    const bool vec_ok = (ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(Cg) & 15) == 0);
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 32) {
+      float v[32];
+      if (num_kb > 0) {
+        tmem_ld_32x32(tmem_acc + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0, v);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = 0.f;
+      }
+      if (m < M) {
+        float* crow = Cg + (int64_t)m * ldc + n0 + c0;
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          const int n = n0 + c0 + i;
+          if (n >= N) break;
+          float o[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float x = v[i + j] * epi.alpha;
+            if (n_split == 1) {
+              if (bias && n + j < N) x += bias[n + j];
+              x = apply_act(x, epi.act, epi.slope);
+            }
+            o[j] = x;
+          }
+          if (vec_ok && n + 3 < N) {
+            *reinterpret_cast<float4*>(crow + i) = make_float4(o[0], o[1], o[2], o[3]);
+          } else {
+            for (int j = 0; j < 4 && n + j < N; ++j) crow[i + j] = o[j];
+          }
+        }
+      }
+    }
+    fence_before_thread_sync();
+  }
+  __syncthreads();
+  if (warp == 2) {
+    fence_after_thread_sync();
+    tmem_dealloc<BN>(tmem_acc);
+  }
+}
+
+// Sum split-K partial tiles in split order, add bias, apply activation.
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ part, int n_split,
+                                                            int64_t group_elems /*M*N*/, int G, int N, float* __restrict__ C,
+                                                            int64_t ldc, int64_t c_group_stride, const float* __restrict__ bias,
+                                                            int64_t bias_group_stride, int act, float slope) {
+  const int64_t total = group_elems * G;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+    for (int s = 0; s < n_split; ++s) acc += part[(int64_t)s * total + i];
+    const int g = (int)(i / group_elems);
+    const int64_t r = i % group_elems;
+    const int64_t m = r / N;
+    const int n = (int)(r % N);
+    if (bias) acc += bias[(int64_t)g * bias_group_stride + n];
+    C[(int64_t)g * c_group_stride + m * ldc + n] = apply_act(acc, act, slope);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ host
+struct OperandDesc {
+  const void* ptr;
+  int64_t rows;          // M (for A) or N (for B)
+  int64_t ld;            // leading dimension in elements (K-major: row stride; MN-major: k-row stride)
+  int64_t group_stride;  // elements
+  int mn_major;
+};
+
+int make_operand_map(CUtensorMap* map, const OperandDesc& op, int64_t K, int G, int box_rows, int eb) {
+  const int bk = ROW_BYTES / eb;
+  const CUtensorMapDataType dt = eb == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  if (!op.mn_major) {
+    uint64_t dims[3] = {(uint64_t)K, (uint64_t)op.rows, (uint64_t)G};
+    uint64_t strides[2] = {(uint64_t)op.ld * eb, (uint64_t)(G > 1 ? op.group_stride : op.ld * op.rows) * eb};
+    uint32_t box[3] = {(uint32_t)bk, (uint32_t)box_rows, 1};
+    return ddl_encode_tmap(map, dt, 3, op.ptr, dims, strides, box, /*swizzle128=*/1);
+  }
+  DDL_REQUIRE(op.rows % bk == 0, "MN-major operand needs rows %% %d == 0 (got %lld)", bk, (long long)op.rows);
+  uint64_t dims[4] = {(uint64_t)bk, (uint64_t)K, (uint64_t)(op.rows / bk), (uint64_t)G};
+  uint64_t strides[3] = {(uint64_t)op.ld * eb, (uint64_t)ROW_BYTES,
+                         (uint64_t)(G > 1 ? op.group_stride : op.ld * K) * eb};
+  uint32_t box[4] = {(uint32_t)bk, (uint32_t)bk, (uint32_t)(box_rows / bk), 1};
+  return ddl_encode_tmap(map, dt, 4, op.ptr, dims, strides, box, eb == 4 ? 2 : 1);
+}
+
+template <int BN, int EB, bool A_MN, bool B_MN, bool SPLIT3>
+int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const Epilogue& epi, int M, int N, int K, int G,
+                int n_split, int kb_per_split, cudaStream_t st) {
+  using Plan = SmemPlan<BN, EB, SPLIT3>;
+  auto kern = gemm_tcgen05_kernel<BN, EB, A_MN, B_MN, SPLIT3>;
+  static bool configured = false;
+  if (!configured) {
+    DDL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Plan::TOTAL));
+    configured = true;
+  }
+  dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, G * n_split);
+  kern<<<grid, kThreads, Plan::TOTAL, st>>>(ta, tb, epi, M, N, K, kb_per_split);
+  DDL_LAUNCH_CHECK();
+  return DDL_OK;
+}
+
+template <int BN, int EB, bool SPLIT3>
+int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const Epilogue& epi, int M,
+                   int N, int K, int G, int n_split, int kbps, cudaStream_t st) {
+  if (!a_mn && !b_mn) return launch_gemm<BN, EB, false, false, SPLIT3>(ta, tb, epi, M, N, K, G, n_split, kbps, st);
+  if (!a_mn && b_mn) return launch_gemm<BN, EB, false, true, SPLIT3>(ta, tb, epi, M, N, K, G, n_split, kbps, st);
+  if (a_mn && !b_mn) return launch_gemm<BN, EB, true, false, SPLIT3>(ta, tb, epi, M, N, K, G, n_split, kbps, st);
+  return launch_gemm<BN, EB, true, true, SPLIT3>(ta, tb, epi, M, N, K, G, n_split, kbps, st);
+}
+
+}  // namespace
+
+extern "C" {
+
+int64_t ddl_gemm_scratch_floats(int M, int N, int G, int n_split) {
+  return n_split > 1 ? (int64_t)n_split * G * M * N : 0;
+}
+
+int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_mn_major, const void* B, int64_t ldb,
+                     int64_t b_group_stride, int b_mn_major, float* C, int64_t ldc, int64_t c_group_stride,
+                     const float* bias, int64_t bias_group_stride, int act, float slope, float alpha, int M, int N,
+                     int K, int G, int dtype_bytes, int precise, int n_split, float* scratch, void* stream) {
+  DDL_REQUIRE(M > 0 && N > 0 && K > 0 && G > 0, "empty GEMM");
+  DDL_REQUIRE(dtype_bytes == 4 || dtype_bytes == 2, "operands must be fp32 (tf32 math) or bf16");
+  DDL_REQUIRE(!(precise && dtype_bytes != 4), "precise (3xTF32) mode needs fp32 operands");
+  const int eb = dtype_bytes, bk = ROW_BYTES / eb;
+  DDL_REQUIRE((lda * eb) % 16 == 0 && (ldb * eb) % 16 == 0, "operand leading dimensions must be multiples of 16 bytes");
+  DDL_REQUIRE((reinterpret_cast<uintptr_t>(A) & 15) == 0 && (reinterpret_cast<uintptr_t>(B) & 15) == 0,
+              "operands must be 16-byte aligned");
+  if (n_split < 1) n_split = 1;
+  const int total_kb = (K + bk - 1) / bk;
+  if (n_split > total_kb) n_split = total_kb;
+  DDL_REQUIRE(n_split == 1 || scratch != nullptr, "split-K needs a scratch buffer of ddl_gemm_scratch_floats() floats");
+  const int kbps = (total_kb + n_split - 1) / n_split;
+  n_split = (total_kb + kbps - 1) / kbps;
+
+  const int BN = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
+  if (a_mn_major) DDL_REQUIRE(M % bk == 0, "MN-major A needs M %% %d == 0", bk);
+  if (b_mn_major) DDL_REQUIRE(N % bk == 0, "MN-major B needs N %% %d == 0", bk);
+
+  CUtensorMap ta, tb;
+  OperandDesc oa{A, M, lda, a_group_stride, a_mn_major}, ob{B, N, ldb, b_group_stride, b_mn_major};
+  if (int e = make_operand_map(&ta, oa, K, G, BM, eb)) return e;
+  if (int e = make_operand_map(&tb, ob, K, G, BN, eb)) return e;
+
+  Epilogue epi;
+  epi.C = n_split > 1 ? scratch : C;
+  epi.ldc = ldc; epi.c_group_stride = c_group_stride;
+  epi.bias = bias; epi.bias_group_stride = bias_group_stride;
+  epi.act = act; epi.slope = slope; epi.alpha = alpha; epi.n_split = n_split;
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc;
+  const bool amn = a_mn_major != 0, bmn = b_mn_major != 0;
+#define DDL_GEMM_CASE(BN_)                                                                                     \
+  if (eb == 4 && precise) rc = dispatch_major<BN_, 4, true>(amn, bmn, ta, tb, epi, M, N, K, G, n_split, kbps, st);   \
+  else if (eb == 4) rc = dispatch_major<BN_, 4, false>(amn, bmn, ta, tb, epi, M, N, K, G, n_split, kbps, st);        \
+  else rc = dispatch_major<BN_, 2, false>(amn, bmn, ta, tb, epi, M, N, K, G, n_split, kbps, st);
+  if (BN == 32) { DDL_GEMM_CASE(32) }
+  else if (BN == 64) { DDL_GEMM_CASE(64) }
+  else { DDL_GEMM_CASE(128) }
+#undef DDL_GEMM_CASE
+  if (rc) return rc;
+  if (n_split > 1) {
+    const int64_t ge = (int64_t)M * N;
+    int64_t blocks = (ge * G + 255) / 256;
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    splitk_reduce_kernel<<<(int)blocks, 256, 0, st>>>(scratch, n_split, ge, G, N, C, ldc, c_group_stride, bias,
+                                                      bias_group_stride, act, slope);
+    DDL_LAUNCH_CHECK();
+  }
+  return DDL_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,117 @@
+/* C ABI of libddl25_kernels.so — the hand-written sm_100a (NVIDIA B200) kernel library of
+ * ddl25spring_b200.  Python binds these through ctypes (ddl25spring_b200/ops/_lib.py); any
+ * other host program can link the library and call them directly.
+ *
+ * Conventions
+ *  - every entry point returns 0 on success, non-zero on failure; ddl_last_error() then
+ *    returns a human-readable reason (thread-local string, valid until the next call).
+ *  - `stream` is a cudaStream_t passed as void* (NULL = default stream). Launches are
+ *    asynchronous; nothing here synchronises unless stated.
+ *  - all tensors are fp32, contiguous, 16-byte aligned unless stated; "flat" vectors follow
+ *    the FlatArena layout (ddl25spring_b200/core/arena.py).
+ *  - "(ref: path:lines)" names the reference code the entry point replaces, relative to the
+ *    DDL25Spring tree; "[north star]" marks ops the reference does not contain.
+ */
+#ifndef DDL25_KERNELS_H_
+#define DDL25_KERNELS_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DDL_MAX_ROWS 128 /* update rows per aggregation launch */
+#define DDL_MAX_OUTS 80  /* broadcast destinations per aggregation launch */
+
+/* ---- library -------------------------------------------------------------------------- */
+const char* ddl_last_error(void);
+/* number of kernels this library has launched in this process (bench.py: gpu_launches) */
+int64_t ddl_launch_count(void);
+void ddl_reset_launch_count(void);
+/* compiled-for architecture string, e.g. "sm_100a" */
+const char* ddl_arch(void);
+
+/* ---- K1: FedAvg / FedSGD aggregation (ref: lab/tutorial_1a/hfl_complete.py:291-306,370-383) --
+ * out[d] = alpha*base[d] + beta * sum_k weights[k]*updates[k*ld + d],  d in [0, D).
+ * `weights` is a HOST array (n_k / sum n) or NULL; `dev_weights` is a DEVICE array that, when
+ * non-NULL, overrides it (Krum's on-GPU selection weights); base may be NULL (alpha ignored). */
+int ddl_weighted_sum(const float* updates, int64_t ld, int K, const float* weights, const float* dev_weights,
+                     const float* base, float alpha, float beta, float* out, int64_t D, void* stream);
+/* Row-pointer form used by the coordinate-sharded multi-GPU exchange: rows[k] / outs[o] are HOST
+ * arrays of DEVICE pointers (local or peer-mapped); only coordinates [d0, d1) are touched and
+ * the result is stored to every outs[o].  peer_rows != 0 uses coherent loads (rows written by
+ * another GPU); max_ctas > 0 caps the grid (keep SMs free for overlapped compute). */
+int ddl_weighted_sum_rows(const float* const* rows, const float* weights, const float* dev_weights, int K,
+                          const float* base, float alpha, float beta, float* const* outs, int n_out, int64_t d0,
+                          int64_t d1, int peer_rows, int max_ctas, void* stream);
+
+/* ---- K4 / K5: coordinate-wise median, trimmed mean [north star] --------------------------- */
+/* lower != 0: lower median for even K (torch.median); else mean of the middle pair. K <= 128. */
+int ddl_coordinate_median(const float* updates, int64_t ld, int K, int lower, float* out, int64_t D, void* stream);
+/* per coordinate drop the `trim` smallest and largest values, mean the rest. K <= 128. */
+int ddl_trimmed_mean(const float* updates, int64_t ld, int K, int trim, float* out, int64_t D, void* stream);
+/* general form: mean of sorted ranks [lo, hi) over rows[0..K), coordinates [d0, d1), broadcast to outs[] */
+int ddl_rank_select_mean_rows(const float* const* rows, int K, int lo, int hi, float* const* outs, int n_out,
+                              int64_t d0, int64_t d1, void* stream);
+
+/* ---- K6: Byzantine perturbation [north star] ---------------------------------------------- */
+/* out = g - scale*(u - g) (+ uniform noise in [-noise, noise]); g == NULL treats g as 0. */
+int ddl_attack_perturb(const float* update, const float* global_or_null, float* out, float scale, float noise,
+                       uint32_t seed, int64_t D, void* stream);
+
+/* ---- K3 epilogue: Krum / Multi-Krum selection from a Gram matrix [north star] -------------- */
+/* gram: K x K (row stride ldg) device matrix G = U U^T.  Writes scores[K], sel[multi] (indices of
+ * the best rows, best first) and selw[K] (1/multi for selected rows else 0). */
+int ddl_krum_select(const float* gram, int ldg, int K, int n_byzantine, int multi, float* scores, int* sel,
+                    float* selw, void* stream);
+
+/* ---- K15: optimizer steps over flat arenas ----------------------------------------------------
+ * (ref: SGD lab/tutorial_1a/hfl_complete.py:196,306,319; Adam lab/tutorial_1b/DP/gradient_aggr/
+ *  intro_DP_GA.py:33,67; AdamW lab/tutorial_2b/vfl.py:50,82).  grads are multiplied by grad_scale
+ * first (folds the 1/world_size of a DP all-reduce into the step). n % 4 == 0. */
+int ddl_sgd_step(float* params, const float* grads, float* momentum_buf, int64_t n, float lr, float weight_decay,
+                 float momentum, float grad_scale, void* stream);
+int ddl_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, int step,
+                  float lr, float beta1, float beta2, float eps, float weight_decay, int decoupled,
+                  float grad_scale, void* stream);
+
+/* ---- K13: softmax cross-entropy, value + gradient in one pass ---------------------------------
+ * (ref: log_softmax+nll_loss hfl_complete.py:62,78; soft-target CE vfl.py:51,79; causalLLMLoss
+ *  lab/tutorial_1b/primer/intro.py:29).  Exactly one of target_idx (int64, element stride
+ * target_stride) / target_prob (float [N,C]) is non-NULL.  *loss_sum += loss_scale * sum_rows(loss_row)
+ * (caller zeroes it); grad (may be NULL) = (softmax*sum(t) - t) * grad_scale; rows whose index
+ * equals ignore_index are skipped; *n_valid (may be NULL) += number of contributing rows. */
+int ddl_softmax_xent(const float* logits, int64_t ld, const int64_t* target_idx, int64_t target_stride,
+                     const float* target_prob, float* grad, float* loss_sum, float* n_valid, int64_t N, int C,
+                     float loss_scale, float grad_scale, int64_t ignore_index, void* stream);
+/* ---- K17: *correct += #rows whose argmax equals target (ref: hfl_complete.py:172-183) ---------- */
+int ddl_eval_top1(const float* logits, int64_t ld, const int64_t* target, int64_t N, int C, int* correct,
+                  void* stream);
+/* ---- K14: VAE loss MSE(sum)+KL and its gradients (ref: lab/tutorial_2a/generative-modeling.py:
+ *  121-130; lab/tutorial_2b/exercise_3.py:140-147).  *loss += value (caller zeroes it). */
+int ddl_vae_loss(const float* x_recon, const float* x, int64_t nx, const float* mu, const float* logvar, int64_t nz,
+                 float* loss, float* grad_x_recon, float* grad_mu, float* grad_logvar, float grad_scale,
+                 void* stream);
+
+/* ---- K10 / K3: grouped GEMM on tcgen05 tensor cores (TMA-fed, TMEM accumulators) ---------------
+ * (ref: every nn.Linear, SURVEY 2.5 - e.g. lab/tutorial_1a/hfl_complete.py:58-61, lab/tutorial_2b/
+ *  vfl.py:21-22,37-39; Krum's Gram matrix U U^T is [north star]).
+ * C[g] = act(alpha * A[g] * B[g]^T + bias[g]),  A: M x K, B: N x K, C: M x N fp32, g < G.
+ *  - a_mn_major / b_mn_major == 0: operand stored [rows, K] (K contiguous, ld = row stride);
+ *    != 0: stored [K, rows] (rows contiguous, ld = k-row stride; rows % (128/dtype_bytes) == 0).
+ *  - dtype_bytes 4: fp32 operands, TF32 math; precise != 0 selects the 3xTF32 error-compensated
+ *    mode (fp32-grade products).  dtype_bytes 2: bf16 operands.
+ *  - act: 0 none, 1 relu, 2 leaky relu(slope).  bias may be NULL.
+ *  - n_split > 1: split-K; `scratch` must hold ddl_gemm_scratch_floats(M, N, G, n_split) floats
+ *    (partials are reduced in a fixed order, so results are deterministic). */
+int64_t ddl_gemm_scratch_floats(int M, int N, int G, int n_split);
+int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_mn_major, const void* B, int64_t ldb,
+                     int64_t b_group_stride, int b_mn_major, float* C, int64_t ldc, int64_t c_group_stride,
+                     const float* bias, int64_t bias_group_stride, int act, float slope, float alpha, int M, int N,
+                     int K, int G, int dtype_bytes, int precise, int n_split, float* scratch, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDL25_KERNELS_H_ */

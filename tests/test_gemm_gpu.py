@@ -1,0 +1,67 @@
+"""tcgen05 GEMM (K10) and Gram (K3) against fp64 oracles."""
+import pytest
+import torch
+
+from ddl25spring_b200.ops import gemm as G
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _rel_err(got, exp):
+    return float((got.double() - exp).abs().max() / exp.abs().max().clamp_min(1e-12))
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 32), (128, 128, 256), (100, 10, 128), (300, 200, 96), (64, 64, 4096),
+                                   (800, 128, 9216)])
+@pytest.mark.parametrize("precise", [False, True])
+def test_gemm_tn(cuda_lib, M, N, K, precise):
+    a, b = torch.randn(M, K, device=DEV), torch.randn(N, K, device=DEV)
+    bias = torch.randn(N, device=DEV)
+    got = G.gemm(a, b, bias=bias, act="relu", precise=precise)
+    exp = torch.relu(a.double() @ b.double().T + bias.double())
+    err = _rel_err(got, exp)
+    assert err < (1e-5 if precise else 3e-3), err
+
+
+@pytest.mark.parametrize("precise", [False, True])
+def test_gemm_mn_major_operands(cuda_lib, precise):
+    Bsz, nin, nout = 100, 256, 128
+    x, w, dy = (torch.randn(Bsz, nin, device=DEV), torch.randn(nout, nin, device=DEV),
+                torch.randn(Bsz, nout, device=DEV))
+    tol = 1e-5 if precise else 3e-3
+    dx = G.linear_dgrad(dy, w, precise=precise)
+    assert _rel_err(dx, dy.double() @ w.double()) < tol
+    dw = G.linear_wgrad(dy, x, precise=precise)
+    assert _rel_err(dw, dy.double().T @ x.double()) < tol
+
+
+def test_gemm_grouped_and_splitk(cuda_lib):
+    Gn, M, N, K = 8, 100, 128, 1024
+    a, b = torch.randn(Gn, M, K, device=DEV), torch.randn(Gn, N, K, device=DEV)
+    bias = torch.randn(Gn, N, device=DEV)
+    exp = torch.baddbmm(bias.double()[:, None, :], a.double(), b.double().transpose(1, 2))
+    got = G.gemm(a, b, bias=bias, precise=True)
+    assert _rel_err(got, exp) < 1e-5
+    got2 = G.gemm(a, b, bias=bias, precise=True, n_split=4)
+    assert _rel_err(got2, exp) < 1e-5
+    got3 = G.gemm(a, b, bias=bias, precise=True, n_split=4)
+    assert torch.equal(got2, got3), "split-K must be deterministic"
+
+
+def test_gemm_bf16(cuda_lib):
+    M, N, K = 256, 128, 512
+    a, b = torch.randn(M, K, device=DEV).bfloat16(), torch.randn(N, K, device=DEV).bfloat16()
+    got = G.gemm(a, b)
+    assert _rel_err(got, a.double() @ b.double().T) < 1e-5   # exact products of bf16 inputs, fp32 accumulate
+
+
+@pytest.mark.parametrize("K,D", [(64, 1_199_872 + 128), (10, 50_000), (128, 300_000)])
+def test_gram(cuda_lib, K, D):
+    u = 0.01 * torch.randn(K, D, device=DEV)
+    exp = u.double() @ u.double().T
+    got = G.gram_tcgen05(u)
+    assert _rel_err(got, exp) < 3e-3
+    gotp = G.gram_tcgen05(u, precise=True)
+    assert _rel_err(gotp, exp) < 5e-5
+    assert torch.equal(G.gram_tcgen05(u), got), "Gram must be deterministic"
