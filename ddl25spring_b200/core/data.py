@@ -69,14 +69,55 @@ def _make_images(n: int, n_classes: int, shape: tuple[int, ...], seed: int, nois
 
 
 class SyntheticMNIST:
-    """MNIST-shaped train/test pair: 1x28x28 fp32, 10 classes, mean≈0 / std≈1 like the
-    reference's ``Normalize((0.1307,), (0.3081,))`` output (hfl_complete.py:19-24)."""
+    """MNIST-shaped train/test pair.
+
+    The canonical form is uint8 pixels + uint8 labels, exactly like the real IDX files, so the
+    same synthetic set can be (a) normalised once into fp32 ``(x/255 - 0.1307)/0.3081`` for this
+    framework (``.train`` / ``.test``; hfl_complete.py:19-24) and (b) written to disk in IDX
+    format for the unmodified reference + torchvision to load (``write_idx``; bench.py
+    ``--impl reference``)."""
 
     def __init__(self, n_train: int = 60_000, n_test: int = 10_000, seed: int = 0, noise: float = 1.0):
-        xtr, ytr, tpl = _make_images(n_train, 10, (1, 28, 28), seed, noise)
-        xte, yte, _ = _make_images(n_test, 10, (1, 28, 28), seed + 1, noise, tpl)
-        self.train = TensorImageSet(xtr, ytr)
-        self.test = TensorImageSet(xte, yte)
+        rng = npr.default_rng(seed)
+        tpl = _class_templates(rng, 10, (1, 28, 28))
+
+        def make(n, sd):
+            r = npr.default_rng(sd)
+            y = r.integers(0, 10, size=n)
+            x = 110.0 + 60.0 * tpl[y] + 60.0 * noise * r.standard_normal((n, 1, 28, 28)).astype(np.float32)
+            return np.clip(np.rint(x), 0, 255).astype(np.uint8), y.astype(np.uint8)
+
+        self.train_u8, self.train_labels = make(n_train, seed + 101)
+        self.test_u8, self.test_labels = make(n_test, seed + 202)
+        self.train = TensorImageSet(self.normalize(self.train_u8), torch.from_numpy(self.train_labels.astype(np.int64)))
+        self.test = TensorImageSet(self.normalize(self.test_u8), torch.from_numpy(self.test_labels.astype(np.int64)))
+
+    @staticmethod
+    def normalize(u8: np.ndarray) -> torch.Tensor:
+        x = torch.from_numpy(u8).float().div_(255.0)
+        return x.sub_(MNIST_MEAN).div_(MNIST_STD)
+
+    def write_idx(self, raw_dir) -> None:
+        """Write the four MNIST IDX files torchvision looks for under ``<root>/MNIST/raw``."""
+        import os
+        import struct
+
+        os.makedirs(raw_dir, exist_ok=True)
+
+        def images(name, a):
+            with open(os.path.join(raw_dir, name), "wb") as f:
+                f.write(struct.pack(">IIII", 2051, a.shape[0], 28, 28))
+                f.write(a.reshape(a.shape[0], 28, 28).tobytes())
+
+        def labels(name, a):
+            with open(os.path.join(raw_dir, name), "wb") as f:
+                f.write(struct.pack(">II", 2049, a.shape[0]))
+                f.write(a.tobytes())
+
+        images("train-images-idx3-ubyte", self.train_u8)
+        labels("train-labels-idx1-ubyte", self.train_labels)
+        images("t10k-images-idx3-ubyte", self.test_u8)
+        labels("t10k-labels-idx1-ubyte", self.test_labels)
 
 
 class SyntheticCIFAR:

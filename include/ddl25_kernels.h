@@ -111,6 +111,23 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
                      const float* bias, int64_t bias_group_stride, int act, float slope, float alpha, int M, int N,
                      int K, int G, int dtype_bytes, int precise, int n_split, float* scratch, void* stream);
 
+/* ---- Packed MnistCnn engine: G clients trained in lock-step, grouped kernels -------------------
+ * (ref: MnistCnn forward/backward + train_epoch, lab/tutorial_1a/hfl_complete.py:39-80, executed
+ *  for all clients packed on the GPU at once instead of one client at a time, :365-375).
+ * W: [G][1 200 000] flat weight arena (FlatArena layout of MnistCnn); rows = G*B activation rows;
+ * bsz[g] = valid rows of client g in this step; perm (may be NULL) = per-client sample order. */
+int ddl_mnist_conv1_fwd(const float* W, const float* X, int64_t x_client_stride, const int* perm, int64_t perm_stride,
+                        int sample_off, float* a1, int G, int B, const int* bsz, void* stream);
+int ddl_mnist_prep_conv2(const float* W, float* wt_fwd, float* wt_dgrad, int G, void* stream);
+/* K9 fprop on tcgen05: conv2 (implicit GEMM, TF32) + bias + ReLU + 2x2 max-pool (+ dropout) */
+int ddl_mnist_conv2_pool_fwd(const float* W, const float* wt_fwd, const float* a1, float* pooled, uint8_t* pmask,
+                             int G, int B, const int* bsz, int train, float p_drop, uint32_t seed, void* stream);
+int ddl_mnist_head_train(float* W, const float* h1, const int64_t* Y, int64_t y_client_stride, const int* perm,
+                         int64_t perm_stride, int sample_off, float* dz1, float* loss_out, int G, int B,
+                         const int* bsz, float p_drop, uint32_t seed, float lr, void* stream);
+int ddl_mnist_head_eval(const float* W, const float* h1, const int64_t* Y, int sample_off, int nrows, float* logits_out,
+                        int* correct, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
