@@ -42,6 +42,7 @@ struct Epilogue {
   int act;              // 0 none, 1 relu, 2 leaky relu
   float slope;
   float alpha;
+  float beta;           // direct (n_split == 1) path only: C = act(alpha*acc + beta*C_old + bias)
   int n_split;          // > 1: write raw partial tiles to C = scratch[split][g][M][N] (ldc = N)
 };
 
@@ -246,6 +247,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
           for (int j = 0; j < 4; ++j) {
             float x = v[i + j] * epi.alpha;
             if (n_split == 1) {
+              if (epi.beta != 0.f && n + j < N) x = fmaf(epi.beta, crow[i + j], x);
               if (bias && n + j < N) x += bias[n + j];
               x = apply_act(x, epi.act, epi.slope);
             }
@@ -347,8 +349,9 @@ int64_t ddl_gemm_scratch_floats(int M, int N, int G, int n_split) {
 
 int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_mn_major, const void* B, int64_t ldb,
                      int64_t b_group_stride, int b_mn_major, float* C, int64_t ldc, int64_t c_group_stride,
-                     const float* bias, int64_t bias_group_stride, int act, float slope, float alpha, int M, int N,
-                     int K, int G, int dtype_bytes, int precise, int n_split, float* scratch, void* stream) {
+                     const float* bias, int64_t bias_group_stride, int act, float slope, float alpha, float beta,
+                     int M, int N, int K, int G, int dtype_bytes, int precise, int n_split, float* scratch,
+                     void* stream) {
   DDL_REQUIRE(M > 0 && N > 0 && K > 0 && G > 0, "empty GEMM");
   DDL_REQUIRE(dtype_bytes == 4 || dtype_bytes == 2, "operands must be fp32 (tf32 math) or bf16");
   DDL_REQUIRE(!(precise && dtype_bytes != 4), "precise (3xTF32) mode needs fp32 operands");
@@ -359,6 +362,7 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
   if (n_split < 1) n_split = 1;
   const int total_kb = (K + bk - 1) / bk;
   if (n_split > total_kb) n_split = total_kb;
+  DDL_REQUIRE(n_split == 1 || beta == 0.f, "beta (accumulate into C) is only supported without split-K");
   DDL_REQUIRE(n_split == 1 || scratch != nullptr, "split-K needs a scratch buffer of ddl_gemm_scratch_floats() floats");
   const int kbps = (total_kb + n_split - 1) / n_split;
   n_split = (total_kb + kbps - 1) / kbps;
@@ -376,7 +380,7 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
   epi.C = n_split > 1 ? scratch : C;
   epi.ldc = ldc; epi.c_group_stride = c_group_stride;
   epi.bias = bias; epi.bias_group_stride = bias_group_stride;
-  epi.act = act; epi.slope = slope; epi.alpha = alpha; epi.n_split = n_split;
+  epi.act = act; epi.slope = slope; epi.alpha = alpha; epi.beta = beta; epi.n_split = n_split;
   cudaStream_t st = (cudaStream_t)stream;
   int rc;
   const bool amn = a_mn_major != 0, bmn = b_mn_major != 0;

@@ -105,3 +105,65 @@ class PackedMnistEngine:
                                                   _lib.p(logits[lo:] if want_logits else None), _lib.p(correct),
                                                   _lib.stream()), "head_eval")
         return logits
+
+
+# ====================================================================== training (appended methods)
+def _alloc_train_scratch(self) -> None:
+    if getattr(self, "wg_part", None) is None:
+        f32 = dict(device=self.device, dtype=torch.float32)
+        self.n_cta = int(self.L.ddl_mnist_wgrad_ctas(self.G))
+        self.wg_part = torch.zeros(self.G * self.n_cta * 3 * 128 * 64, **f32)
+        self.c2b_part = torch.zeros(self.G * self.B, 64, **f32)
+        self.c1_part = torch.zeros(self.G * self.B, 320, **f32)
+
+
+def train_step(self, W, X, x_stride, Y, y_stride, perm, perm_stride, sample_off, bsz, lr: float, seed: int) -> None:
+    """One lock-step SGD step of all G clients (forward, backward and in-place update of ``W``)."""
+    _alloc_train_scratch(self)
+    L, G, B, st = self.L, self.G, self.B, _lib.stream
+    cb = _ints(bsz)
+    Wv = W.view(G, P)
+    w1 = Wv[:, OFF["fc1.weight"]:OFF["fc1.weight"] + FC1 * FLAT].unflatten(1, (FC1, FLAT))
+    self.forward_features(W, X, x_stride, perm, perm_stride, sample_off, bsz, True, seed)
+    _lib.check(L.ddl_mnist_head_train(_lib.p(W), _lib.p(self.h1), _lib.p(Y), _lib.i64(y_stride), _lib.p(perm),
+                                      _lib.i64(perm_stride), int(sample_off), _lib.p(self.dz1), _lib.p(self.loss), G, B, cb,
+                                      _lib.f32(self.p2), int(seed) & 0xFFFFFFFF, _lib.f32(lr), st()), "head_train")
+    # fc1 backward: dgrad first (reads the old weights), then wgrad with the SGD step fused in its epilogue
+    gemm(self.dz1, w1, b_mn=True, precise=True, out=self.dpool)
+    gemm(self.dz1, self.pooled, a_mn=True, b_mn=True, precise=True, alpha=-lr, beta=1.0, out=w1)
+    _lib.check(L.ddl_mnist_pool_bwd(_lib.p(self.dpool), _lib.p(self.pmask), _lib.p(self.dy2), _lib.p(self.c2b_part), G, B,
+                                    cb, _lib.f32(self.p1), st()), "pool_bwd")
+    _lib.check(L.ddl_mnist_conv2_dgrad(_lib.p(self.wt_dgrad), _lib.p(self.dy2), _lib.p(self.a1), _lib.p(self.da1), G, B, cb,
+                                       st()), "conv2_dgrad")
+    _lib.check(L.ddl_mnist_conv2_wgrad(_lib.p(self.a1), _lib.p(self.dy2), _lib.p(self.wg_part), G, B, cb, st()),
+               "conv2_wgrad")
+    _lib.check(L.ddl_mnist_conv1_wgrad(_lib.p(X), _lib.i64(x_stride), _lib.p(perm), _lib.i64(perm_stride), int(sample_off),
+                                       _lib.p(self.da1), _lib.p(self.c1_part), G, B, cb, st()), "conv1_wgrad")
+    _lib.check(L.ddl_mnist_small_update(_lib.p(W), _lib.p(self.wg_part), self.n_cta, _lib.p(self.c2b_part),
+                                        _lib.p(self.c1_part), _lib.p(self.wt_fwd), _lib.p(self.wt_dgrad), G, B, cb,
+                                        _lib.f32(lr), st()), "small_update")
+
+
+def local_train(self, W, X, Y, perm, counts, batch_size: int, epochs: int, lr: float, seed: int) -> int:
+    """``epochs`` local epochs of minibatch SGD for all clients at once.
+
+    ``W`` [G, P] weights (updated in place), ``X`` [G, n_max, 784], ``Y`` [G, n_max] int64,
+    ``perm`` [G, epochs * n_max] int32 sample orders (epoch e at column offset e * n_max),
+    ``counts`` host list of per-client sample counts.  Returns the number of steps run."""
+    n_max = X.shape[1]
+    assert batch_size <= self.B
+    self.prep_weights(W)
+    steps = 0
+    n_steps = -(-max(counts) // batch_size)
+    for e in range(epochs):
+        for s in range(n_steps):
+            off = s * batch_size
+            bsz = [max(0, min(batch_size, int(c) - off)) for c in counts]
+            train_step(self, W, X, n_max * 784, Y, n_max, perm, perm.shape[1], e * n_max + off, bsz, lr,
+                       (seed * 2654435761 + e * 7919 + s * 104729) & 0xFFFFFFFF)
+            steps += 1
+    return steps
+
+
+PackedMnistEngine.train_step = train_step
+PackedMnistEngine.local_train = local_train

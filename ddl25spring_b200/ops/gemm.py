@@ -33,7 +33,8 @@ def _grouped(t: torch.Tensor):
 
 
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False, bias: torch.Tensor | None = None,
-         act: str | None = None, slope: float = 0.01, alpha: float = 1.0, precise: bool = False, n_split: int = 1,
+         act: str | None = None, slope: float = 0.01, alpha: float = 1.0, beta: float = 0.0, precise: bool = False,
+         n_split: int = 1,
          out: torch.Tensor | None = None) -> torch.Tensor:
     """``C = act(alpha * op(A) @ op(B)^T + bias)``.
 
@@ -57,7 +58,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.shape[-1] == N
         bias_stride = bias.stride(0) if bias.dim() == 2 else 0
-    if precise:
+    if precise and beta == 0.0:
         # The tensor core's fp32 accumulator truncates on every add, so the error of a K-long chain
         # grows ~linearly in K (measured on B200: 2e-6 at K=128, 8e-5 at K=9216).  Cap each
         # accumulation chain at PRECISE_CHAIN products and finish the sum in fp32 on the CUDA cores.
@@ -70,7 +71,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         _lib.p(A), _lib.i64(A.stride(1)), _lib.i64(A.stride(0)), int(a_mn),
         _lib.p(B), _lib.i64(B.stride(1)), _lib.i64(B.stride(0)), int(b_mn),
         _lib.p(O), _lib.i64(O.stride(1)), _lib.i64(O.stride(0)),
-        _lib.p(bias), _lib.i64(bias_stride), ACT[act], _lib.f32(slope), _lib.f32(alpha),
+        _lib.p(bias), _lib.i64(bias_stride), ACT[act], _lib.f32(slope), _lib.f32(alpha), _lib.f32(beta),
         int(M), int(N), int(K), int(G), int(eb), int(precise), int(n_split), _lib.p(scratch), _lib.stream())
     _lib.check(rc, "ddl_gemm_tcgen05")
     return out[0] if (squeeze and out.dim() == 3) else out

@@ -97,7 +97,8 @@ int ddl_vae_loss(const float* x_recon, const float* x, int64_t nx, const float* 
 /* ---- K10 / K3: grouped GEMM on tcgen05 tensor cores (TMA-fed, TMEM accumulators) ---------------
  * (ref: every nn.Linear, SURVEY 2.5 - e.g. lab/tutorial_1a/hfl_complete.py:58-61, lab/tutorial_2b/
  *  vfl.py:21-22,37-39; Krum's Gram matrix U U^T is [north star]).
- * C[g] = act(alpha * A[g] * B[g]^T + bias[g]),  A: M x K, B: N x K, C: M x N fp32, g < G.
+ * C[g] = act(alpha * A[g] * B[g]^T + beta * C[g] + bias[g]),  A: M x K, B: N x K, C: M x N fp32, g < G
+ * (beta != 0 needs n_split == 1; alpha = -lr, beta = 1 fuses the SGD step into a weight-gradient GEMM).
  *  - a_mn_major / b_mn_major == 0: operand stored [rows, K] (K contiguous, ld = row stride);
  *    != 0: stored [K, rows] (rows contiguous, ld = k-row stride; rows % (128/dtype_bytes) == 0).
  *  - dtype_bytes 4: fp32 operands, TF32 math; precise != 0 selects the 3xTF32 error-compensated
@@ -108,8 +109,9 @@ int ddl_vae_loss(const float* x_recon, const float* x, int64_t nx, const float* 
 int64_t ddl_gemm_scratch_floats(int M, int N, int G, int n_split);
 int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_mn_major, const void* B, int64_t ldb,
                      int64_t b_group_stride, int b_mn_major, float* C, int64_t ldc, int64_t c_group_stride,
-                     const float* bias, int64_t bias_group_stride, int act, float slope, float alpha, int M, int N,
-                     int K, int G, int dtype_bytes, int precise, int n_split, float* scratch, void* stream);
+                     const float* bias, int64_t bias_group_stride, int act, float slope, float alpha, float beta,
+                     int M, int N, int K, int G, int dtype_bytes, int precise, int n_split, float* scratch,
+                     void* stream);
 
 /* ---- Packed MnistCnn engine: G clients trained in lock-step, grouped kernels -------------------
  * (ref: MnistCnn forward/backward + train_epoch, lab/tutorial_1a/hfl_complete.py:39-80, executed
@@ -127,6 +129,20 @@ int ddl_mnist_head_train(float* W, const float* h1, const int64_t* Y, int64_t y_
                          const int* bsz, float p_drop, uint32_t seed, float lr, void* stream);
 int ddl_mnist_head_eval(const float* W, const float* h1, const int64_t* Y, int sample_off, int nrows, float* logits_out,
                         int* correct, void* stream);
+
+/* backward of the packed engine (ref: autograd backward + optimizer.step, hfl_complete.py:79-80) */
+int ddl_mnist_pool_bwd(const float* dpool, const uint8_t* pmask, float* dy2, float* c2b_part, int G, int B,
+                       const int* bsz, float p_drop, void* stream);
+int ddl_mnist_conv2_dgrad(const float* wt_dgrad, const float* dy2, const float* a1, float* da1, int G, int B,
+                          const int* bsz, void* stream);
+/* wg_part: [G][ddl_mnist_wgrad_ctas(G)][3][128][64] floats of scratch */
+int ddl_mnist_wgrad_ctas(int G);
+int ddl_mnist_conv2_wgrad(const float* a1, const float* dy2, float* wg_part, int G, int B, const int* bsz,
+                          void* stream);
+int ddl_mnist_conv1_wgrad(const float* X, int64_t x_client_stride, const int* perm, int64_t perm_stride, int sample_off,
+                          const float* da1, float* c1_part, int G, int B, const int* bsz, void* stream);
+int ddl_mnist_small_update(float* W, const float* wg_part, int n_cta, const float* c2b_part, const float* c1_part,
+                           float* wt_fwd, float* wt_dgrad, int G, int B, const int* bsz, float lr, void* stream);
 
 #ifdef __cplusplus
 }
