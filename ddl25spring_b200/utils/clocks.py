@@ -18,7 +18,7 @@ _REASON_BITS = {
 class ClockSampler:
     """Background sampler: NVML when importable, else ``nvidia-smi`` polling."""
 
-    def __init__(self, device_index: int = 0, period_s: float = 0.1):
+    def __init__(self, device_index: int = 0, period_s: float = 0.02):
         self.idx, self.period = device_index, period_s
         self.samples: list[int] = []
         self.reasons: set[str] = set()
