@@ -144,6 +144,24 @@ int ddl_mnist_conv1_wgrad(const float* X, int64_t x_client_stride, const int* pe
 int ddl_mnist_small_update(float* W, const float* wg_part, int n_cta, const float* c2b_part, const float* c1_part,
                            float* wt_fwd, float* wt_dgrad, int G, int B, const int* bsz, float lr, void* stream);
 
+/* ---- Gram matrix without any allocation (no counterpart in the reference) ----------------------
+ * G = U U^T like ddl_gemm_tcgen05(A = B = U, n_split > 1), for callers that cannot provide a scratch
+ * buffer at call time: plain C/C++ hosts without PyTorch's caching allocator, or services whose
+ * memory is fixed at start-up and for which a cudaMalloc in the round loop (it synchronises the
+ * device and may fail late) is not acceptable.  The split-K partial tiles go to a static device
+ * array that ships inside the library: DDL_GRAM_STATIC_SCRATCH_FLOATS floats (4 MiB) held by every
+ * GPU that loads the library until the process exits.  This call never allocates or frees.
+ *  - limit: n_split * K * K <= DDL_GRAM_STATIC_SCRATCH_FLOATS (K <= 128 clients), else an error;
+ *  - all calls on a device share the one array: calls that may overlap on the GPU race - keep them
+ *    on one stream (or order them with events); leftover contents never need clearing because every
+ *    partial tile is fully rewritten before it is read;
+ *  - the first call on each device looks up the array's device address (cudaGetSymbolAddress) and
+ *    does the one-time kernel set-up: make that first call before starting any stream capture.
+ * updates: [K, D] fp32, row stride ld (ld*4 and the pointer 16-byte aligned); gram: [K, K], row stride ldg. */
+#define DDL_GRAM_STATIC_SCRATCH_FLOATS (1 << 20)
+int ddl_gram_static_scratch(const float* updates, int64_t ld, int K, int64_t D, float* gram, int64_t ldg,
+                            int n_split, int precise, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
