@@ -210,8 +210,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     }
     // ---- epilogue: TMEM -> registers -> global
     const int quarter = warp & 3;            // TMEM lane quarter this warp may read
-    const int row = quarter * 32 + lane;     // accumulator row == TMEM lane
-    const int m = m0 + row;
     if (num_kb > 0) {
       mbar_wait(accum_bar, 0);
       fence_after_thread_sync();
@@ -226,9 +224,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       ldc = epi.ldc;
     }
     const float* bias = (epi.bias && n_split == 1) ? epi.bias + (int64_t)g * epi.bias_group_stride : nullptr;
-    const bool vec_ok = (ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(Cg) & 15) == 0);
+    const bool direct = (n_split == 1);
+    // Transpose each 32x32 accumulator chunk through a per-warp shared-memory tile (the operand ring is
+    // idle by now) so that every global access of the warp is one contiguous 128-byte row segment:
+    // lane = column.  The C reads of the beta path are issued as a batch before they are consumed.
+    float* wsm = reinterpret_cast<float*>(stage_base) + (warp - 2) * (32 * 33);
+    const int mrow0 = m0 + quarter * 32;
 #pragma unroll 1
     for (int c0 = 0; c0 < BN; c0 += 32) {
+      if (n0 + c0 >= N) break;
       float v[32];
       if (num_kb > 0) {
         tmem_ld_32x32(tmem_acc + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0, v);
@@ -236,30 +240,27 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = 0.f;
       }
-      if (m < M) {
-        float* crow = Cg + (int64_t)m * ldc + n0 + c0;
 #pragma unroll
-        for (int i = 0; i < 32; i += 4) {
-          const int n = n0 + c0 + i;
-          if (n >= N) break;
-          float o[4];
+      for (int i = 0; i < 32; ++i) wsm[lane * 33 + i] = v[i] * epi.alpha;
+      __syncwarp();
+      const int n = n0 + c0 + lane;
+      const bool ncol_ok = n < N;
+      const float bn = (bias && ncol_ok) ? bias[n] : 0.f;
+      float* cbase = Cg + (int64_t)mrow0 * ldc + n;
+      if (direct && epi.beta != 0.f) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            float x = v[i + j] * epi.alpha;
-            if (n_split == 1) {
-              if (epi.beta != 0.f && n + j < N) x = fmaf(epi.beta, crow[i + j], x);
-              if (bias && n + j < N) x += bias[n + j];
-              x = apply_act(x, epi.act, epi.slope);
-            }
-            o[j] = x;
-          }
-          if (vec_ok && n + 3 < N) {
-            *reinterpret_cast<float4*>(crow + i) = make_float4(o[0], o[1], o[2], o[3]);
-          } else {
-            for (int j = 0; j < 4 && n + j < N; ++j) crow[i + j] = o[j];
-          }
-        }
+        for (int rr = 0; rr < 32; ++rr) v[rr] = (ncol_ok && mrow0 + rr < M) ? cbase[(int64_t)rr * ldc] : 0.f;
       }
+#pragma unroll
+      for (int rr = 0; rr < 32; ++rr) {
+        float x = wsm[rr * 33 + lane];
+        if (direct) {
+          if (epi.beta != 0.f) x = fmaf(epi.beta, v[rr], x);
+          x = apply_act(x + bn, epi.act, epi.slope);
+        }
+        if (ncol_ok && mrow0 + rr < M) cbase[(int64_t)rr * ldc] = x;
+      }
+      __syncwarp();
     }
     fence_before_thread_sync();
   }

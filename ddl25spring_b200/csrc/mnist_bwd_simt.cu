@@ -145,9 +145,9 @@ __global__ void __launch_bounds__(256) small_update_kernel(float* __restrict__ W
   const int n = si.bsz[g];
   float* Wg = W + (int64_t)g * P;
   const int nthreads = gridDim.x * blockDim.x;
-  const int total = 9 * C1 * C2 + C2 + 320;
+  const int total = 9 * C1 * C2;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += nthreads) {
-    if (i < 9 * C1 * C2) {
+    {
       const int co = i & 63, ci = (i >> 6) & 31, tap = i >> 11;
       const int r = tap / 3, s = tap % 3;
       float* wp = Wg + OFF_C2W + (co * C1 + ci) * 9 + tap;
@@ -155,6 +155,7 @@ __global__ void __launch_bounds__(256) small_update_kernel(float* __restrict__ W
       if (n > 0) {
         const float* pp = wg_part + (((int64_t)g * n_cta * 3 + r) * 128 + s * 32 + ci) * 64 + co;
         float sum = 0.f;
+#pragma unroll 6
         for (int jc = 0; jc < n_cta; ++jc) sum += pp[(int64_t)jc * 3 * 128 * 64];
         wv -= si.lr * sum;
         *wp = wv;
@@ -162,16 +163,25 @@ __global__ void __launch_bounds__(256) small_update_kernel(float* __restrict__ W
       const float tv = ddl::to_tf32(wv);
       wt_fwd[(int64_t)g * 9 * C2 * C1 + (tap * C2 + co) * C1 + ci] = tv;
       wt_dgrad[(int64_t)g * 9 * C2 * C1 + ((tap * 2 + (co >> 5)) * C1 + ci) * 32 + (co & 31)] = tv;
-    } else if (n > 0) {
-      const int k = i - 9 * C1 * C2;
+    }
+  }
+  // small reductions over the client's rows: one warp per output, lanes stride over the rows
+  if (n > 0) {
+    const int lane = threadIdx.x & 31;
+    const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = nthreads >> 5;
+    for (int k = wid; k < C2 + 320; k += nwarps) {
       float sum = 0.f;
       if (k < C2) {
-        for (int b = 0; b < n; ++b) sum += c2b_part[((int64_t)g * si.B + b) * C2 + k];
-        Wg[OFF_C2B + k] -= si.lr * sum;
+        for (int b = lane; b < n; b += 32) sum += c2b_part[((int64_t)g * si.B + b) * C2 + k];
       } else {
+        for (int b = lane; b < n; b += 32) sum += c1_part[((int64_t)g * si.B + b) * 320 + (k - C2)];
+      }
+      sum = ddl::warp_sum(sum);
+      if (lane == 0) {
         const int o = k - C2;
-        for (int b = 0; b < n; ++b) sum += c1_part[((int64_t)g * si.B + b) * 320 + o];
-        Wg[(o < 288 ? OFF_C1W + o : OFF_C1B + (o - 288))] -= si.lr * sum;
+        float* dst = k < C2 ? Wg + OFF_C2B + k : Wg + (o < 288 ? OFF_C1W + o : OFF_C1B + (o - 288));
+        *dst -= si.lr * sum;
       }
     }
   }

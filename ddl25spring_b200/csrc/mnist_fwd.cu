@@ -90,7 +90,9 @@ constexpr int W_BYTES = 9 * W_TILE_BYTES;              // 72 KB
 constexpr int WIN_BYTES = WIN_ROWS * 128;              // 23 552 B (multiple of 1024)
 constexpr int STG_PITCH = 68;                          // floats; conflict-free for row writes and column reads
 constexpr int STG_BYTES = TILE_M * STG_PITCH * 4;
-constexpr int CONV2_SMEM = W_BYTES + kStages * WIN_BYTES + STG_BYTES + 256 + 1024;
+constexpr int POOL_PITCH = 25;                          // floats per channel of the pooled staging tile (24 + 1 pad)
+constexpr int POOL_BYTES = C2 * POOL_PITCH * 4 + C2 * 24 + C2 * 4;   // pooled values | mask bytes | bias
+constexpr int CONV2_SMEM = W_BYTES + kStages * WIN_BYTES + STG_BYTES + POOL_BYTES + 256 + 1024;
 
 struct Conv2Params {
   const float* W;        // weight arena base (bias read from OFF_C2B of each client's row)
@@ -111,7 +113,10 @@ conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_co
   uint8_t* s_w = smem;
   uint8_t* s_win = smem + W_BYTES;
   float* s_stage = reinterpret_cast<float*>(s_win + kStages * WIN_BYTES);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(s_stage) + STG_BYTES);
+  float* s_pool = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(s_stage) + STG_BYTES);   // [64][25]
+  uint8_t* s_pmask = reinterpret_cast<uint8_t*>(s_pool + C2 * POOL_PITCH);                     // [64][24]
+  float* s_bias = reinterpret_cast<float*>(s_pmask + C2 * 24);                                 // [64]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(s_stage) + STG_BYTES + POOL_BYTES);
   uint64_t* full_bar = bars;                 // [kStages] window landed
   uint64_t* empty_bar = bars + kStages;      // [kStages] MMAs reading the window retired
   uint64_t* acc_full = bars + 2 * kStages;   // [2]
@@ -195,7 +200,8 @@ conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_co
     const int m = quarter * 32 + lane;            // accumulator row = flat position inside the tile
     const int et = (warp - 2) * 32 + lane;        // 0..127 for the pooling phase
     const int pc = et & 63, half = et >> 6;       // pooled channel / pooled row within the tile
-    const float* bias_g = prm.W + (int64_t)g * P + OFF_C2B;
+    if (et < C2) s_bias[et] = prm.W[(int64_t)g * P + OFF_C2B + et];
+    epi_bar_sync();
     const float keep_scale = TRAIN ? 1.f / (1.f - si.p1) : 1.f;
     uint32_t acc_phase = 0;
     int buf = 0;
@@ -212,10 +218,11 @@ conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_co
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
           float4 o;
-          o.x = fmaxf(v[i] + __ldg(bias_g + c0 + i), 0.f);
-          o.y = fmaxf(v[i + 1] + __ldg(bias_g + c0 + i + 1), 0.f);
-          o.z = fmaxf(v[i + 2] + __ldg(bias_g + c0 + i + 2), 0.f);
-          o.w = fmaxf(v[i + 3] + __ldg(bias_g + c0 + i + 3), 0.f);
+          const float4 bb = *reinterpret_cast<const float4*>(s_bias + c0 + i);
+          o.x = fmaxf(v[i] + bb.x, 0.f);
+          o.y = fmaxf(v[i + 1] + bb.y, 0.f);
+          o.z = fmaxf(v[i + 2] + bb.z, 0.f);
+          o.w = fmaxf(v[i + 3] + bb.w, 0.f);
           dst[i >> 2] = o;
         }
       }
@@ -223,9 +230,9 @@ conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_co
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);   // TMEM buffer may be overwritten by tile t+2
       epi_bar_sync();
-      // pooled row ph = 2*hb + half ; window rows (2*half, 2*half+1) of the 4-row tile
-      const int ph = hb * 2 + half;
-      const int64_t obase = (int64_t)row * FLAT + pc * (HP * HP) + ph * HP;
+      // pooled row ph = 2*hb + half ; window rows (2*half, 2*half+1) of the 4-row tile.  Results go to
+      // a small staging tile first so that the global stores below are contiguous 96 B runs per channel.
+      const int64_t tile_base = (int64_t)row * FLAT + hb * 2 * HP;      // + c*144 + [0, 24)
 #pragma unroll 4
       for (int pw = 0; pw < HP; ++pw) {
         const int m00 = (2 * half) * H1 + 2 * pw;
@@ -237,11 +244,24 @@ conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_co
         if (v10 > best) { best = v10; arg = 2; }
         if (v11 > best) { best = v11; arg = 3; }
         bool keep = true;
-        if (TRAIN) keep = ddl::rng_uniform(si.seed, (uint32_t)(obase + pw)) >= si.p1;
-        prm.pooled[obase + pw] = keep ? best * keep_scale : 0.f;
-        if (TRAIN) prm.pmask[obase + pw] = (uint8_t)(arg | ((keep && best > 0.f) ? 4 : 0));
+        const int o = half * HP + pw;
+        if (TRAIN) keep = ddl::rng_uniform(si.seed, (uint32_t)(tile_base + pc * (HP * HP) + o)) >= si.p1;
+        s_pool[pc * POOL_PITCH + o] = keep ? best * keep_scale : 0.f;
+        if (TRAIN) s_pmask[pc * 24 + o] = (uint8_t)(arg | ((keep && best > 0.f) ? 4 : 0));
       }
-      epi_bar_sync();                                  // staging buffer is reused by the next tile
+      epi_bar_sync();
+      for (int idx = et; idx < C2 * 6; idx += 128) {                    // 64 channels x 6 float4
+        const int c = idx / 6, k4 = idx % 6;
+        const float* src = s_pool + c * POOL_PITCH + 4 * k4;
+        *reinterpret_cast<float4*>(prm.pooled + tile_base + c * (HP * HP) + 4 * k4) = make_float4(src[0], src[1], src[2], src[3]);
+      }
+      if (TRAIN) {
+        for (int idx = et; idx < C2 * 3; idx += 128) {                  // 64 channels x 3 x 8 mask bytes
+          const int c = idx / 3, k8 = idx % 3;
+          *reinterpret_cast<uint2*>(prm.pmask + tile_base + c * (HP * HP) + 8 * k8) =
+              *reinterpret_cast<const uint2*>(s_pmask + c * 24 + 8 * k8);
+        }
+      }
       if (++buf == 2) { buf = 0; acc_phase ^= 1; }
     }
   }

@@ -57,7 +57,7 @@ class PackedMnistEngine:
         self.h1 = torch.zeros(G, B, FC1, **f32)
         self.wt_fwd = torch.zeros(G * 9 * 64, 32, **f32)
         self.wt_dgrad = torch.zeros(G * 9 * 64, 32, **f32)
-        self.n_split_fc1 = 9
+        self.n_split_fc1 = 18 if train else 9    # K = 9216: 512-long chains, 8 clients x 18 = 144 CTAs
         if train:
             self.pmask = torch.zeros(rows, FLAT, device=self.device, dtype=torch.uint8)
             self.dz1 = torch.zeros(G, B, FC1, **f32)
