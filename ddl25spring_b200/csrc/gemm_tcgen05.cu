@@ -144,27 +144,24 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
       mbar_wait(SPLIT3 ? &split_bar[s] : &full_bar[s], phase);
       fence_after_thread_sync();
       if (elect_one()) {
+        // K-major : a k-step advances 32 B inside the 128 B swizzle row; 8-row groups are 1024 B apart.
+        // MN-major: a k-step is UMMA_K k-rows of 128 B; MN atoms are BK*128 B apart; 32-bit MN-major
+        //           operands must use the 128B swizzle with 32B atoms (pattern period 4 k-rows, SBO 512).
+        constexpr uint32_t a_lay = (A_MN && EB == 4) ? LAYOUT_SW128_BASE32B : LAYOUT_SW128;
+        constexpr uint32_t b_lay = (B_MN && EB == 4) ? LAYOUT_SW128_BASE32B : LAYOUT_SW128;
+        constexpr uint32_t a_sbo = (A_MN && EB == 4) ? 512 : 1024, b_sbo = (B_MN && EB == 4) ? 512 : 1024;
+        constexpr uint32_t a_lbo = A_MN ? BK * ROW_BYTES : 16, b_lbo = B_MN ? BK * ROW_BYTES : 16;
+        constexpr uint32_t a_step = A_MN ? UMMA_K * ROW_BYTES : 32, b_step = B_MN ? UMMA_K * ROW_BYTES : 32;
         const uint32_t a_hi = smem_u32(stage_base + s * Plan::STAGE_BYTES);
-        const uint32_t b_hi = a_hi + Plan::A_BYTES;
-        const uint32_t a_lo = b_hi + Plan::B_BYTES;
-        const uint32_t b_lo = a_lo + Plan::A_BYTES;
+        const uint64_t da_hi0 = smem_desc_sw128(a_hi, a_lbo, a_sbo, a_lay);
+        const uint64_t db_hi0 = smem_desc_sw128(a_hi + Plan::A_BYTES, b_lbo, b_sbo, b_lay);
+        constexpr uint32_t LO_OFF = Plan::A_BYTES + Plan::B_BYTES;       // lo tiles follow the hi tiles
 #pragma unroll
         for (int kk = 0; kk < KSTEPS; ++kk) {
-          // K-major : advance 32 B inside the 128 B swizzle row; 8-row groups are 1024 B apart
-          // MN-major: one k-step = UMMA_K k-rows of 128 B (8-row swizzle atoms 1024 B apart); MN atoms BK*128 B apart
-          const uint32_t a_off = A_MN ? kk * UMMA_K * ROW_BYTES : kk * 32;
-          const uint32_t b_off = B_MN ? kk * UMMA_K * ROW_BYTES : kk * 32;
-          const uint32_t a_lbo = A_MN ? BK * ROW_BYTES : 16, b_lbo = B_MN ? BK * ROW_BYTES : 16;
           const bool acc = (kb > 0) || (kk > 0);
-          // 32-bit MN-major operands must use the 128B swizzle with 32B atoms (pattern period 4 k-rows)
-          constexpr uint32_t a_lay = (A_MN && EB == 4) ? LAYOUT_SW128_BASE32B : LAYOUT_SW128;
-          constexpr uint32_t b_lay = (B_MN && EB == 4) ? LAYOUT_SW128_BASE32B : LAYOUT_SW128;
-          constexpr uint32_t a_sbo = (A_MN && EB == 4) ? 512 : 1024, b_sbo = (B_MN && EB == 4) ? 512 : 1024;
-          const uint64_t da_hi = smem_desc_sw128(a_hi + a_off, a_lbo, a_sbo, a_lay);
-          const uint64_t db_hi = smem_desc_sw128(b_hi + b_off, b_lbo, b_sbo, b_lay);
+          const uint64_t da_hi = desc_advance(da_hi0, kk * a_step), db_hi = desc_advance(db_hi0, kk * b_step);
           if constexpr (SPLIT3) {
-            const uint64_t da_lo = smem_desc_sw128(a_lo + a_off, a_lbo, a_sbo, a_lay);
-            const uint64_t db_lo = smem_desc_sw128(b_lo + b_off, b_lbo, b_sbo, b_lay);
+            const uint64_t da_lo = desc_advance(da_hi, LO_OFF), db_lo = desc_advance(db_hi, LO_OFF);
             mma_tf32(tmem_acc, da_lo, db_hi, idesc, acc);
             mma_tf32(tmem_acc, da_hi, db_lo, idesc, true);
             mma_tf32(tmem_acc, da_hi, db_hi, idesc, true);

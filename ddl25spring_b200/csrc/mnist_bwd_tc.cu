@@ -31,6 +31,7 @@ constexpr int WIN_BYTES = WIN_ROWS * 128;              // 23 552
 
 // ------------------------------------------------------------------------------------------ dgrad
 constexpr int DG_STAGES = 3;
+constexpr int DG_SUB = 4;                              // independent accumulators per tile (MMA chains are latency-bound)
 constexpr int DG_STAGE_BYTES = 2 * WIN_BYTES;          // two 32-column halves of the dy2 window
 constexpr int DG_W_BYTES = 9 * 2 * C1 * 128;           // [tap][half][ci 32][co_l 32] = 72 KB
 constexpr int DG_SMEM = DG_W_BYTES + DG_STAGES * DG_STAGE_BYTES + 256 + 1024;
@@ -71,7 +72,7 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tm_dy2, const __grid_cons
     mbar_init(w_bar, 1);
     mbar_fence_init();
   }
-  if (warp == 2) tmem_alloc<64>(tmem_slot);
+  if (warp == 2) tmem_alloc<2 * DG_SUB * C1>(tmem_slot);
   fence_before_thread_sync();
   __syncthreads();
   fence_after_thread_sync();
@@ -103,20 +104,17 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tm_dy2, const __grid_cons
         mbar_wait(&full_bar[s], phase);
         fence_after_thread_sync();
         if (elect_one()) {
-          const uint32_t win = smem_u32(s_win + s * DG_STAGE_BYTES);
-          const uint32_t wbase = smem_u32(s_w);
-          const uint32_t acc = tmem_base + buf * C1;
+          const uint64_t a_base = smem_desc_sw128(smem_u32(s_win + s * DG_STAGE_BYTES), 16, 1024);
+          const uint64_t b_base = smem_desc_sw128(smem_u32(s_w), 16, 1024);
+          const uint32_t acc = tmem_base + buf * (DG_SUB * C1);
 #pragma unroll
           for (int tap = 0; tap < 9; ++tap) {
-            const uint32_t shift = (MAX_OFF - ((tap / 3) * H1 + (tap % 3))) * 128;   // row (q - off) of the window
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) {
-              const uint32_t a_t = win + hh * WIN_BYTES + shift;
-              const uint32_t b_t = wbase + (tap * 2 + hh) * (C1 * 128);
 #pragma unroll
-              for (int kk = 0; kk < 4; ++kk)
-                mma_tf32(acc, smem_desc_sw128(a_t + kk * 32, 16, 1024), smem_desc_sw128(b_t + kk * 32, 16, 1024), idesc,
-                         (tap | hh | kk) != 0);
+              for (int kk = 0; kk < 4; ++kk)    // window row (q - off): shift = 54 - off
+                mma_tf32(acc + (((tap * 2 + hh) * 4 + kk) % DG_SUB) * C1, desc_advance(a_base, hh * WIN_BYTES + (MAX_OFF - ((tap / 3) * H1 + (tap % 3))) * 128 + kk * 32),
+                         desc_advance(b_base, (tap * 2 + hh) * (C1 * 128) + kk * 32), idesc, ((tap * 2 + hh) * 4 + kk) >= DG_SUB);
             }
           }
           mma_commit(&empty_bar[s]);
@@ -137,7 +135,14 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tm_dy2, const __grid_cons
       mbar_wait(&acc_full[buf], acc_phase);
       fence_after_thread_sync();
       float v[32];
-      tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * C1, v);
+      tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * (DG_SUB * C1), v);
+#pragma unroll
+      for (int sub = 1; sub < DG_SUB; ++sub) {
+        float u[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * (DG_SUB * C1) + sub * C1, u);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] += u[i];
+      }
       fence_before_thread_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
@@ -160,7 +165,7 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tm_dy2, const __grid_cons
   __syncthreads();
   if (warp == 2) {
     fence_after_thread_sync();
-    tmem_dealloc<64>(tmem_base);
+    tmem_dealloc<2 * DG_SUB * C1>(tmem_base);
   }
 }
 

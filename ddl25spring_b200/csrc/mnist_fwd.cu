@@ -85,6 +85,10 @@ __global__ void __launch_bounds__(256) prep_conv2_kernel(const float* __restrict
 
 // ------------------------------------------------------------------------------------------ conv2
 constexpr int kStages = 4;
+// A chain of tcgen05.mma into ONE accumulator is latency-bound at small N (measured ~90 cycles per dependent
+// MMA at N = 64 on B200 vs a 32-48 cycle issue floor), so the 36 MMAs of a tile alternate between FWD_SUB
+// independent TMEM accumulators that the epilogue adds up.
+constexpr int FWD_SUB = 2;
 constexpr int W_TILE_BYTES = C2 * 128;                 // 64 couts x 32 cins x 4 B = 8 KB per tap
 constexpr int W_BYTES = 9 * W_TILE_BYTES;              // 72 KB
 constexpr int WIN_BYTES = WIN_ROWS * 128;              // 23 552 B (multiple of 1024)
@@ -140,7 +144,7 @@ conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_co
     mbar_init(w_bar, 1);
     mbar_fence_init();
   }
-  if (warp == 2) tmem_alloc<128>(tmem_slot);
+  if (warp == 2) tmem_alloc<2 * FWD_SUB * C2>(tmem_slot);
   fence_before_thread_sync();
   __syncthreads();
   fence_after_thread_sync();
@@ -174,17 +178,15 @@ conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_co
         mbar_wait(&full_bar[s], phase);
         fence_after_thread_sync();
         if (elect_one()) {
-          const uint32_t win = smem_u32(s_win + s * WIN_BYTES);
-          const uint32_t wbase = smem_u32(s_w);
-          const uint32_t acc = tmem_base + buf * C2;
+          const uint64_t a_base = smem_desc_sw128(smem_u32(s_win + s * WIN_BYTES), 16, 1024);
+          const uint64_t b_base = smem_desc_sw128(smem_u32(s_w), 16, 1024);
+          const uint32_t acc = tmem_base + buf * (FWD_SUB * C2);
 #pragma unroll
           for (int tap = 0; tap < 9; ++tap) {
-            const uint32_t a_tap = win + ((tap / 3) * H1 + (tap % 3)) * 128;   // shifted window
-            const uint32_t b_tap = wbase + tap * W_TILE_BYTES;
 #pragma unroll
-            for (int kk = 0; kk < 4; ++kk)
-              mma_tf32(acc, smem_desc_sw128(a_tap + kk * 32, 16, 1024), smem_desc_sw128(b_tap + kk * 32, 16, 1024), idesc,
-                       (tap | kk) != 0);
+            for (int kk = 0; kk < 4; ++kk)      // tap (r, s) = the window shifted by r*26 + s rows
+              mma_tf32(acc + ((tap * 4 + kk) % FWD_SUB) * C2, desc_advance(a_base, ((tap / 3) * H1 + (tap % 3)) * 128 + kk * 32),
+                       desc_advance(b_base, tap * W_TILE_BYTES + kk * 32), idesc, (tap * 4 + kk) >= FWD_SUB);
           }
           mma_commit(&empty_bar[s]);
           mma_commit(&acc_full[buf]);
@@ -213,7 +215,14 @@ conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_co
 #pragma unroll
       for (int c0 = 0; c0 < C2; c0 += 32) {
         float v[32];
-        tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * C2 + c0, v);
+        tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * (FWD_SUB * C2) + c0, v);
+#pragma unroll
+        for (int sub = 1; sub < FWD_SUB; ++sub) {
+          float u[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * (FWD_SUB * C2) + sub * C2 + c0, u);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] += u[i];
+        }
         float4* dst = reinterpret_cast<float4*>(s_stage + m * STG_PITCH + c0);
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
@@ -268,7 +277,7 @@ conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_co
   __syncthreads();
   if (warp == 2) {
     fence_after_thread_sync();
-    tmem_dealloc<128>(tmem_base);
+    tmem_dealloc<2 * FWD_SUB * C2>(tmem_base);
   }
 }
 

@@ -95,15 +95,16 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_const
       fence_after_thread_sync();
       if (elect_one()) {
         const uint32_t a_win = smem_u32(smem + s * WG_STAGE_BYTES);
-        const uint32_t b_win = a_win + WG_A_BYTES;
+        const uint64_t a_base = smem_desc_sw128(a_win, 128, 512, LAYOUT_SW128_BASE32B);
+        const uint64_t b_base = smem_desc_sw128(a_win + WG_A_BYTES, WG_BH_BYTES, 512, LAYOUT_SW128_BASE32B);
+        // kk outer / r inner: consecutive MMAs go to the three different accumulators, so the dependent
+        // chains (latency-bound at N = 64) overlap
 #pragma unroll
-        for (int r = 0; r < 3; ++r) {
+        for (int kk = 0; kk < WG_KB / 8; ++kk) {
 #pragma unroll
-          for (int kk = 0; kk < WG_KB / 8; ++kk) {
-            const uint64_t da = smem_desc_sw128(a_win + (kk * 8 + r * H1) * 128, 128, 512, LAYOUT_SW128_BASE32B);
-            const uint64_t db = smem_desc_sw128(b_win + kk * 8 * 128, WG_BH_BYTES, 512, LAYOUT_SW128_BASE32B);
-            mma_tf32(tmem_base + r * C2, da, db, idesc, (kb | kk) != 0);
-          }
+          for (int r = 0; r < 3; ++r)
+            mma_tf32(tmem_base + r * C2, desc_advance(a_base, (kk * 8 + r * H1) * 128), desc_advance(b_base, kk * 8 * 128),
+                     idesc, (kb | kk) != 0);
         }
         mma_commit(&empty_bar[s]);
         if (kb == my_kb - 1) mma_commit(acc_bar);

@@ -133,6 +133,12 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr, uint32_t lbo
   return d;
 }
 
+// Advance a descriptor's start address by `byte_off` (a multiple of 16).  The single MMA-issuing thread is
+// latency-bound on its own instruction stream, so descriptors are built once per tile and every
+// tcgen05.mma only pays one add per operand (shared-memory addresses stay below 2^18, so the 14-bit
+// start-address field cannot overflow into its neighbours).
+__device__ __forceinline__ uint64_t desc_advance(uint64_t desc, uint32_t byte_off) { return desc + (uint64_t)(byte_off >> 4); }
+
 enum : uint32_t { FMT_F16 = 0, FMT_BF16 = 1, FMT_TF32 = 2 };
 
 // Instruction descriptor (32-bit) for kind::tf32 / kind::f16 with fp32 accumulation:

@@ -11,3 +11,6 @@ srv = PackedFedAvgServer(0.01, 100, split(ds.train, 100, True, 10), 0.08, 1, 10,
 res = srv.run(rounds)
 torch.cuda.synchronize()
 print("ms/round", [round(x, 3) for x in res.device_time_ms], "acc", res.test_accuracy[-1])
+import time
+t0 = time.perf_counter(); srv.run(1); t1 = time.perf_counter(); torch.cuda.synchronize(); t2 = time.perf_counter()
+print("host issue+test sync ms %.3f, total ms %.3f" % ((t1 - t0) * 1e3, (t2 - t0) * 1e3))
