@@ -1,0 +1,183 @@
+"""Data parallelism: bucketed gradient all-reduce overlapped with backward, and weight averaging.
+
+Reference behaviour being replaced (lab/tutorial_1b/DP):
+
+* gradient aggregation (gradient_aggr/intro_DP_GA.py:53-67): after the WHOLE backward, barrier, flatten
+  every gradient into one vector, copy it to the CPU, one gloo all-reduce, copy back, divide by W, step.
+  Nothing overlaps.
+* weight aggregation (weight_aggr/intro_DP_WA.py:52-67): local step, then all-reduce of the weights — but
+  the average is assigned to the loop variable (``param = ...``, :67) and never written back, so replicas
+  silently diverge.  :class:`WeightAveraging` implements the intended semantics.
+
+Here the gradients already live in one flat arena (no flatten/copy), the arena is cut into buckets in
+REVERSE parameter order (the order autograd produces them), and a post-accumulate-grad hook launches the
+reduction of a bucket the moment its last gradient lands, so communication runs under the rest of the
+backward.  The 1/W is folded into the fused optimizer step (``grad_scale``).  The reduction itself is
+pluggable: ``torch.distributed`` (NCCL / gloo) or the peer-memory kernel of :mod:`parallel.symm_impl`.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+from .. import ops
+from ..core.arena import FlatArena
+
+
+@dataclass
+class Bucket:
+    lo: int                      # element range [lo, hi) of the flat gradient arena
+    hi: int
+    n_params: int
+    ready: int = 0
+    work: object = None
+    names: list[str] = field(default_factory=list)
+
+
+def make_buckets(arena: FlatArena, bucket_bytes: int) -> tuple[list[Bucket], dict[str, int]]:
+    """Greedy buckets over the parameter list walked backwards; returns (buckets, param name -> bucket)."""
+    specs = [s for s in arena.specs if not s.is_buffer]
+    buckets: list[Bucket] = []
+    owner: dict[str, int] = {}
+    cur_hi = specs[-1].offset + specs[-1].numel if specs else 0
+    cur_names: list[str] = []
+    cur_lo = cur_hi
+    for s in reversed(specs):
+        cur_lo = s.offset
+        cur_names.append(s.name)
+        if (cur_hi - cur_lo) * 4 >= bucket_bytes:
+            buckets.append(Bucket(cur_lo, cur_hi, len(cur_names), names=cur_names))
+            cur_hi, cur_names = cur_lo, []
+    if cur_names:
+        buckets.append(Bucket(cur_lo, cur_hi, len(cur_names), names=cur_names))
+    for i, b in enumerate(buckets):
+        for n in b.names:
+            owner[n] = i
+    return buckets, owner
+
+
+class DataParallel:
+    """Wraps ``module`` for synchronous data-parallel training.
+
+    >>> dp = DataParallel(model, optimizer="adam", lr=8e-4)
+    >>> loss = loss_fn(dp.module(x), y); dp.backward(loss); dp.step()
+    """
+
+    def __init__(self, module: nn.Module, *, bucket_mb: float = 4.0, optimizer: str = "sgd", lr: float = 0.01,
+                 weight_decay: float = 0.0, betas=(0.9, 0.999), eps: float = 1e-8, group=None, reducer=None,
+                 overlap: bool = True):
+        self.module = module
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.arena = FlatArena.from_module(module, with_grad=True)
+        self.buckets, self._owner = make_buckets(self.arena, int(bucket_mb * 2 ** 20))
+        self.reducer = reducer                   # callable(flat_grad_view) -> handle with .wait(), or None
+        self.overlap = overlap
+        self.optimizer, self.lr, self.wd, self.betas, self.eps = optimizer, lr, weight_decay, betas, eps
+        self.step_count = 0
+        self._m = self._v = None
+        if optimizer in ("adam", "adamw"):
+            self._m, self._v = torch.zeros_like(self.arena.flat), torch.zeros_like(self.arena.flat)
+        self._launched: list[int] = []
+        if self.world > 1 and overlap:
+            for name, p in module.named_parameters():
+                if p.requires_grad:
+                    p.register_post_accumulate_grad_hook(self._make_hook(self._owner[name]))
+        self.sync_params()
+
+    # ------------------------------------------------------------------ set-up
+    def sync_params(self) -> None:
+        """Rank 0's initial weights everywhere (the labs rely on identical seeds instead)."""
+        if self.world > 1:
+            dist.broadcast(self.arena.flat, src=dist.get_global_rank(self.group, 0) if self.group else 0, group=self.group)
+
+    def _make_hook(self, bi: int):
+        def hook(_param):
+            b = self.buckets[bi]
+            b.ready += 1
+            if b.ready == b.n_params:
+                self._launch(bi)
+        return hook
+
+    def _launch(self, bi: int) -> None:
+        b = self.buckets[bi]
+        view = self.arena.grad[b.lo:b.hi]
+        if self.reducer is not None:
+            b.work = self.reducer(view, b.lo, b.hi)
+        else:
+            b.work = dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        self._launched.append(bi)
+
+    # ------------------------------------------------------------------ training step
+    def zero_grad(self) -> None:
+        self.arena.grad.zero_()
+        for b in self.buckets:
+            b.ready, b.work = 0, None
+        self._launched = []
+
+    def backward(self, loss: torch.Tensor) -> None:
+        """Backward with bucket reductions launched from the autograd hooks; returns once all buckets are
+        reduced (gradients hold the SUM over ranks; the 1/W is applied in :meth:`step`)."""
+        loss.backward()
+        self.finish()
+
+    def finish(self) -> None:
+        if self.world == 1:
+            return
+        for bi, b in enumerate(self.buckets):
+            if b.work is None:            # parameters without gradient this step, or overlap disabled
+                self._launch(bi)
+        for b in self.buckets:
+            if b.work is not None and hasattr(b.work, "wait"):
+                b.work.wait()
+
+    def step(self) -> None:
+        """Fused optimizer step over the flat arena (K15) with the DP mean folded in."""
+        self.step_count += 1
+        scale = 1.0 / self.world
+        with torch.no_grad():
+            if self.optimizer == "sgd":
+                ops.sgd_step(self.arena.flat, self.arena.grad, self.lr, self.wd, grad_scale=scale)
+            else:
+                ops.adam_step(self.arena.flat, self.arena.grad, self._m, self._v, self.step_count, self.lr, self.betas[0],
+                              self.betas[1], self.eps, self.wd, decoupled=self.optimizer == "adamw", grad_scale=scale)
+        self.zero_grad()
+
+    def train_step(self, loss_fn, *batch) -> torch.Tensor:
+        loss = loss_fn(self.module, *batch)
+        self.backward(loss)
+        self.step()
+        return loss.detach()
+
+
+class WeightAveraging:
+    """DP by weight aggregation: every rank takes its own optimizer step, then the weights are averaged
+    and WRITTEN BACK (the reference computes the average and drops it: intro_DP_WA.py:67)."""
+
+    def __init__(self, module: nn.Module, optimizer: torch.optim.Optimizer | None = None, *, lr: float = 0.01,
+                 group=None, every: int = 1):
+        self.module, self.group, self.every = module, group, every
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.arena = FlatArena.from_module(module, with_grad=True)
+        self.optimizer = optimizer
+        self.lr = lr
+        self.iters = 0
+        if self.world > 1:
+            dist.broadcast(self.arena.flat, src=0, group=group)
+
+    def step(self) -> None:
+        if self.optimizer is not None:
+            self.optimizer.step()
+            self.optimizer.zero_grad(set_to_none=False)
+        else:
+            with torch.no_grad():
+                ops.sgd_step(self.arena.flat, self.arena.grad, self.lr)
+            self.arena.grad.zero_()
+        self.iters += 1
+        if self.world > 1 and self.iters % self.every == 0:
+            with torch.no_grad():
+                dist.all_reduce(self.arena.flat, group=self.group)
+                self.arena.flat.div_(self.world)        # in place: every parameter view sees the average

@@ -1,0 +1,221 @@
+"""Pipeline (model) parallelism: schedules as data + a stage executor, and the PP x DP mesh.
+
+Covers lab/tutorial_1b/PP/1F1B:
+
+* ``sequential``  – one batch in flight (intro_PP_1F1B.py:47-98);
+* ``gpipe``       – all-forward-then-all-backward over M micro-batches, loss / M on the last stage
+                    (intro_PP_1F1B_MB.py:48-141);
+* ``one_f_one_b`` – a CORRECT 1F1B: warm-up forwards, steady 1F/1B alternation, cool-down backwards.
+                    The reference's attempt (intro_PP_1F1B_MP.py:86-206) interleaves on stage 1 only and then
+                    runs a second backward phase, so its ranks disagree on the message order and hang at
+                    iteration 0 (lab/homework-1.ipynb cell 48);
+* :class:`Mesh`   – ``pipeline_id = rank // S``, ``stage_id = rank % S`` (intro_PP_1F1B_MP.py:28-29) with the
+                    per-stage DP groups created COLLECTIVELY (every rank calls every ``new_group``; the
+                    reference does not).
+
+A schedule is a list of :class:`Op` per stage; the executor just walks it.  Deadlock-freedom is a
+property of the data: :func:`check_schedule` simulates the per-stage lists against each other and
+is run in the unit tests for every (schedule, stages, micro-batches) combination, and every
+distributed test runs under a timeout.
+
+Transport: ``torch.distributed`` p2p on the tensors' own device — NCCL device-to-device on GPUs (no
+CPU bounce as in the reference's ``.to("cpu")`` before every send), gloo on CPU.  Receives for the
+next micro-batch are posted before computing the current one, so transfer overlaps compute.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Callable, Sequence
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+F, B = "F", "B"
+
+
+@dataclass(frozen=True)
+class Op:
+    kind: str      # "F" or "B"
+    mb: int        # micro-batch index
+
+
+def gpipe(n_stages: int, stage: int, n_micro: int) -> list[Op]:
+    return [Op(F, i) for i in range(n_micro)] + [Op(B, i) for i in range(n_micro)]
+
+
+def sequential(n_stages: int, stage: int, n_micro: int = 1) -> list[Op]:
+    return gpipe(n_stages, stage, 1)
+
+
+def one_f_one_b(n_stages: int, stage: int, n_micro: int) -> list[Op]:
+    warm = min(n_stages - 1 - stage, n_micro)
+    ops = [Op(F, i) for i in range(warm)]
+    f, b = warm, 0
+    while f < n_micro:                       # steady state: one forward, one backward
+        ops.append(Op(F, f)); f += 1
+        ops.append(Op(B, b)); b += 1
+    while b < n_micro:                       # cool-down
+        ops.append(Op(B, b)); b += 1
+    return ops
+
+
+SCHEDULES: dict[str, Callable[[int, int, int], list[Op]]] = {"gpipe": gpipe, "1f1b": one_f_one_b, "sequential": sequential}
+
+
+def check_schedule(name: str, n_stages: int, n_micro: int) -> int:
+    """Simulate all stages with blocking-receive semantics; returns the number of time steps, raises
+    ``RuntimeError`` on deadlock or on a stage consuming a message that is never produced."""
+    scheds = [list(SCHEDULES[name](n_stages, s, n_micro)) for s in range(n_stages)]
+    pc = [0] * n_stages
+    done_f = [set() for _ in range(n_stages)]      # forwards finished per stage
+    done_b = [set() for _ in range(n_stages)]
+    steps = 0
+    while any(pc[s] < len(scheds[s]) for s in range(n_stages)):
+        progressed = False
+        snapshot_f = [set(x) for x in done_f]
+        snapshot_b = [set(x) for x in done_b]
+        for s in range(n_stages):
+            if pc[s] >= len(scheds[s]):
+                continue
+            op = scheds[s][pc[s]]
+            if op.kind == F:
+                ready = s == 0 or op.mb in snapshot_f[s - 1]
+            else:
+                ready = op.mb in snapshot_f[s] and (s == n_stages - 1 or op.mb in snapshot_b[s + 1])
+            if ready:
+                (done_f if op.kind == F else done_b)[s].add(op.mb)
+                pc[s] += 1
+                progressed = True
+        steps += 1
+        if not progressed:
+            raise RuntimeError(f"schedule {name!r} deadlocks with {n_stages} stages / {n_micro} micro-batches at {pc}")
+    for s in range(n_stages):
+        if done_f[s] != set(range(n_micro)) or done_b[s] != set(range(n_micro)):
+            raise RuntimeError(f"schedule {name!r}: stage {s} did not process every micro-batch")
+    return steps
+
+
+# ------------------------------------------------------------------------------------------ mesh
+class Mesh:
+    """``n_pipelines`` x ``n_stages`` process mesh with one DP group per stage."""
+
+    def __init__(self, n_stages: int, n_pipelines: int = 1, rank: int | None = None):
+        self.n_stages, self.n_pipelines = n_stages, n_pipelines
+        self.rank = dist.get_rank() if rank is None else rank
+        self.pipeline_id, self.stage_id = divmod(self.rank, n_stages)
+        self.dp_group = None
+        if n_pipelines > 1:
+            for s in range(n_stages):        # collective: EVERY rank creates EVERY group, in the same order
+                ranks = [p * n_stages + s for p in range(n_pipelines)]
+                grp = dist.new_group(ranks)
+                if s == self.stage_id:
+                    self.dp_group = grp
+
+    def rank_of(self, stage: int) -> int:
+        return self.pipeline_id * self.n_stages + stage
+
+    @property
+    def prev_rank(self):
+        return None if self.stage_id == 0 else self.rank_of(self.stage_id - 1)
+
+    @property
+    def next_rank(self):
+        return None if self.stage_id == self.n_stages - 1 else self.rank_of(self.stage_id + 1)
+
+
+# ------------------------------------------------------------------------------------------ executor
+class PipelineStage:
+    """Runs one stage of a pipeline according to a schedule.
+
+    ``module``: this stage's layers.  Stage 0 gets the micro-batch input from ``inputs``; the last
+    stage computes ``loss_fn(output, target) / n_micro`` and starts the backward.  Activations /
+    gradients of shape ``act_shape`` travel between neighbouring stages.
+    """
+
+    def __init__(self, module: nn.Module, mesh: Mesh, act_shape: Sequence[int], *, schedule: str = "1f1b",
+                 n_micro: int = 1, loss_fn=None, act_dtype=torch.float32, device=None):
+        self.module, self.mesh, self.n_micro = module, mesh, n_micro
+        self.schedule = SCHEDULES[schedule](mesh.n_stages, mesh.stage_id, n_micro)
+        self.loss_fn = loss_fn
+        self.act_shape, self.act_dtype = tuple(act_shape), act_dtype
+        self.device = torch.device(device) if device is not None else next(module.parameters()).device
+        self.is_first, self.is_last = mesh.stage_id == 0, mesh.stage_id == mesh.n_stages - 1
+        self.losses: list[float] = []
+
+    def _buf(self):
+        return torch.empty(self.act_shape, dtype=self.act_dtype, device=self.device)
+
+    def run(self, inputs: Sequence[torch.Tensor] | None = None, targets: Sequence[torch.Tensor] | None = None) -> list[float]:
+        """One training iteration (all micro-batches, forward and backward).  Gradients accumulate in
+        ``module.parameters()``; the caller zeroes them and steps its optimizer."""
+        m = self.mesh
+        saved_in: dict[int, torch.Tensor] = {}
+        saved_out: dict[int, torch.Tensor] = {}
+        pending_send: list = []
+        recv_f: dict[int, tuple] = {}
+        recv_b: dict[int, tuple] = {}
+        self.losses = []
+
+        def post_recv(op: Op):
+            if op.kind == F and not self.is_first and op.mb not in recv_f:
+                t = self._buf()
+                recv_f[op.mb] = (t, dist.irecv(t, src=m.prev_rank))
+            if op.kind == B and not self.is_last and op.mb not in recv_b:
+                t = self._buf()
+                recv_b[op.mb] = (t, dist.irecv(t, src=m.next_rank))
+
+        ops = self.schedule
+        if ops:
+            post_recv(ops[0])
+        for i, op in enumerate(ops):
+            if i + 1 < len(ops):
+                post_recv(ops[i + 1])                 # prefetch the next message while this op computes
+            if op.kind == F:
+                if self.is_first:
+                    x = inputs[op.mb].to(self.device)
+                else:
+                    t, req = recv_f.pop(op.mb)
+                    req.wait()
+                    x = t.requires_grad_()
+                out = self.module(x)
+                saved_in[op.mb] = x
+                if self.is_last:
+                    loss = self.loss_fn(out, targets[op.mb].to(self.device)) / self.n_micro
+                    saved_out[op.mb] = loss
+                    self.losses.append(float(loss.detach()) * self.n_micro)
+                else:
+                    saved_out[op.mb] = out
+                    payload = out.detach().contiguous()
+                    pending_send.append((dist.isend(payload, dst=m.next_rank), payload))
+            else:
+                out = saved_out.pop(op.mb)
+                if self.is_last:
+                    out.backward()
+                else:
+                    t, req = recv_b.pop(op.mb)
+                    req.wait()
+                    out.backward(t)
+                x = saved_in.pop(op.mb)
+                if not self.is_first:
+                    payload = x.grad.contiguous()
+                    pending_send.append((dist.isend(payload, dst=m.prev_rank), payload))
+        for r, _keepalive in pending_send:
+            r.wait()
+        return self.losses
+
+    def allreduce_grads(self) -> None:
+        """Average gradients over the stage's DP group (PP x DP; intro_PP_1F1B_MP.py:232-235) — one flat
+        all-reduce over the stage's gradient arena instead of one call per parameter."""
+        if self.mesh.dp_group is None:
+            return
+        grads = [p.grad for p in self.module.parameters() if p.grad is not None]
+        if not grads:
+            return
+        flat = torch.cat([g.reshape(-1) for g in grads])
+        dist.all_reduce(flat, group=self.mesh.dp_group)
+        flat.div_(self.mesh.n_pipelines)
+        off = 0
+        for g in grads:
+            g.copy_(flat[off:off + g.numel()].view_as(g))
+            off += g.numel()
