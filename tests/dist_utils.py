@@ -16,7 +16,7 @@ def free_port() -> int:
         return s.getsockname()[1]
 
 
-def _entry(rank, world, port, fn, args, q):
+def _entry(rank, world, port, fn, args, q, release):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     try:
         torch.set_num_threads(1)
@@ -30,6 +30,7 @@ def _entry(rank, world, port, fn, args, q):
             dist.destroy_process_group()
         except Exception:
             pass
+        release.wait(60)      # tensors in the queue are shared through this process: stay alive until they are read
 
 
 def run_distributed(fn, world: int, args=(), timeout: float = 120.0):
@@ -37,7 +38,8 @@ def run_distributed(fn, world: int, args=(), timeout: float = 120.0):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = free_port()
-    procs = [ctx.Process(target=_entry, args=(r, world, port, fn, args, q)) for r in range(world)]
+    release = ctx.Event()
+    procs = [ctx.Process(target=_entry, args=(r, world, port, fn, args, q, release)) for r in range(world)]
     for p in procs:
         p.start()
     results = {}
@@ -48,6 +50,7 @@ def run_distributed(fn, world: int, args=(), timeout: float = 120.0):
                 raise RuntimeError(f"rank {rank} failed:\n{payload}")
             results[rank] = payload
     finally:
+        release.set()
         for p in procs:
             p.join(timeout=10)
             if p.is_alive():
