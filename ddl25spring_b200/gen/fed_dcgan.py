@@ -1,0 +1,125 @@
+"""Federated DCGAN (BASELINE.json config 5, north star): FedAvg of generator AND discriminator.
+
+Every client holds 64x64 images, runs ``local_steps`` of the standard DCGAN update (D on real + fake,
+then G; BCE-with-logits), and sends both networks' flat arenas — parameters AND BatchNorm running
+statistics (``include_buffers=True``) — which the server averages with the sample-count weights through
+the same K1 aggregation kernel as every other FedAvg in this framework.  With ``torch.distributed``
+initialised the clients are dealt to the ranks and the partial sums are all-reduced.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+from .. import ops
+from ..core.arena import FlatArena
+from ..core.seeds import clients_per_round
+from ..models.dcgan import Discriminator, Generator
+
+
+class DCGANPair:
+    def __init__(self, device, nz=100, ngf=64, ndf=64):
+        self.G, self.D = Generator(nz, ngf).to(device), Discriminator(ndf).to(device)
+        self.ga = FlatArena.from_module(self.G, include_buffers=True, with_grad=True)
+        self.da = FlatArena.from_module(self.D, include_buffers=True, with_grad=True)
+        self.nz, self.device = nz, device
+
+    def n_param_elems(self):
+        return (sum(s.numel for s in self.ga.specs if not s.is_buffer), sum(s.numel for s in self.da.specs if not s.is_buffer))
+
+
+def dcgan_local_steps(pair: DCGANPair, images: torch.Tensor, steps: int, batch: int, lr: float, gen: torch.Generator,
+                      m_g, v_g, m_d, v_d, step0: int, beta1: float = 0.5):
+    """``steps`` DCGAN iterations with fused Adam over the flat arenas; returns (d_loss, g_loss) of the last step."""
+    G, D, dev = pair.G, pair.D, pair.device
+    G.train(); D.train()
+    n = len(images)
+    d_loss = g_loss = torch.zeros((), device=dev)
+    pg, pd = pair.n_param_elems()
+    for s in range(steps):
+        idx = torch.randint(0, n, (batch,), generator=gen)
+        real = images[idx].to(dev)
+        z = torch.randn(batch, pair.nz, generator=gen).to(dev)
+        # --- D step
+        pair.da.grad.zero_()
+        fake = G(z)
+        d_loss = F.binary_cross_entropy_with_logits(D(real), torch.ones(batch, device=dev)) + \
+            F.binary_cross_entropy_with_logits(D(fake.detach()), torch.zeros(batch, device=dev))
+        d_loss.backward()
+        ops.adam_step(pair.da.flat[:_pad4(pd)], pair.da.grad[:_pad4(pd)], m_d, v_d, step0 + s + 1, lr, beta1, 0.999)
+        # --- G step
+        pair.ga.grad.zero_()
+        g_loss = F.binary_cross_entropy_with_logits(D(fake), torch.ones(batch, device=dev))
+        g_loss.backward()
+        ops.adam_step(pair.ga.flat[:_pad4(pg)], pair.ga.grad[:_pad4(pg)], m_g, v_g, step0 + s + 1, lr, beta1, 0.999)
+    return float(d_loss.detach()), float(g_loss.detach())
+
+
+def _pad4(n: int) -> int:
+    return (n + 3) // 4 * 4
+
+
+class FederatedDCGAN:
+    def __init__(self, client_images: list[torch.Tensor], client_fraction: float = 1.0, local_steps: int = 2, batch_size: int = 16,
+                 lr: float = 2e-4, seed: int = 0, device=None, ngf: int = 64, ndf: int = 64):
+        self.device = torch.device(device) if device is not None else torch.device("cuda" if torch.cuda.is_available() else "cpu")
+        self.clients = client_images
+        self.counts = [len(c) for c in client_images]
+        self.k = clients_per_round(len(client_images), client_fraction)
+        self.local_steps, self.batch, self.lr, self.seed = local_steps, batch_size, lr, seed
+        self.rng = np.random.default_rng(seed)
+        torch.manual_seed(seed)
+        self.glob = DCGANPair(self.device, ngf=ngf, ndf=ndf)
+        self.work = DCGANPair(self.device, ngf=ngf, ndf=ndf)
+        self.rank, self.world = (dist.get_rank(), dist.get_world_size()) if dist.is_initialized() else (0, 1)
+        pg, pd = self.glob.n_param_elems()
+        z = lambda n: torch.zeros(_pad4(n), device=self.device)
+        self._adam = {}                      # per-client Adam moments persist across rounds
+        self._zeros = z
+        self.history: list[tuple[float, float]] = []
+
+    def _moments(self, c):
+        if c not in self._adam:
+            pg, pd = self.glob.n_param_elems()
+            self._adam[c] = [self._zeros(pg), self._zeros(pg), self._zeros(pd), self._zeros(pd), 0]
+        return self._adam[c]
+
+    def run(self, nr_rounds: int):
+        for r in range(nr_rounds):
+            chosen = self.rng.choice(len(self.clients), self.k, replace=False)
+            w = np.asarray([self.counts[int(c)] for c in chosen], dtype=np.float64)
+            w = w / w.sum()
+            mine = [(p, int(c)) for p, c in enumerate(chosen) if p % self.world == self.rank]
+            UG = torch.zeros(max(1, len(mine)), self.glob.ga.size, device=self.device)
+            UD = torch.zeros(max(1, len(mine)), self.glob.da.size, device=self.device)
+            losses = []
+            for i, (pos, c) in enumerate(mine):
+                with torch.no_grad():
+                    self.work.ga.flat.copy_(self.glob.ga.flat)
+                    self.work.da.flat.copy_(self.glob.da.flat)
+                mom = self._moments(c)
+                gen = torch.Generator().manual_seed(self.seed + c + 1 + r * self.k)
+                losses.append(dcgan_local_steps(self.work, self.clients[c], self.local_steps, self.batch, self.lr, gen,
+                                                mom[0], mom[1], mom[2], mom[3], mom[4]))
+                mom[4] += self.local_steps
+                UG[i].copy_(self.work.ga.flat.detach())
+                UD[i].copy_(self.work.da.flat.detach())
+            lw = [float(w[pos]) for pos, _ in mine] or [0.0]
+            with torch.no_grad():
+                aggG = ops.weighted_sum(UG, lw)
+                aggD = ops.weighted_sum(UD, lw)
+                if self.world > 1:
+                    dist.all_reduce(aggG); dist.all_reduce(aggD)
+                self.glob.ga.flat.copy_(aggG)
+                self.glob.da.flat.copy_(aggD)
+            if losses:
+                self.history.append(tuple(np.mean(losses, axis=0)))
+        return self.history
+
+    @torch.no_grad()
+    def sample(self, n: int, seed: int = 0) -> torch.Tensor:
+        self.glob.G.eval()
+        z = torch.randn(n, self.glob.nz, generator=torch.Generator().manual_seed(seed)).to(self.device)
+        return self.glob.G(z)
