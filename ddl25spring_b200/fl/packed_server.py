@@ -111,7 +111,8 @@ class PackedFedAvgServer:
     def _engine(self, G: int) -> PackedMnistEngine:
         if G not in self._engines:
             self._engines[G] = PackedMnistEngine(G, self.batch_size, device=self.device, p_drop1=self.p1, p_drop2=self.p2)
-            self._bufs[G] = (torch.empty(G, P, device=self.device),
+            w_rows = self.collective.row_buffer(G) if self.collective is not None else torch.empty(G, P, device=self.device)
+            self._bufs[G] = (w_rows,
                              torch.zeros(G, self.n_max, 784, device=self.device),
                              torch.zeros(G, self.n_max, dtype=torch.int64, device=self.device),
                              torch.zeros(G, self.nr_local_epochs * self.n_max, dtype=torch.int32).pin_memory()

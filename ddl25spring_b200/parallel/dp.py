@@ -42,7 +42,7 @@ def make_buckets(arena: FlatArena, bucket_bytes: int) -> tuple[list[Bucket], dic
     specs = [s for s in arena.specs if not s.is_buffer]
     buckets: list[Bucket] = []
     owner: dict[str, int] = {}
-    cur_hi = specs[-1].offset + specs[-1].numel if specs else 0
+    cur_hi = arena.size if specs else 0          # include the arena's zero padding: bucket ends stay float4-aligned
     cur_names: list[str] = []
     cur_lo = cur_hi
     for s in reversed(specs):
@@ -74,7 +74,12 @@ class DataParallel:
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.arena = FlatArena.from_module(module, with_grad=True)
         self.buckets, self._owner = make_buckets(self.arena, int(bucket_mb * 2 ** 20))
-        self.reducer = reducer                   # callable(flat_grad_view) -> handle with .wait(), or None
+        self.reducer = reducer                   # callable(flat_grad_view, lo, hi) -> handle with .wait(), or None
+        if reducer is not None and hasattr(reducer, "grad"):
+            # the fused peer-memory reducer works in place on a symmetric buffer: make it the gradient arena
+            self.arena.grad = reducer.grad[:self.arena.size]
+            self.arena.grad.zero_()
+            self.arena.bind_grads()
         self.overlap = overlap
         self.optimizer, self.lr, self.wd, self.betas, self.eps = optimizer, lr, weight_decay, betas, eps
         self.step_count = 0

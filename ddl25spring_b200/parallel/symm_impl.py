@@ -1,0 +1,205 @@
+"""Symmetric peer memory over NVLink (one process per GPU) and the fused collectives built on it.
+
+:class:`SymmetricArena` allocates same-sized device buffers on every rank (``cudaMalloc`` in
+``csrc/symm.cu``), exchanges CUDA-IPC handles through ``torch.distributed`` once, and exposes
+
+* ``local(name)``      – this rank's buffer as a torch tensor (zero-copy, ``__cuda_array_interface__``);
+* ``peer_ptrs(name)``  – device pointers of the same buffer on every rank (index = rank);
+* a signal pad + error flag for the in-kernel cross-GPU barriers.
+
+:class:`SymmetricAggregator` is the multi-GPU server-aggregate hook of :class:`fl.packed_server.
+PackedFedAvgServer`: each rank's clients' weight rows live in a symmetric buffer, and ONE kernel per
+GPU (``ddl_symm_reduce``) pulls this GPU's coordinate shard of every row on every GPU, reduces it
+(weighted mean / median / trimmed mean) and stores the result into every rank's replica.
+:class:`SymmetricGradReducer` plugs the same kernel into :class:`parallel.dp.DataParallel` as the
+bucketed gradient all-reduce (in place over the symmetric gradient arena, on a side stream).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib
+
+
+class _DevBuf:
+    """Raw device allocation viewed as a torch tensor through the CUDA array interface."""
+
+    def __init__(self, ptr: int, nbytes: int, device_index: int):
+        self.ptr, self.nbytes = ptr, nbytes
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3, "strides": None}
+        self.tensor = torch.as_tensor(self, device=torch.device("cuda", device_index))
+
+
+class SymmetricArena:
+    def __init__(self, group=None):
+        assert dist.is_initialized() and torch.cuda.is_available()
+        self.group = group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.dev = torch.cuda.current_device()
+        self.L = _lib.lib()
+        self._bufs: dict[str, _DevBuf] = {}
+        self._peers: dict[str, list[int]] = {}
+        self.epoch = 0
+        self.done_counter = C.c_int64(0)
+        pads = self.alloc("__pads__", 4 * 2 * 16 + 64, torch.int32)       # int[2*world] (+ slack)
+        self.pad_ptrs = self.peer_ptrs("__pads__")
+        self.local_flags = torch.zeros(2, dtype=torch.int32, device="cuda")
+        self.err = torch.zeros(1, dtype=torch.int32, device="cuda")
+        del pads
+        self.barrier()
+
+    # ------------------------------------------------------------------ allocation + exchange
+    def alloc(self, name: str, nbytes: int, dtype=torch.float32) -> torch.Tensor:
+        """Collective: every rank must call with the same ``name`` / size, in the same order."""
+        nbytes = (int(nbytes) + 255) // 256 * 256
+        ptr = C.c_void_p()
+        _lib.check(self.L.ddl_symm_alloc(C.byref(ptr), C.c_int64(nbytes)), "ddl_symm_alloc")
+        buf = _DevBuf(ptr.value, nbytes, self.dev)
+        handle = (C.c_ubyte * 64)()
+        _lib.check(self.L.ddl_ipc_export(C.c_void_p(ptr.value), handle), "ddl_ipc_export")
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle), group=self.group)
+        peers = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                peers.append(ptr.value)
+                continue
+            out = C.c_void_p()
+            _lib.check(self.L.ddl_ipc_import((C.c_ubyte * 64).from_buffer_copy(h), C.byref(out)), "ddl_ipc_import")
+            peers.append(out.value)
+        self._bufs[name], self._peers[name] = buf, peers
+        return buf.tensor.view(dtype)
+
+    def local(self, name: str, dtype=torch.float32) -> torch.Tensor:
+        return self._bufs[name].tensor.view(dtype)
+
+    def peer_ptrs(self, name: str) -> list[int]:
+        return self._peers[name]
+
+    # ------------------------------------------------------------------ barriers / errors
+    def next_epoch(self) -> int:
+        self.epoch += 1
+        return self.epoch
+
+    def barrier(self) -> None:
+        """Cross-GPU barrier executed BY the GPUs (in stream order), not by the hosts."""
+        _lib.check(self.L.ddl_symm_barrier(_lib.host_ptrs(self.pad_ptrs), self.rank, self.world, self.next_epoch(),
+                                           _lib.p(self.err), _lib.stream()), "ddl_symm_barrier")
+
+    def check(self) -> None:
+        e = int(self.err.item())
+        if e:
+            raise RuntimeError(f"peer-memory collective timed out on rank {self.rank} (code {e}): a rank did not launch its kernel")
+
+    def reduce(self, mode: int, row_ptrs, weights, out_ptrs, d0: int, d1: int, *, base=None, alpha=0.0, beta=1.0,
+               rank_lo=0, rank_hi=1, max_ctas: int = 0) -> None:
+        K = len(row_ptrs)
+        _lib.check(self.L.ddl_symm_reduce(int(mode), _lib.host_ptrs(row_ptrs), _lib.host_floats(weights), K, _lib.p(base),
+                                          _lib.f32(alpha), _lib.f32(beta), int(rank_lo), int(rank_hi), _lib.host_ptrs(out_ptrs),
+                                          len(out_ptrs), _lib.i64(d0), _lib.i64(d1), _lib.host_ptrs(self.pad_ptrs), self.rank,
+                                          self.world, self.next_epoch(), _lib.p(self.local_flags), C.byref(self.done_counter),
+                                          _lib.p(self.err), int(max_ctas), _lib.stream()), "ddl_symm_reduce")
+
+
+def shard_bounds(n: int, world: int, rank: int, align: int = 4) -> tuple[int, int]:
+    """Contiguous, ``align``-aligned coordinate shard of rank ``rank``."""
+    per = -(-n // world)
+    per = (per + align - 1) // align * align
+    lo = min(n, rank * per)
+    return lo, min(n, lo + per)
+
+
+class SymmetricAggregator:
+    """Fused cross-GPU aggregation for the packed FedAvg server (weighted mean, median, trimmed mean; Krum
+    gathers the rows it needs with peer copies and scores locally)."""
+
+    def __init__(self, arena: SymmetricArena | None = None, max_rows_per_rank: int = 16, row_elems: int = 1_200_000):
+        self.arena = arena or SymmetricArena()
+        self.G, self.P = max_rows_per_rank, row_elems
+        self.rows = self.arena.alloc("client_rows", self.G * self.P * 4).view(self.G, self.P)
+        self.result = self.arena.alloc("agg_result", self.P * 4)
+        self.row_ptrs = self.arena.peer_ptrs("client_rows")
+        self.res_ptrs = self.arena.peer_ptrs("agg_result")
+
+    def row_buffer(self, G: int) -> torch.Tensor:
+        """Symmetric storage for this rank's ``G`` client weight rows (the engine trains in place in it)."""
+        assert G <= self.G
+        return self.rows[:G]
+
+    def aggregate(self, aggregator, W_local: torch.Tensor, mine_pos, weights: torch.Tensor, gflat: torch.Tensor) -> None:
+        from ..fl.aggregators import CoordinateMedian, Krum, TrimmedMean, WeightedMean
+
+        a = self.arena
+        world, K = a.world, len(weights)
+        if W_local.numel() and W_local.data_ptr() != self.rows.data_ptr():
+            self.rows[:W_local.shape[0]].copy_(W_local)
+        # row k of the round lives on rank k % world at local index k // world (round-robin deal)
+        ptrs = [self.row_ptrs[k % world] + (k // world) * self.P * 4 for k in range(K)]
+        d0, d1 = shard_bounds(self.P, world, a.rank)
+        w = [float(x) for x in weights.tolist()]
+        if isinstance(aggregator, WeightedMean):
+            a.reduce(0, ptrs, w, self.res_ptrs, d0, d1)
+        elif isinstance(aggregator, (CoordinateMedian, TrimmedMean)) and K <= 64:
+            if isinstance(aggregator, CoordinateMedian):
+                lo, hi = ((K - 1) // 2, (K - 1) // 2 + 1) if (K % 2 or aggregator.lower) else (K // 2 - 1, K // 2 + 1)
+            else:
+                t = aggregator.trim_count(K)
+                lo, hi = t, K - t
+            a.reduce(1, ptrs, w, self.res_ptrs, d0, d1, rank_lo=lo, rank_hi=hi)
+        else:
+            # Krum / large K: assemble the full update matrix with peer loads (weights 1 on one row = copy),
+            # then run the single-GPU rule; every rank computes the same result.
+            U = getattr(self, "_U", None)
+            if U is None or U.shape[0] != K:
+                U = self._U = torch.empty(K, self.P, device="cuda")
+            a.barrier()
+            for k in range(K):
+                src = _DevView(ptrs[k], self.P)
+                U[k].copy_(src.tensor)
+            a.barrier()
+            agg = aggregator(U, weights, global_flat=gflat.detach())
+            gflat.copy_(agg)
+            return
+        gflat.copy_(self.result)
+
+
+class _DevView:
+    def __init__(self, ptr: int, n_floats: int):
+        self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (ptr, False), "version": 3, "strides": None}
+        self.tensor = torch.as_tensor(self, device="cuda")
+
+
+class SymmetricGradReducer:
+    """``reducer`` for :class:`parallel.dp.DataParallel`: in-place sum of a gradient bucket over all ranks by
+    the fused peer-memory kernel, launched on a side stream so it overlaps the rest of backward."""
+
+    def __init__(self, arena: SymmetricArena, n_elems: int, max_ctas: int = 32):
+        self.arena = arena
+        self.grad = arena.alloc("dp_grad", n_elems * 4)
+        self.ptrs = arena.peer_ptrs("dp_grad")
+        self.stream = torch.cuda.Stream()
+        self.max_ctas = max_ctas
+
+    class _Work:
+        def __init__(self, ev):
+            self.ev = ev
+
+        def wait(self):
+            torch.cuda.current_stream().wait_event(self.ev)
+
+    def __call__(self, view: torch.Tensor, lo: int, hi: int):
+        a = self.arena
+        ready = torch.cuda.Event()
+        ready.record()
+        n = hi - lo
+        s0, s1 = shard_bounds(n, a.world, a.rank)
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(ready)
+            a.reduce(0, self.ptrs, [1.0] * a.world, self.ptrs, lo + s0, lo + s1, max_ctas=self.max_ctas)
+            done = torch.cuda.Event()
+            done.record()
+        return self._Work(done)

@@ -23,6 +23,7 @@ extern "C" {
 
 #define DDL_MAX_ROWS 128 /* update rows per aggregation launch */
 #define DDL_MAX_OUTS 80  /* broadcast destinations per aggregation launch */
+#define DDL_MAX_WORLD 16 /* ranks (GPUs) in a symmetric-memory group */
 
 /* ---- library -------------------------------------------------------------------------- */
 const char* ddl_last_error(void);
@@ -161,6 +162,26 @@ int ddl_mnist_small_update(float* W, const float* wg_part, int n_cta, const floa
 #define DDL_GRAM_STATIC_SCRATCH_FLOATS (1 << 20)
 int ddl_gram_static_scratch(const float* updates, int64_t ld, int K, int64_t D, float* gram, int64_t ldg,
                             int n_split, int precise, void* stream);
+
+/* ---- Symmetric peer memory + fused cross-GPU reduce (K1 / K2 / K4 / K5 over NVLink) ------------
+ * (ref: gloo all_reduce of flattened grads/weights, lab/tutorial_1b/DP/gradient_aggr/intro_DP_GA.py:53-67,
+ *  weight_aggr/intro_DP_WA.py:54-67; client-message reduction lab/tutorial_1a/hfl_complete.py:370-383).
+ * ddl_symm_alloc/ipc_*: cudaMalloc'd buffers shared between the ranks of one node with CUDA IPC.
+ * ddl_symm_reduce: ONE kernel per GPU = entry barrier + reduce of coordinates [d0, d1) over all rows
+ * (local or peer pointers; HOST arrays of device pointers) + store to every outs[] replica + exit barrier.
+ *  mode 0: out = alpha*base + beta*sum_k weights[k]*rows[k]; mode 1: mean of sorted ranks [rank_lo, rank_hi).
+ * pads[p]: int[2*world] signal pad on GPU p; epoch must increase by 1 per collective on every rank;
+ * local_flags: int[2] device-local (zeroed once); *done_counter_host: host counter owned by the caller;
+ * *err (device int, zeroed once) becomes non-zero if a peer did not arrive within 5 s. */
+int ddl_symm_alloc(void** ptr, int64_t bytes);
+int ddl_symm_free(void* ptr);
+int ddl_ipc_export(void* ptr, unsigned char* handle64);
+int ddl_ipc_import(const unsigned char* handle64, void** ptr);
+int ddl_ipc_close(void* ptr);
+int ddl_symm_barrier(int* const* pads, int rank, int world, int epoch, int* err, void* stream);
+int ddl_symm_reduce(int mode, const float* const* rows, const float* weights, int K, const float* base, float alpha, float beta,
+                    int rank_lo, int rank_hi, float* const* outs, int n_out, int64_t d0, int64_t d1, int* const* pads, int rank,
+                    int world, int epoch, int* local_flags, int64_t* done_counter_host, int* err, int max_ctas, void* stream);
 
 #ifdef __cplusplus
 }

@@ -16,11 +16,15 @@ def free_port() -> int:
         return s.getsockname()[1]
 
 
-def _entry(rank, world, port, fn, args, q, release):
+def _entry(rank, world, port, fn, args, q, release, backend="gloo"):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     try:
         torch.set_num_threads(1)
-        dist.init_process_group("gloo", rank=rank, world_size=world)
+        if backend == "nccl":
+            torch.cuda.set_device(rank)
+            dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+        else:
+            dist.init_process_group("gloo", rank=rank, world_size=world)
         out = fn(rank, world, *args)
         q.put((rank, "ok", out))
     except Exception:
@@ -33,13 +37,13 @@ def _entry(rank, world, port, fn, args, q, release):
         release.wait(60)      # tensors in the queue are shared through this process: stay alive until they are read
 
 
-def run_distributed(fn, world: int, args=(), timeout: float = 120.0):
+def run_distributed(fn, world: int, args=(), timeout: float = 120.0, backend: str = "gloo"):
     """Run ``fn(rank, world, *args)`` on ``world`` gloo ranks; returns the list of per-rank results."""
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = free_port()
     release = ctx.Event()
-    procs = [ctx.Process(target=_entry, args=(r, world, port, fn, args, q, release)) for r in range(world)]
+    procs = [ctx.Process(target=_entry, args=(r, world, port, fn, args, q, release, backend)) for r in range(world)]
     for p in procs:
         p.start()
     results = {}

@@ -1,0 +1,125 @@
+"""Fused peer-memory collectives over NVLink: needs >= 2 GPUs (gpurun --gpus 2)."""
+import pytest
+import torch
+
+from tests.dist_utils import run_distributed
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+
+
+def _reduce_worker(rank, world):
+    import torch.distributed as dist
+    from ddl25spring_b200.parallel.symm_impl import SymmetricArena, shard_bounds
+    a = SymmetricArena()
+    n, G = 1_200_000, 3
+    rows = a.alloc("rows", G * n * 4).view(G, n)
+    res = a.alloc("res", n * 4)
+    g = torch.Generator(device="cuda").manual_seed(100 + rank)
+    rows.copy_(torch.randn(G, n, generator=g, device="cuda"))
+    allrows = [torch.empty(G, n, device="cuda") for _ in range(world)]
+    dist.all_gather(allrows, rows.contiguous())
+    U = torch.stack([allrows[k % world][k // world] for k in range(G * world)])
+    K = G * world
+    ptrs = [a.peer_ptrs("rows")[k % world] + (k // world) * n * 4 for k in range(K)]
+    w = [(k + 1) / sum(range(1, K + 1)) for k in range(K)]
+    d0, d1 = shard_bounds(n, world, rank)
+    out = {}
+    for rep in range(3):                      # repeated use: epochs / counters must keep working
+        a.reduce(0, ptrs, w, a.peer_ptrs("res"), d0, d1)
+    torch.cuda.synchronize(); a.check()
+    exp = (U.double() * torch.tensor(w, device="cuda", dtype=torch.float64)[:, None]).sum(0).float()
+    out["wsum_err"] = float((res - exp).abs().max())
+    a.reduce(1, ptrs, w, a.peer_ptrs("res"), d0, d1, rank_lo=(K - 1) // 2 if K % 2 else K // 2 - 1, rank_hi=(K - 1) // 2 + 1 if K % 2 else K // 2 + 1)
+    torch.cuda.synchronize(); a.check()
+    s = U.sort(0).values
+    med = s[(K - 1) // 2] if K % 2 else 0.5 * (s[K // 2 - 1] + s[K // 2])
+    out["median_err"] = float((res - med).abs().max())
+    # timing: device time of the fused all-reduce-like op, max over ranks
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.barrier(); torch.cuda.synchronize()
+    e0.record()
+    for _ in range(10):
+        a.reduce(0, ptrs, w, a.peer_ptrs("res"), d0, d1)
+    e1.record(); torch.cuda.synchronize(); a.check()
+    t = torch.tensor([e0.elapsed_time(e1) / 10], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    out["fused_ms"] = float(t)
+    # NCCL baseline for the same math: local weighted partial sum + all_reduce
+    part = torch.empty(n, device="cuda")
+    wl = torch.tensor([w[k] for k in range(K) if k % world == rank], device="cuda")
+    torch.cuda.synchronize(); e0.record()
+    for _ in range(10):
+        torch.mv(rows.t(), wl, out=part)
+        dist.all_reduce(part)
+    e1.record(); torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / 10], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    out["nccl_ms"] = float(t)
+    return out
+
+
+@pytest.mark.timeout(300)
+def test_symm_reduce_matches_oracle():
+    world = min(torch.cuda.device_count(), 8)
+    outs = run_distributed(_reduce_worker, world, timeout=240, backend="nccl")
+    for o in outs:
+        assert o["wsum_err"] < 1e-5 and o["median_err"] < 1e-6, o
+    print("fused vs nccl ms:", outs[0]["fused_ms"], outs[0]["nccl_ms"])
+
+
+def _dp_worker(rank, world):
+    import torch.nn.functional as F
+    from ddl25spring_b200.parallel.dp import DataParallel
+    from ddl25spring_b200.parallel.symm_impl import SymmetricArena, SymmetricGradReducer
+    torch.manual_seed(0)
+    m = torch.nn.Sequential(torch.nn.Linear(64, 512), torch.nn.ReLU(), torch.nn.Linear(512, 512), torch.nn.ReLU(),
+                            torch.nn.Linear(512, 10)).cuda()
+    import copy
+    m2 = copy.deepcopy(m)
+    arena = SymmetricArena()
+    n = sum(p.numel() for p in m.parameters()) + 1024
+    dp = DataParallel(m, bucket_mb=0.25, optimizer="sgd", lr=0.05, reducer=SymmetricGradReducer(arena, n))
+    ref = DataParallel(m2, bucket_mb=0.25, optimizer="sgd", lr=0.05)          # NCCL all_reduce path
+    g = torch.Generator().manual_seed(rank)
+    x, y = torch.randn(32, 64, generator=g).cuda(), torch.randint(0, 10, (32,), generator=g).cuda()
+    for _ in range(3):
+        dp.train_step(lambda mod, a, b: F.cross_entropy(mod(a), b), x, y)
+        ref.train_step(lambda mod, a, b: F.cross_entropy(mod(a), b), x, y)
+    torch.cuda.synchronize(); arena.check()
+    return float((dp.arena.flat - ref.arena.flat).abs().max()), len(dp.buckets)
+
+
+@pytest.mark.timeout(300)
+def test_dp_with_fused_reducer_matches_nccl():
+    world = min(torch.cuda.device_count(), 8)
+    outs = run_distributed(_dp_worker, world, timeout=240, backend="nccl")
+    for err, nb in outs:
+        assert err < 1e-5 and nb > 1, (err, nb)
+
+
+def _fedavg_worker(rank, world, agg_name):
+    from ddl25spring_b200.core.data import SyntheticMNIST, split
+    from ddl25spring_b200.fl.aggregators import make_aggregator
+    from ddl25spring_b200.fl.packed_server import PackedFedAvgServer
+    from ddl25spring_b200.parallel.symm import make_collective
+    ds = SyntheticMNIST(n_train=2400, n_test=400, seed=2, noise=0.8)
+    subsets = split(ds.train, 12, True, 3)
+    kw = dict(n_byzantine=1) if agg_name == "krum" else {}
+    outs = {}
+    for name, coll in (("fused", make_collective()), ("nccl", None)):
+        srv = PackedFedAvgServer(0.05, 50, subsets, 0.5, 1, 3, test_set=ds.test, device="cuda", p_drop1=0.0, p_drop2=0.0,
+                                 aggregator=make_aggregator(agg_name, **kw), collective=coll)
+        res = srv.run(2)
+        torch.cuda.synchronize()
+        outs[name] = (srv.arena.flat.clone().cpu(), res.test_accuracy)
+    return outs
+
+
+@pytest.mark.timeout(400)
+@pytest.mark.parametrize("agg_name", ["mean", "median", "krum"])
+def test_packed_fedavg_fused_equals_nccl_path(agg_name):
+    world = min(torch.cuda.device_count(), 8)
+    outs = run_distributed(_fedavg_worker, world, (agg_name,), timeout=300, backend="nccl")
+    for o in outs:
+        torch.testing.assert_close(o["fused"][0], o["nccl"][0], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(outs[0]["fused"][0], outs[-1]["fused"][0], rtol=0, atol=0)
