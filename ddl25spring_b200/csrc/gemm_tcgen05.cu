@@ -52,6 +52,18 @@ __device__ __forceinline__ float apply_act(float v, int act, float slope) {
   return v;
 }
 
+// K7: the A operand is the CONCATENATION along K of up to 8 matrices that live in different buffers —
+// the party embeddings of vertical FL, each in its owner GPU's (peer-mapped) memory.  The K loop walks
+// the parts; every k-block is TMA-loaded straight from the owning GPU, so the all-gather of embeddings
+// (torch.cat at lab/tutorial_2b/vfl.py:36) happens inside the top model's first GEMM.
+constexpr int kMaxParts = 8;
+struct GatherMaps {
+  CUtensorMap maps[kMaxParts];   // A part p: [M, dims[p]] fp32, K-major
+  int kb_start[kMaxParts + 1];   // first k-block of part p (prefix sums of ceil(dims[p] / 32))
+  int col_off[kMaxParts];        // column of W where part p's slab starts
+  int n_parts;
+};
+
 template <int BN, int EB /*element bytes*/, bool SPLIT3>
 struct SmemPlan {
   static constexpr int A_BYTES = BM * ROW_BYTES;
@@ -64,10 +76,10 @@ struct SmemPlan {
   static constexpr int TOTAL = STAGES * STAGE_BYTES + BAR_BYTES + 1024 /*alignment slack*/;
 };
 
-template <int BN, int EB, bool A_MN, bool B_MN, bool SPLIT3>
-__global__ void __launch_bounds__(kThreads, 1)
-gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-                    const Epilogue epi, const int M, const int N, const int K, const int kblocks_per_split) {
+template <int BN, int EB, bool A_MN, bool B_MN, bool SPLIT3, bool GATHER>
+__device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, const CUtensorMap& tma_b, const GatherMaps* gm,
+                                                  const Epilogue& epi, const int M, const int N, const int K,
+                                                  const int kblocks_per_split) {
   using Plan = SmemPlan<BN, EB, SPLIT3>;
   constexpr int STAGES = Plan::STAGES;
   constexpr int BK = ROW_BYTES / EB;         // elements per k-block (32 tf32 / 64 bf16)
@@ -92,14 +104,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
   const int n_split = epi.n_split > 1 ? epi.n_split : 1;
   const int g = blockIdx.z / n_split;
   const int split = blockIdx.z % n_split;
-  const int total_kblocks = (K + BK - 1) / BK;
+  const int total_kblocks = GATHER ? gm->kb_start[gm->n_parts] : (K + BK - 1) / BK;
   const int kb_begin = split * kblocks_per_split;
   int kb_end = kb_begin + kblocks_per_split;
   if (kb_end > total_kblocks) kb_end = total_kblocks;
   const int num_kb = kb_end > kb_begin ? kb_end - kb_begin : 0;
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tma_a);
+    if constexpr (!GATHER) tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
   }
   if (warp == 1 && lane == 0) {
@@ -127,6 +139,27 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
         uint8_t* a_dst = stage_base + s * Plan::STAGE_BYTES;
         uint8_t* b_dst = a_dst + Plan::A_BYTES;
         mbar_arrive_expect_tx(&full_bar[s], Plan::A_BYTES + Plan::B_BYTES);
+        if constexpr (GATHER) {
+          const int gkb = kb_begin + kb;
+          int p = 0;
+          while (p + 1 < gm->n_parts && gkb >= gm->kb_start[p + 1]) ++p;
+          const int kl = (gkb - gm->kb_start[p]) * BK;           // columns past dims[p] are zero-filled by TMA
+          // constant indices only: a dynamically indexed descriptor address would make the compiler stage the
+          // parameter block through local memory, where the TMA unit cannot read it
+          switch (p) {
+            case 0: tma_load_3d(a_dst, &gm->maps[0], &full_bar[s], kl, m0, 0); break;
+            case 1: tma_load_3d(a_dst, &gm->maps[1], &full_bar[s], kl, m0, 0); break;
+            case 2: tma_load_3d(a_dst, &gm->maps[2], &full_bar[s], kl, m0, 0); break;
+            case 3: tma_load_3d(a_dst, &gm->maps[3], &full_bar[s], kl, m0, 0); break;
+            case 4: tma_load_3d(a_dst, &gm->maps[4], &full_bar[s], kl, m0, 0); break;
+            case 5: tma_load_3d(a_dst, &gm->maps[5], &full_bar[s], kl, m0, 0); break;
+            case 6: tma_load_3d(a_dst, &gm->maps[6], &full_bar[s], kl, m0, 0); break;
+            default: tma_load_3d(a_dst, &gm->maps[7], &full_bar[s], kl, m0, 0); break;
+          }
+          tma_load_3d(b_dst, &tma_b, &full_bar[s], gm->col_off[p] + kl, n0, g);
+          if (++s == STAGES) { s = 0; phase ^= 1; }
+          continue;
+        }
         const int k0 = (kb_begin + kb) * BK;
         if constexpr (A_MN) tma_load_4d(a_dst, &tma_a, &full_bar[s], 0, k0, m0 / BK, g);
         else tma_load_3d(a_dst, &tma_a, &full_bar[s], k0, m0, g);
@@ -268,6 +301,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
   }
 }
 
+template <int BN, int EB, bool A_MN, bool B_MN, bool SPLIT3>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                    const Epilogue epi, const int M, const int N, const int K, const int kblocks_per_split) {
+  gemm_tcgen05_body<BN, EB, A_MN, B_MN, SPLIT3, false>(tma_a, tma_b, nullptr, epi, M, N, K, kblocks_per_split);
+}
+
+template <int BN, bool SPLIT3>
+__global__ void __launch_bounds__(kThreads, 1)
+gather_gemm_tcgen05_kernel(const __grid_constant__ GatherMaps gm, const __grid_constant__ CUtensorMap tma_b,
+                           const Epilogue epi, const int M, const int N, const int kblocks_per_split) {
+  gemm_tcgen05_body<BN, 4, false, false, SPLIT3, true>(tma_b, tma_b, &gm, epi, M, N, 0, kblocks_per_split);
+}
+
 // Sum split-K partial tiles in split order, add bias, apply activation.
 __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ part, int n_split,
                                                             int64_t group_elems /*M*N*/, int G, int N, float* __restrict__ C,
@@ -397,6 +444,69 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
     splitk_reduce_kernel<<<(int)blocks, 256, 0, st>>>(scratch, n_split, ge, G, N, C, ldc, c_group_stride, bias,
                                                       bias_group_stride, act, slope);
+    DDL_LAUNCH_CHECK();
+  }
+  return DDL_OK;
+}
+
+// K7 host side: A = cat_p(parts[p]) along K, parts may be peer-mapped device pointers.
+int ddl_gather_gemm_tcgen05(const float* const* parts, const int* part_dims, const int64_t* part_lds, int n_parts,
+                            const float* W, int64_t ldw, float* C, int64_t ldc, const float* bias, int act, float slope,
+                            int M, int N, int precise, int n_split, float* scratch, void* stream) {
+  DDL_REQUIRE(n_parts >= 1 && n_parts <= kMaxParts, "n_parts=%d outside [1, %d]", n_parts, kMaxParts);
+  DDL_REQUIRE(M > 0 && N > 0, "empty GEMM");
+  GatherMaps gm;
+  gm.n_parts = n_parts;
+  int kb = 0, col = 0;
+  for (int p = 0; p < n_parts; ++p) {
+    DDL_REQUIRE(part_dims[p] > 0 && (part_lds[p] * 4) % 16 == 0 && (reinterpret_cast<uintptr_t>(parts[p]) & 15) == 0,
+                "part %d: need dim > 0, 16-byte aligned pointer and row stride", p);
+    OperandDesc od{parts[p], M, part_lds[p], 0, 0};
+    // TMA needs the innermost extent to be a multiple of 16 bytes (a 14-float extent hangs the copy on B200):
+    // describe round_up(dim, 4) columns; the caller keeps the up-to-3 padding columns of each part at zero.
+    const int kdesc = (part_dims[p] + 3) / 4 * 4;
+    DDL_REQUIRE(part_lds[p] >= kdesc, "part %d: row stride %lld < padded width %d", p, (long long)part_lds[p], kdesc);
+    if (int e = make_operand_map(&gm.maps[p], od, kdesc, 1, BM, 4)) return e;
+    gm.kb_start[p] = kb;
+    gm.col_off[p] = col;
+    kb += (part_dims[p] + 31) / 32;
+    col += kdesc;                 // slabs of W start on 16-byte boundaries (TMA box origins must be 16-byte aligned)
+  }
+  for (int p = n_parts; p <= kMaxParts; ++p) gm.kb_start[p] = kb;
+  const int Ktot = col;
+  DDL_REQUIRE((ldw * 4) % 16 == 0 && (reinterpret_cast<uintptr_t>(W) & 15) == 0, "W must be 16-byte aligned with a 16-byte row stride");
+  if (n_split < 1) n_split = 1;
+  if (n_split > kb) n_split = kb;
+  DDL_REQUIRE(n_split == 1 || scratch != nullptr, "split-K needs scratch");
+  const int kbps = (kb + n_split - 1) / n_split;
+  n_split = (kb + kbps - 1) / kbps;
+  const int BN = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
+  CUtensorMap tb;
+  OperandDesc ob{W, N, ldw, 0, 0};
+  if (int e = make_operand_map(&tb, ob, Ktot, 1, BN, 4)) return e;
+  Epilogue epi;
+  epi.C = n_split > 1 ? scratch : C;
+  epi.ldc = ldc; epi.c_group_stride = 0; epi.bias = bias; epi.bias_group_stride = 0;
+  epi.act = act; epi.slope = slope; epi.alpha = 1.f; epi.beta = 0.f; epi.n_split = n_split;
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, n_split);
+#define DDL_GATHER_CASE(BN_, P_)                                                                              \
+  {                                                                                                            \
+    auto kern = gather_gemm_tcgen05_kernel<BN_, P_>;                                                           \
+    using Plan = SmemPlan<BN_, 4, P_>;                                                                         \
+    DDL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Plan::TOTAL));      \
+    kern<<<grid, kThreads, Plan::TOTAL, st>>>(gm, tb, epi, M, N, kbps);                                        \
+  }
+  if (BN == 32) { if (precise) DDL_GATHER_CASE(32, true) else DDL_GATHER_CASE(32, false) }
+  else if (BN == 64) { if (precise) DDL_GATHER_CASE(64, true) else DDL_GATHER_CASE(64, false) }
+  else { if (precise) DDL_GATHER_CASE(128, true) else DDL_GATHER_CASE(128, false) }
+#undef DDL_GATHER_CASE
+  DDL_LAUNCH_CHECK();
+  if (n_split > 1) {
+    const int64_t ge = (int64_t)M * N;
+    int64_t blocks = (ge + 255) / 256;
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    splitk_reduce_kernel<<<(int)blocks, 256, 0, st>>>(scratch, n_split, ge, 1, N, C, ldc, 0, bias, 0, act, slope);
     DDL_LAUNCH_CHECK();
   }
   return DDL_OK;

@@ -154,6 +154,31 @@ __global__ void __launch_bounds__(256) symm_reduce_kernel(RowTable tab, OutTable
     }
     for (int o = 0; o < a.n_out; ++o) reinterpret_cast<float4*>(ot.outs[o])[v] = r;
   }
+  if constexpr (MODE == 2) {
+    // all-to-all half of the coordinate-sharded exchange: local[k][j] = rows[k][4*v0 + j], j < 4*(v1 - v0).
+    // The caller then runs the Gram GEMM (K3) on the local [K, shard] matrix: every GPU pulls only ITS slice
+    // of every client's update over NVLink instead of whole updates.
+    const int64_t ld4 = a.v1 - a.v0;            // float4 per local row (a.rank_lo carries extra row padding)
+    float4* dst = reinterpret_cast<float4*>(ot.outs[0]);
+    for (int64_t v = a.v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < a.v1; v += stride) {
+      for (int k = 0; k < a.K; k += 4) {
+        float4 x[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (k + u < a.K) x[u] = ld_peer(reinterpret_cast<const float4*>(tab.rows[k + u]) + v);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (k + u < a.K) {
+            float4 y = x[u];
+            if (a.base != nullptr) {              // optional: subtract the global model -> update deltas
+              const float4 b = reinterpret_cast<const float4*>(a.base)[v];
+              y.x -= b.x; y.y -= b.y; y.z -= b.z; y.w -= b.w;
+            }
+            dst[(int64_t)(k + u) * (ld4 + a.rank_lo) + (v - a.v0)] = y;
+          }
+      }
+    }
+  }
   if constexpr (MODE == 1) {
     // one coordinate per thread (KP values in registers), 128 B coalesced peer loads per warp per row
     for (int64_t d = 4 * a.v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; d < 4 * a.v1; d += stride) {
@@ -238,12 +263,14 @@ int ddl_symm_barrier(int* const* pads, int rank, int world, int epoch, int* err,
   return DDL_OK;
 }
 
-// mode 0: out = alpha*base + beta*sum_k w_k rows_k ; mode 1: mean of sorted ranks [rank_lo, rank_hi) (K <= 64)
+// mode 0: out = alpha*base + beta*sum_k w_k rows_k ; mode 1: mean of sorted ranks [rank_lo, rank_hi) (K <= 64);
+// mode 2: outs[0][k][j] = rows[k][d0 + j] - (base ? base[d0 + j] : 0), local row pitch (d1 - d0) + 4*rank_lo floats
 int ddl_symm_reduce(int mode, const float* const* rows, const float* weights, int K, const float* base, float alpha, float beta,
                     int rank_lo, int rank_hi, float* const* outs, int n_out, int64_t d0, int64_t d1, int* const* pads, int rank,
                     int world, int epoch, int* local_flags, int64_t* done_counter_host, int* err, int max_ctas, void* stream) {
   DDL_REQUIRE(d0 % 4 == 0 && d1 % 4 == 0 && d1 >= d0, "coordinate range must be float4 aligned");
-  DDL_REQUIRE(mode == 0 || (K <= 64 && rank_lo >= 0 && rank_lo < rank_hi && rank_hi <= K), "bad rank window / K for rank-select mode");
+  DDL_REQUIRE(mode != 1 || (K <= 64 && rank_lo >= 0 && rank_lo < rank_hi && rank_hi <= K), "bad rank window / K for rank-select mode");
+  DDL_REQUIRE(mode >= 0 && mode <= 2, "mode must be 0 (weighted sum), 1 (rank-select mean) or 2 (gather shard)");
   RowTable tab;
   OutTable ot;
   PeerPads pp;
@@ -259,6 +286,7 @@ int ddl_symm_reduce(int mode, const float* const* rows, const float* weights, in
   a.done_target = (unsigned int)(*done_counter_host);
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == 0) symm_reduce_kernel<0, 1><<<(int)g, 256, 0, st>>>(tab, ot, pp, a);
+  else if (mode == 2) symm_reduce_kernel<2, 1><<<(int)g, 256, 0, st>>>(tab, ot, pp, a);
   else if (K <= 8) symm_reduce_kernel<1, 8><<<(int)g, 256, 0, st>>>(tab, ot, pp, a);
   else if (K <= 16) symm_reduce_kernel<1, 16><<<(int)g, 256, 0, st>>>(tab, ot, pp, a);
   else if (K <= 32) symm_reduce_kernel<1, 32><<<(int)g, 256, 0, st>>>(tab, ot, pp, a);

@@ -109,3 +109,32 @@ def gram_tcgen05(updates: torch.Tensor, out: torch.Tensor | None = None, n_split
     if n_split is None:
         n_split = default_gram_splits(K, D)
     return gemm(updates, updates, n_split=n_split, precise=precise, out=out)
+
+
+def gather_linear_ptrs(part_ptrs, part_dims, part_lds, M: int, w: torch.Tensor, bias: torch.Tensor | None = None,
+                       act: str | None = None, precise: bool = True, slope: float = 0.01, out: torch.Tensor | None = None):
+    """K7: ``act(cat_p(parts[p]) @ w.T + bias)`` where ``parts[p]`` are raw device pointers (local or peer-mapped)
+    to ``[M, dims[p]]`` fp32 matrices with row strides ``part_lds[p]``."""
+    import ctypes as C
+    n = len(part_ptrs)
+    N = w.shape[0]
+    assert w.is_cuda and w.dtype == torch.float32 and w.shape[1] == sum(part_dims)
+    # re-pack W so that every party's slab starts on a 16-byte boundary (TMA box origins must be aligned)
+    pads = [(d + 3) // 4 * 4 for d in part_dims]
+    if pads == list(part_dims) and w.stride(1) == 1 and (w.stride(0) * 4) % 16 == 0:
+        wp = w
+    else:
+        wp = torch.zeros(N, sum(pads), device=w.device, dtype=torch.float32)
+        so = do = 0
+        for d, pd in zip(part_dims, pads):
+            wp[:, do:do + d] = w[:, so:so + d]
+            so, do = so + d, do + pd
+    w = wp
+    if out is None:
+        out = torch.empty(M, N, device=w.device, dtype=torch.float32)
+    rc = _lib.lib().ddl_gather_gemm_tcgen05(_lib.host_ptrs(part_ptrs), (C.c_int * n)(*[int(d) for d in part_dims]),
+                                            (C.c_int64 * n)(*[int(x) for x in part_lds]), n, _lib.p(w), _lib.i64(w.stride(0)),
+                                            _lib.p(out), _lib.i64(out.stride(0)), _lib.p(bias), ACT[act], _lib.f32(slope), int(M),
+                                            int(N), int(precise), 1, _lib.p(None), _lib.stream())
+    _lib.check(rc, "ddl_gather_gemm_tcgen05")
+    return out

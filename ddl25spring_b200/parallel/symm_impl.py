@@ -55,7 +55,8 @@ class SymmetricArena:
     # ------------------------------------------------------------------ allocation + exchange
     def alloc(self, name: str, nbytes: int, dtype=torch.float32) -> torch.Tensor:
         """Collective: every rank must call with the same ``name`` / size, in the same order."""
-        nbytes = (int(nbytes) + 255) // 256 * 256
+        want = int(nbytes)
+        nbytes = (want + 255) // 256 * 256
         ptr = C.c_void_p()
         _lib.check(self.L.ddl_symm_alloc(C.byref(ptr), C.c_int64(nbytes)), "ddl_symm_alloc")
         buf = _DevBuf(ptr.value, nbytes, self.dev)
@@ -72,10 +73,12 @@ class SymmetricArena:
             _lib.check(self.L.ddl_ipc_import((C.c_ubyte * 64).from_buffer_copy(h), C.byref(out)), "ddl_ipc_import")
             peers.append(out.value)
         self._bufs[name], self._peers[name] = buf, peers
-        return buf.tensor.view(dtype)
+        self._sizes = getattr(self, "_sizes", {})
+        self._sizes[name] = want
+        return buf.tensor[:want].view(dtype)
 
     def local(self, name: str, dtype=torch.float32) -> torch.Tensor:
-        return self._bufs[name].tensor.view(dtype)
+        return self._bufs[name].tensor[:self._sizes[name]].view(dtype)
 
     def peer_ptrs(self, name: str) -> list[int]:
         return self._peers[name]
@@ -151,19 +154,33 @@ class SymmetricAggregator:
                 lo, hi = t, K - t
             a.reduce(1, ptrs, w, self.res_ptrs, d0, d1, rank_lo=lo, rank_hi=hi)
         else:
-            # Krum / large K: assemble the full update matrix with peer loads (weights 1 on one row = copy),
-            # then run the single-GPU rule; every rank computes the same result.
+            # Krum: coordinate-sharded.  One fused kernel pulls THIS GPU's slice of every client's update delta
+            # over NVLink into a local [K, shard] matrix; the tcgen05 Gram GEMM (K3) runs on that slice; the
+            # K x K partial Grams are summed with one more fused reduce; scores / selection are computed
+            # redundantly (identically) on every rank and the selected rows are averaged by the K1 kernel.
+            assert isinstance(aggregator, Krum) and K <= 128
+            from ..ops.gemm import gram_tcgen05
+            from .. import ops
+            shard = d1 - d0
+            pad = (-shard) % 32                                   # keep local rows 128-byte aligned for TMA
             U = getattr(self, "_U", None)
-            if U is None or U.shape[0] != K:
-                U = self._U = torch.empty(K, self.P, device="cuda")
-            a.barrier()
-            for k in range(K):
-                src = _DevView(ptrs[k], self.P)
-                U[k].copy_(src.tensor)
-            a.barrier()
-            agg = aggregator(U, weights, global_flat=gflat.detach())
-            gflat.copy_(agg)
-            return
+            if U is None or U.shape != (K, shard + pad):
+                U = self._U = torch.zeros(K, shard + pad, device="cuda")
+                self._gpart = a.alloc(f"gram_part_{K}", K * K * 4).view(K, K)
+                self._gsum = a.alloc(f"gram_sum_{K}", K * K * 4).view(K, K)
+                self._gpart_ptrs, self._gsum_ptrs = a.peer_ptrs(f"gram_part_{K}"), a.peer_ptrs(f"gram_sum_{K}")
+            a.reduce(2, ptrs, w, [U.data_ptr()], d0, d1, base=gflat.detach(), rank_lo=pad // 4)
+            gram_tcgen05(U, out=self._gpart, precise=aggregator.precise)
+            if (K * K) % 4 == 0:
+                a.reduce(0, self._gpart_ptrs, [1.0] * world, self._gsum_ptrs, 0, K * K)
+                G = self._gsum
+            else:                                                 # odd K: K*K is not float4-divisible
+                dist.all_reduce(self._gpart)
+                G = self._gpart
+            sel, selw, scores = ops.krum_select(U, aggregator.f, aggregator.multi, gram_matrix=G)
+            aggregator.last_selected, aggregator.last_scores = sel, scores
+            # selection weights live on the device; every rank reduces its shard of the selected rows
+            a.reduce(0, ptrs, selw.tolist(), self.res_ptrs, d0, d1)
         gflat.copy_(self.result)
 
 
@@ -203,3 +220,64 @@ class SymmetricGradReducer:
             done = torch.cuda.Event()
             done.record()
         return self._Work(done)
+
+
+class FusedVFLGather:
+    """``gather_linear`` hook for :class:`parallel.vfl.DistributedVFL` (K7).
+
+    Forward: every party writes its embedding into a (double-buffered) symmetric buffer, a GPU-side barrier
+    orders the writes, and ONE tcgen05 GEMM per rank computes ``cat(E_0..E_{W-1}) @ fc1.weight.T + bias`` with
+    its k-blocks TMA-loaded directly from the owning GPUs — the concatenated embedding matrix never exists.
+    Backward: the embedding gradient needs only this party's weight slab (local GEMM = the scatter of
+    lab/tutorial_2b/vfl.py:81); the weight gradient is slab-sparse per rank and is summed with one fused
+    peer-memory reduce so every replica of the top model takes the same step.
+    """
+
+    def __init__(self, arena: SymmetricArena, max_batch: int, dims, n_out: int):
+        self.arena, self.dims = arena, [int(d) for d in dims]
+        self.ld = (max(self.dims) + 3) // 4 * 4
+        self.max_batch = max_batch
+        self.bufs = [arena.alloc(f"vfl_emb_{i}", max_batch * self.ld * 4).view(max_batch, self.ld) for i in range(2)]
+        self.ptrs = [arena.peer_ptrs(f"vfl_emb_{i}") for i in range(2)]
+        ktot = sum(self.dims)
+        self.nw = (n_out * ktot + 127) // 128 * 128
+        self.dw_part = arena.alloc("vfl_dw_part", self.nw * 4)
+        self.dw_sum = arena.alloc("vfl_dw_sum", self.nw * 4)
+        self.dw_part_ptrs, self.dw_sum_ptrs = arena.peer_ptrs("vfl_dw_part"), arena.peer_ptrs("vfl_dw_sum")
+        self.step = 0
+
+    def __call__(self, emb, dims, rank, weight, bias):
+        return _FusedGatherLinear.apply(emb, weight, bias, self, rank)
+
+
+class _FusedGatherLinear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, emb, weight, bias, h: FusedVFLGather, rank: int):
+        from ..ops.gemm import gather_linear_ptrs
+        B, d = emb.shape
+        slot = h.step % 2
+        h.step += 1
+        h.bufs[slot][:B, :d].copy_(emb.detach())
+        h.arena.barrier()                                   # all parties' embeddings are in place
+        out = gather_linear_ptrs(h.ptrs[slot], h.dims, [h.ld] * len(h.dims), B, weight.detach(), bias.detach(), precise=True)
+        ctx.save_for_backward(emb.detach(), weight.detach())
+        ctx.h, ctx.rank = h, rank
+        return out
+
+    @staticmethod
+    def backward(ctx, gout):
+        emb, weight = ctx.saved_tensors
+        h, rank = ctx.h, ctx.rank
+        a = h.arena
+        off = sum(h.dims[:rank])
+        d = h.dims[rank]
+        gout = gout.contiguous()
+        demb = gout @ weight[:, off:off + d]                # scatter: only this party's slab is needed
+        n_out, ktot = weight.shape
+        part = h.dw_part[:n_out * ktot].view(n_out, ktot)
+        part.zero_()
+        part[:, off:off + d] = gout.t() @ emb
+        d0, d1 = shard_bounds(h.nw, a.world, a.rank)
+        a.reduce(0, h.dw_part_ptrs, [1.0] * a.world, h.dw_sum_ptrs, d0, d1)
+        dw = h.dw_sum[:n_out * ktot].view(n_out, ktot).clone()
+        return demb, dw, gout.sum(0), None, None

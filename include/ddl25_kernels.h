@@ -183,6 +183,17 @@ int ddl_symm_reduce(int mode, const float* const* rows, const float* weights, in
                     int rank_lo, int rank_hi, float* const* outs, int n_out, int64_t d0, int64_t d1, int* const* pads, int rank,
                     int world, int epoch, int* local_flags, int64_t* done_counter_host, int* err, int max_ctas, void* stream);
 
+/* ---- K7: vertical-FL embedding gather fused into the top model's first GEMM --------------------
+ * (ref: torch.cat(party_outs, 1) + fc1, lab/tutorial_2b/vfl.py:36-37; exercise_3.py:128,85).
+ * C[M,N] = act(cat_p(parts[p])[M, sum dims] * W^T + bias); W is [N, sum_p round_up(dims[p], 4)]: the slab of part p
+ * starts at column sum_{q<p} round_up(dims[q], 4) (TMA box origins must be 16-byte aligned), padding columns are ignored; parts[p] are device pointers that may be
+ * peer-mapped (each party's embedding stays in its owner GPU's HBM; k-blocks are TMA-loaded over NVLink).
+ * parts / part_dims / part_lds are HOST arrays (n_parts <= 8); part_lds[p] >= round_up(part_dims[p], 4) and the
+ * padding columns [dims, round_up(dims, 4)) of every part must be zero. */
+int ddl_gather_gemm_tcgen05(const float* const* parts, const int* part_dims, const int64_t* part_lds, int n_parts,
+                            const float* W, int64_t ldw, float* C, int64_t ldc, const float* bias, int act, float slope,
+                            int M, int N, int precise, int n_split, float* scratch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

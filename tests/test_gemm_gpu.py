@@ -65,3 +65,18 @@ def test_gram(cuda_lib, K, D):
     gotp = G.gram_tcgen05(u, precise=True)
     assert _rel_err(gotp, exp) < 5e-5
     assert torch.equal(G.gram_tcgen05(u), got), "Gram must be deterministic"
+
+
+@pytest.mark.parametrize("dims", [[14, 16, 14, 16], [64, 32], [16, 8, 12], [7, 4, 6, 13, 40]])
+def test_gather_gemm_local_parts(cuda_lib, dims):
+    """K7 with all parts in local memory: act(cat(parts) @ W.T + b)."""
+    M, N = 200, 128
+    ld = (max(dims) + 3) // 4 * 4
+    parts = [torch.randn(M, ld, device=DEV) for _ in dims]
+    for p_, d_ in zip(parts, dims):
+        p_[:, d_:] = 0          # contract: padding columns of a part are zero
+    W, b = torch.randn(N, sum(dims), device=DEV), torch.randn(N, device=DEV)
+    got = G.gather_linear_ptrs([p.data_ptr() for p in parts], dims, [ld] * len(dims), M, W, b, act="leaky_relu")
+    cat = torch.cat([p[:, :d] for p, d in zip(parts, dims)], 1).double()
+    exp = torch.nn.functional.leaky_relu(cat @ W.double().T + b.double(), 0.01)
+    assert _rel_err(got, exp) < 1e-5

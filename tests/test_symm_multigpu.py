@@ -123,3 +123,41 @@ def test_packed_fedavg_fused_equals_nccl_path(agg_name):
     for o in outs:
         torch.testing.assert_close(o["fused"][0], o["nccl"][0], rtol=1e-4, atol=1e-5)
     torch.testing.assert_close(outs[0]["fused"][0], outs[-1]["fused"][0], rtol=0, atol=0)
+
+
+def _vfl_worker(rank, world):
+    from ddl25spring_b200.core.data import SyntheticHeart
+    from ddl25spring_b200.parallel import vfl
+    from ddl25spring_b200.parallel.symm_impl import FusedVFLGather, SymmetricArena
+    tab = SyntheticHeart().encoded()
+    parts = vfl.balanced_partition(tab.columns, world)
+    idx = tab.column_index(parts[rank])
+    x_local, y = tab.x[:256, idx].cuda(), tab.y[:256].cuda()
+    dims = [2 * len(p) for p in parts]
+    arena = SymmetricArena()
+    out = {}
+    for name in ("fused", "allgather"):
+        hook = FusedVFLGather(arena, 256, dims, 128) if name == "fused" else None
+        net = vfl.DistributedVFL(len(idx), dims, act_on_logits=False, seed=3, gather_linear=hook).cuda()
+        net.bottom.dropout.p = 0.0
+        opt = torch.optim.SGD(net.parameters(), lr=0.1)
+        losses = []
+        for _ in range(4):
+            opt.zero_grad()
+            loss = torch.nn.functional.cross_entropy(net(x_local), y)
+            loss.backward()
+            opt.step()
+            losses.append(float(loss))
+        torch.cuda.synchronize(); arena.check()
+        out[name] = (losses, net.top_model.fc1.weight.detach().cpu().clone(), net.bottom.fc1.weight.detach().cpu().clone())
+    return out
+
+
+@pytest.mark.timeout(300)
+def test_vfl_fused_gather_gemm_equals_allgather_path():
+    world = min(torch.cuda.device_count(), 8)
+    outs = run_distributed(_vfl_worker, world, timeout=240, backend="nccl")
+    for o in outs:
+        assert o["fused"][0] == pytest.approx(o["allgather"][0], rel=2e-4)
+        torch.testing.assert_close(o["fused"][1], o["allgather"][1], rtol=1e-3, atol=1e-5)
+        torch.testing.assert_close(o["fused"][2], o["allgather"][2], rtol=1e-3, atol=1e-5)
