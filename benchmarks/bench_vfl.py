@@ -1,0 +1,68 @@
+"""Vertical FL, one party per GPU (BASELINE.json config 3): embedding gather fused into the top model's first GEMM.
+
+  torchrun --nproc-per-node N benchmarks/bench_vfl.py [--batch 4096 --emb 64]
+
+Lab shapes (B = 64, 60 features) are microseconds; the bench states the scaled shapes it uses.
+fused = FusedVFLGather (barrier kernel + ONE tcgen05 GEMM pulling k-blocks from the owner GPUs with TMA);
+nccl  = all_gather + cat + F.linear."""
+import argparse, json, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batch", type=int, default=4096)
+    ap.add_argument("--emb", type=int, default=64)
+    ap.add_argument("--out", type=int, default=128)
+    ap.add_argument("--iters", type=int, default=50)
+    a = ap.parse_args()
+    from ddl25spring_b200.ops.gemm import gather_linear_ptrs
+    from ddl25spring_b200.parallel.symm_impl import SymmetricArena
+    from ddl25spring_b200.utils.timing import max_over_ranks
+    world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0"))
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+    dist.init_process_group("nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
+    arena = SymmetricArena()
+    dims = [a.emb] * world
+    emb = arena.alloc("emb", a.batch * a.emb * 4).view(a.batch, a.emb)
+    emb.copy_(torch.randn(a.batch, a.emb, device="cuda"))
+    torch.manual_seed(0)
+    W = torch.randn(a.out, a.emb * world, device="cuda")
+    b = torch.randn(a.out, device="cuda")
+    ptrs = arena.peer_ptrs("emb")
+    out = torch.empty(a.batch, a.out, device="cuda")
+    parts = [torch.empty(a.batch, a.emb, device="cuda") for _ in range(world)]
+
+    def fused():
+        arena.barrier()
+        gather_linear_ptrs(ptrs, dims, [a.emb] * world, a.batch, W, b, precise=True, out=out)
+
+    def nccl():
+        dist.all_gather(parts, emb)
+        return torch.nn.functional.linear(torch.cat(parts, 1), W, b)
+
+    def t(fn):
+        for _ in range(5):
+            fn()
+        torch.cuda.synchronize(); dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(a.iters):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        return max_over_ranks(e0.elapsed_time(e1) / a.iters * 1e3, "cuda")
+
+    r = {"world": world, "batch": a.batch, "emb_per_party": a.emb, "top_fc1_out": a.out, "us": {"fused": round(t(fused), 2), "nccl_allgather_cat_linear": round(t(nccl), 2)}}
+    ref = nccl()
+    fused()
+    r["max_abs_err_vs_fp32"] = float((out - ref).abs().max())
+    arena.check()
+    if rank == 0:
+        print(json.dumps(r))
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

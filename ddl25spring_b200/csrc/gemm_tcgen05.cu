@@ -44,6 +44,7 @@ struct Epilogue {
   float alpha;
   float beta;           // direct (n_split == 1) path only: C = act(alpha*acc + beta*C_old + bias)
   int n_split;          // > 1: write raw partial tiles to C = scratch[split][g][M][N] (ldc = N)
+  int same_ab;          // A and B are the same matrix (Gram / SYRK): stage each tile once, use it as both operands
 };
 
 __device__ __forceinline__ float apply_act(float v, int act, float slope) {
@@ -138,7 +139,7 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
         mbar_wait(&empty_bar[s], phase ^ 1);
         uint8_t* a_dst = stage_base + s * Plan::STAGE_BYTES;
         uint8_t* b_dst = a_dst + Plan::A_BYTES;
-        mbar_arrive_expect_tx(&full_bar[s], Plan::A_BYTES + Plan::B_BYTES);
+        mbar_arrive_expect_tx(&full_bar[s], epi.same_ab ? Plan::A_BYTES : Plan::A_BYTES + Plan::B_BYTES);
         if constexpr (GATHER) {
           const int gkb = kb_begin + kb;
           int p = 0;
@@ -163,8 +164,10 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
         const int k0 = (kb_begin + kb) * BK;
         if constexpr (A_MN) tma_load_4d(a_dst, &tma_a, &full_bar[s], 0, k0, m0 / BK, g);
         else tma_load_3d(a_dst, &tma_a, &full_bar[s], k0, m0, g);
-        if constexpr (B_MN) tma_load_4d(b_dst, &tma_b, &full_bar[s], 0, k0, n0 / BK, g);
-        else tma_load_3d(b_dst, &tma_b, &full_bar[s], k0, n0, g);
+        if (!epi.same_ab) {
+          if constexpr (B_MN) tma_load_4d(b_dst, &tma_b, &full_bar[s], 0, k0, n0 / BK, g);
+          else tma_load_3d(b_dst, &tma_b, &full_bar[s], k0, n0, g);
+        }
         if (++s == STAGES) { s = 0; phase ^= 1; }
       }
     }
@@ -187,7 +190,7 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
         constexpr uint32_t a_step = A_MN ? UMMA_K * ROW_BYTES : 32, b_step = B_MN ? UMMA_K * ROW_BYTES : 32;
         const uint32_t a_hi = smem_u32(stage_base + s * Plan::STAGE_BYTES);
         const uint64_t da_hi0 = smem_desc_sw128(a_hi, a_lbo, a_sbo, a_lay);
-        const uint64_t db_hi0 = smem_desc_sw128(a_hi + Plan::A_BYTES, b_lbo, b_sbo, b_lay);
+        const uint64_t db_hi0 = smem_desc_sw128(epi.same_ab ? a_hi : a_hi + Plan::A_BYTES, b_lbo, b_sbo, b_lay);
         constexpr uint32_t LO_OFF = Plan::A_BYTES + Plan::B_BYTES;       // lo tiles follow the hi tiles
 #pragma unroll
         for (int kk = 0; kk < KSTEPS; ++kk) {
@@ -426,6 +429,9 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
   epi.ldc = ldc; epi.c_group_stride = c_group_stride;
   epi.bias = bias; epi.bias_group_stride = bias_group_stride;
   epi.act = act; epi.slope = slope; epi.alpha = alpha; epi.beta = beta; epi.n_split = n_split;
+  // Gram / SYRK: identical operands that fit one tile in both dimensions are staged once
+  epi.same_ab = (A == B && lda == ldb && a_group_stride == b_group_stride && a_mn_major == 0 && b_mn_major == 0 && M == N &&
+                 M <= BM && N <= BN && !precise) ? 1 : 0;
   cudaStream_t st = (cudaStream_t)stream;
   int rc;
   const bool amn = a_mn_major != 0, bmn = b_mn_major != 0;
@@ -487,7 +493,7 @@ int ddl_gather_gemm_tcgen05(const float* const* parts, const int* part_dims, con
   Epilogue epi;
   epi.C = n_split > 1 ? scratch : C;
   epi.ldc = ldc; epi.c_group_stride = 0; epi.bias = bias; epi.bias_group_stride = 0;
-  epi.act = act; epi.slope = slope; epi.alpha = 1.f; epi.beta = 0.f; epi.n_split = n_split;
+  epi.act = act; epi.slope = slope; epi.alpha = 1.f; epi.beta = 0.f; epi.n_split = n_split; epi.same_ab = 0;
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, n_split);
 #define DDL_GATHER_CASE(BN_, P_)                                                                              \

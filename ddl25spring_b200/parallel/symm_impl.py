@@ -125,6 +125,8 @@ class SymmetricAggregator:
         self.G, self.P = max_rows_per_rank, row_elems
         self.rows = self.arena.alloc("client_rows", self.G * self.P * 4).view(self.G, self.P)
         self.result = self.arena.alloc("agg_result", self.P * 4)
+        self.partial = self.arena.alloc("agg_partial", self.P * 4)
+        self.partial_ptrs = self.arena.peer_ptrs("agg_partial")
         self.row_ptrs = self.arena.peer_ptrs("client_rows")
         self.res_ptrs = self.arena.peer_ptrs("agg_result")
 
@@ -145,7 +147,15 @@ class SymmetricAggregator:
         d0, d1 = shard_bounds(self.P, world, a.rank)
         w = [float(x) for x in weights.tolist()]
         if isinstance(aggregator, WeightedMean):
-            a.reduce(0, ptrs, w, self.res_ptrs, d0, d1)
+            # hierarchical: a linear rule lets every GPU pre-reduce ITS clients locally (HBM speed) so that only one
+            # partial row per GPU crosses NVLink; the fused kernel then sums the W partials shard by shard.
+            from .. import ops
+            n_local = W_local.shape[0]
+            if n_local:
+                ops.weighted_sum(self.rows[:n_local], [w[p] for p in mine_pos], self.partial)
+            else:
+                self.partial.zero_()
+            a.reduce(0, self.partial_ptrs, [1.0] * world, self.res_ptrs, d0, d1)
         elif isinstance(aggregator, (CoordinateMedian, TrimmedMean)) and K <= 64:
             if isinstance(aggregator, CoordinateMedian):
                 lo, hi = ((K - 1) // 2, (K - 1) // 2 + 1) if (K % 2 or aggregator.lower) else (K // 2 - 1, K // 2 + 1)
