@@ -213,7 +213,7 @@ int ddl_mnist_small_update(float* W, const float* wg_part, int n_cta, const floa
                            float* wt_fwd, float* wt_dgrad, int G, int B, const int* bsz, float lr, void* stream) {
   DDL_REQUIRE(G >= 1 && G <= MAX_G, "G=%d outside [1, %d]", G, MAX_G);
   StepInfo si = make_step(G, B, bsz, 0, 0.f, 0.f, lr);
-  dim3 grid(9, G);
+  dim3 grid(72, G);          // one conv2 weight per thread: the 18-partial reduction is latency-bound, so go wide
   small_update_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(W, wg_part, n_cta, c2b_part, c1_part, wt_fwd, wt_dgrad, si);
   DDL_LAUNCH_CHECK();
   return DDL_OK;

@@ -31,7 +31,9 @@ constexpr int WIN_BYTES = WIN_ROWS * 128;              // 23 552
 
 // ------------------------------------------------------------------------------------------ dgrad
 constexpr int DG_STAGES = 3;
-constexpr int DG_SUB = 4;                              // independent accumulators per tile (MMA chains are latency-bound)
+constexpr int DG_SUB = 1;                              // accumulators per tile (interleaving chains did not help: DESIGN.md finding 7)
+constexpr int DG_EPI_GROUPS = 2;                       // epilogue warpgroups on alternating tiles / TMEM buffers
+constexpr int DG_THREADS = 64 + DG_EPI_GROUPS * 128;
 constexpr int DG_STAGE_BYTES = 2 * WIN_BYTES;          // two 32-column halves of the dy2 window
 constexpr int DG_W_BYTES = 9 * 2 * C1 * 128;           // [tap][half][ci 32][co_l 32] = 72 KB
 constexpr int DG_SMEM = DG_W_BYTES + DG_STAGES * DG_STAGE_BYTES + 256 + 1024;
@@ -43,7 +45,7 @@ struct DgradParams {
   StepInfo si;
 };
 
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(DG_THREADS, 1)
 conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tm_dy2, const __grid_constant__ CUtensorMap tm_w, const DgradParams prm) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -130,8 +132,8 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tm_dy2, const __grid_cons
     const int quarter = warp & 3;
     const int m = quarter * 32 + lane;
     uint32_t acc_phase = 0;
-    int buf = 0;
-    for (int t = j; t < ntiles; t += prm.ctas_per_client) {
+    const int buf = (warp - 2) >> 2;                  // warpgroup w drains TMEM buffer w = every other tile
+    for (int t = j + buf * prm.ctas_per_client; t < ntiles; t += DG_EPI_GROUPS * prm.ctas_per_client) {
       mbar_wait(&acc_full[buf], acc_phase);
       fence_after_thread_sync();
       float v[32];
@@ -159,7 +161,7 @@ conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tm_dy2, const __grid_cons
           dst[i] = o;
         }
       }
-      if (++buf == 2) { buf = 0; acc_phase ^= 1; }
+      acc_phase ^= 1;
     }
   }
   __syncthreads();
@@ -195,7 +197,7 @@ extern "C" int ddl_mnist_conv2_dgrad(const float* wt_dgrad, const float* dy2, co
     DDL_CUDA_CHECK(cudaFuncSetAttribute(conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DG_SMEM));
     configured = true;
   }
-  conv2_dgrad_kernel<<<prm.ctas_per_client * G, 192, DG_SMEM, (cudaStream_t)stream>>>(tm_d, tm_w, prm);
+  conv2_dgrad_kernel<<<prm.ctas_per_client * G, DG_THREADS, DG_SMEM, (cudaStream_t)stream>>>(tm_d, tm_w, prm);
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

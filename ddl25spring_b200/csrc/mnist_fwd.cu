@@ -84,11 +84,15 @@ __global__ void __launch_bounds__(256) prep_conv2_kernel(const float* __restrict
 }
 
 // ------------------------------------------------------------------------------------------ conv2
-constexpr int kStages = 4;
+constexpr int kStages = 3;
+// Two epilogue warpgroups work on alternating tiles / TMEM buffers: one 4-warp epilogue (tcgen05.ld -> staging ->
+// pool -> store, ~3000 cycles of latency per tile) could not keep up with the ~1200-cycle MMA phase (ncu: tensor
+// pipe 38 % active), see profiles/r1_ncu_conv2_fwd_summary.txt.
+constexpr int kEpiGroups = 2;
 // A chain of tcgen05.mma into ONE accumulator is latency-bound at small N (measured ~90 cycles per dependent
 // MMA at N = 64 on B200 vs a 32-48 cycle issue floor), so the 36 MMAs of a tile alternate between FWD_SUB
 // independent TMEM accumulators that the epilogue adds up.
-constexpr int FWD_SUB = 2;
+constexpr int FWD_SUB = 1;
 constexpr int W_TILE_BYTES = C2 * 128;                 // 64 couts x 32 cins x 4 B = 8 KB per tap
 constexpr int W_BYTES = 9 * W_TILE_BYTES;              // 72 KB
 constexpr int WIN_BYTES = WIN_ROWS * 128;              // 23 552 B (multiple of 1024)
@@ -96,7 +100,8 @@ constexpr int STG_PITCH = 68;                          // floats; conflict-free 
 constexpr int STG_BYTES = TILE_M * STG_PITCH * 4;
 constexpr int POOL_PITCH = 25;                          // floats per channel of the pooled staging tile (24 + 1 pad)
 constexpr int POOL_BYTES = C2 * POOL_PITCH * 4 + C2 * 24 + C2 * 4;   // pooled values | mask bytes | bias
-constexpr int CONV2_SMEM = W_BYTES + kStages * WIN_BYTES + STG_BYTES + POOL_BYTES + 256 + 1024;
+constexpr int CONV2_SMEM = W_BYTES + kStages * WIN_BYTES + kEpiGroups * (STG_BYTES + POOL_BYTES) + 256 + 1024;
+constexpr int kConv2Threads = 64 + kEpiGroups * 128;
 
 struct Conv2Params {
   const float* W;        // weight arena base (bias read from OFF_C2B of each client's row)
@@ -106,21 +111,23 @@ struct Conv2Params {
   StepInfo si;
 };
 
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
 
 template <bool TRAIN>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(kConv2Threads, 1)
 conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__ CUtensorMap tm_w,
                       const Conv2Params prm) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* s_w = smem;
   uint8_t* s_win = smem + W_BYTES;
-  float* s_stage = reinterpret_cast<float*>(s_win + kStages * WIN_BYTES);
-  float* s_pool = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(s_stage) + STG_BYTES);   // [64][25]
+  const int wg = (threadIdx.x >= 64) ? ((threadIdx.x - 64) >> 7) : 0;          // epilogue warpgroup of this thread
+  uint8_t* s_epi = s_win + kStages * WIN_BYTES + wg * (STG_BYTES + POOL_BYTES);
+  float* s_stage = reinterpret_cast<float*>(s_epi);
+  float* s_pool = reinterpret_cast<float*>(s_epi + STG_BYTES);                                 // [64][25]
   uint8_t* s_pmask = reinterpret_cast<uint8_t*>(s_pool + C2 * POOL_PITCH);                     // [64][24]
   float* s_bias = reinterpret_cast<float*>(s_pmask + C2 * 24);                                 // [64]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(s_stage) + STG_BYTES + POOL_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_win + kStages * WIN_BYTES + kEpiGroups * (STG_BYTES + POOL_BYTES));
   uint64_t* full_bar = bars;                 // [kStages] window landed
   uint64_t* empty_bar = bars + kStages;      // [kStages] MMAs reading the window retired
   uint64_t* acc_full = bars + 2 * kStages;   // [2]
@@ -200,14 +207,15 @@ conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_co
     // ===================== epilogue: bias + ReLU + 2x2 max-pool + dropout =====================
     const int quarter = warp & 3;
     const int m = quarter * 32 + lane;            // accumulator row = flat position inside the tile
-    const int et = (warp - 2) * 32 + lane;        // 0..127 for the pooling phase
+    const int et = ((warp - 2) & 3) * 32 + lane;  // 0..127 inside this epilogue warpgroup
+    const int bar_id = 1 + wg;
     const int pc = et & 63, half = et >> 6;       // pooled channel / pooled row within the tile
     if (et < C2) s_bias[et] = prm.W[(int64_t)g * P + OFF_C2B + et];
-    epi_bar_sync();
+    epi_bar_sync(bar_id);
     const float keep_scale = TRAIN ? 1.f / (1.f - si.p1) : 1.f;
     uint32_t acc_phase = 0;
-    int buf = 0;
-    for (int t = j; t < ntiles; t += prm.ctas_per_client) {
+    const int buf = wg;                            // warpgroup w drains TMEM buffer w = every other tile of this CTA
+    for (int t = j + wg * prm.ctas_per_client; t < ntiles; t += kEpiGroups * prm.ctas_per_client) {
       const int row = g * si.B + t / TILES_PER_SAMPLE;
       const int hb = t % TILES_PER_SAMPLE;
       mbar_wait(&acc_full[buf], acc_phase);
@@ -238,7 +246,7 @@ conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_co
       fence_before_thread_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);   // TMEM buffer may be overwritten by tile t+2
-      epi_bar_sync();
+      epi_bar_sync(bar_id);
       // pooled row ph = 2*hb + half ; window rows (2*half, 2*half+1) of the 4-row tile.  Results go to
       // a small staging tile first so that the global stores below are contiguous 96 B runs per channel.
       const int64_t tile_base = (int64_t)row * FLAT + hb * 2 * HP;      // + c*144 + [0, 24)
@@ -258,7 +266,7 @@ conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_co
         s_pool[pc * POOL_PITCH + o] = keep ? best * keep_scale : 0.f;
         if (TRAIN) s_pmask[pc * 24 + o] = (uint8_t)(arg | ((keep && best > 0.f) ? 4 : 0));
       }
-      epi_bar_sync();
+      epi_bar_sync(bar_id);
       for (int idx = et; idx < C2 * 6; idx += 128) {                    // 64 channels x 6 float4
         const int c = idx / 6, k4 = idx % 6;
         const float* src = s_pool + c * POOL_PITCH + 4 * k4;
@@ -271,7 +279,7 @@ conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_co
               *reinterpret_cast<const uint2*>(s_pmask + c * 24 + 8 * k8);
         }
       }
-      if (++buf == 2) { buf = 0; acc_phase ^= 1; }
+      acc_phase ^= 1;
     }
   }
   __syncthreads();
@@ -345,8 +353,8 @@ int ddl_mnist_conv2_pool_fwd(const float* W, const float* wt_fwd, const float* a
     configured = true;
   }
   const int grid = prm.ctas_per_client * G;
-  if (train) conv2_pool_fwd_kernel<true><<<grid, 192, CONV2_SMEM, (cudaStream_t)stream>>>(tm_a, tm_w, prm);
-  else conv2_pool_fwd_kernel<false><<<grid, 192, CONV2_SMEM, (cudaStream_t)stream>>>(tm_a, tm_w, prm);
+  if (train) conv2_pool_fwd_kernel<true><<<grid, kConv2Threads, CONV2_SMEM, (cudaStream_t)stream>>>(tm_a, tm_w, prm);
+  else conv2_pool_fwd_kernel<false><<<grid, kConv2Threads, CONV2_SMEM, (cudaStream_t)stream>>>(tm_a, tm_w, prm);
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
