@@ -1,0 +1,122 @@
+"""Autograd bridges from ``torch.nn`` modules to the hand-written kernels.
+
+``KernelLinear`` / ``kernel_linear`` run forward, input-gradient and weight-gradient of a Linear layer on the tcgen05
+GEMM (K10: one kernel, K-major and MN-major operands, no transposes); ``kernel_cross_entropy`` is the fused
+softmax-xent (K13: value + gradient in one pass, incl. the shifted causal-LM form); ``kernel_rms_norm`` the RMSNorm
+pair.  On CPU tensors every function falls back to the plain PyTorch statement of the same math (the oracle).
+``use_kernels(model)`` swaps the ``nn.Linear`` modules of a model (e.g. the LLaMA of models/llama.py) in place.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from . import _lib
+from .gemm import gemm
+
+
+class _LinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b, precise):
+        x2 = x.reshape(-1, x.shape[-1]).contiguous()
+        y = gemm(x2, w, bias=b, precise=precise)
+        ctx.save_for_backward(x2, w)
+        ctx.has_bias, ctx.precise, ctx.shape = b is not None, precise, x.shape
+        return y.view(*x.shape[:-1], w.shape[0])
+
+    @staticmethod
+    def backward(ctx, gy):
+        x2, w = ctx.saved_tensors
+        g2 = gy.reshape(-1, gy.shape[-1]).contiguous()
+        n_out, n_in = w.shape
+        mn_ok = n_in % 32 == 0 and n_out % 32 == 0 and (w.stride(0) * 4) % 16 == 0
+        gx = gw = gb = None
+        if ctx.needs_input_grad[0]:
+            gx = (gemm(g2, w, b_mn=True, precise=ctx.precise) if mn_ok else g2 @ w).view(ctx.shape)
+        if ctx.needs_input_grad[1]:
+            gw = gemm(g2, x2, a_mn=True, b_mn=True, precise=ctx.precise) if mn_ok else g2.t() @ x2
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            gb = g2.sum(0)
+        return gx, gw, gb, None
+
+
+def kernel_linear(x, w, b=None, precise: bool = True):
+    if not x.is_cuda or x.dtype != torch.float32 or (w.stride(0) * 4) % 16 != 0 or w.stride(1) != 1:
+        return F.linear(x, w, b)
+    return _LinearFn.apply(x, w, b, precise)
+
+
+class KernelLinear(nn.Linear):
+    precise = True
+
+    def forward(self, x):
+        return kernel_linear(x, self.weight, self.bias, self.precise)
+
+
+class _XentFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target, ignore_index):
+        from . import softmax_xent
+        n_valid = (target != ignore_index).sum().clamp_min(1)
+        loss, grad = softmax_xent(logits, target, reduction="sum", want_grad=True, ignore_index=ignore_index)
+        ctx.save_for_backward(grad, n_valid)
+        return loss / n_valid
+
+    @staticmethod
+    def backward(ctx, g):
+        grad, n_valid = ctx.saved_tensors
+        return grad * (g / n_valid), None, None
+
+
+def kernel_cross_entropy(logits: torch.Tensor, target: torch.Tensor, ignore_index: int = -100):
+    """mean cross-entropy over the rows whose target != ignore_index (``F.cross_entropy`` semantics)."""
+    if not logits.is_cuda or logits.dtype != torch.float32:
+        return F.cross_entropy(logits, target, ignore_index=ignore_index)
+    return _XentFn.apply(logits.contiguous(), target.contiguous(), ignore_index)
+
+
+def kernel_causal_lm_loss(logits: torch.Tensor, tokens: torch.Tensor):
+    """Shifted next-token loss (lab/tutorial_1b/primer/intro.py:29) through the fused kernel."""
+    V = logits.shape[-1]
+    return kernel_cross_entropy(logits[:, :-1].reshape(-1, V), tokens.to(logits.device)[:, 1:].reshape(-1))
+
+
+class _RMSNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, eps):
+        x2 = x.reshape(-1, x.shape[-1]).contiguous()
+        y = torch.empty_like(x2)
+        rstd = torch.empty(x2.shape[0], device=x.device, dtype=torch.float32)
+        _lib.check(_lib.lib().ddl_rmsnorm_fwd(_lib.p(x2), _lib.p(w), _lib.p(y), _lib.p(rstd), _lib.i64(x2.shape[0]), int(x2.shape[1]),
+                                              _lib.f32(eps), _lib.stream()), "ddl_rmsnorm_fwd")
+        ctx.save_for_backward(x2, w, rstd)
+        ctx.shape = x.shape
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x2, w, rstd = ctx.saved_tensors
+        g2 = gy.reshape(-1, gy.shape[-1]).contiguous()
+        dx, dw = torch.empty_like(x2), torch.zeros_like(w)
+        _lib.check(_lib.lib().ddl_rmsnorm_bwd(_lib.p(x2), _lib.p(w), _lib.p(g2), _lib.p(rstd), _lib.p(dx), _lib.p(dw),
+                                              _lib.i64(x2.shape[0]), int(x2.shape[1]), _lib.stream()), "ddl_rmsnorm_bwd")
+        return dx.view(ctx.shape), dw, None
+
+
+def kernel_rms_norm(x, w, eps: float = 1e-5):
+    if not x.is_cuda or x.dtype != torch.float32:
+        return x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + eps) * w
+    return _RMSNormFn.apply(x, w.contiguous(), eps)
+
+
+def use_kernels(model: nn.Module, precise: bool = True) -> nn.Module:
+    """Route every ``nn.Linear`` (and RMSNorm of models/llama.py) of ``model`` through the kernels, in place."""
+    from ..models.llama import RMSNorm
+    for mod in model.modules():
+        if type(mod) is nn.Linear:
+            mod.__class__ = KernelLinear
+            mod.precise = precise
+        elif isinstance(mod, RMSNorm):
+            mod.forward = (lambda m: (lambda x: kernel_rms_norm(x, m.weight, m.eps)))(mod)
+    return model

@@ -194,6 +194,12 @@ int ddl_gather_gemm_tcgen05(const float* const* parts, const int* part_dims, con
                             const float* W, int64_t ldw, float* C, int64_t ldc, const float* bias, int act, float slope,
                             int M, int N, int precise, int n_split, float* scratch, void* stream);
 
+/* ---- K16 (part): RMSNorm forward / backward, one warp per row (ref: the LLaMA blocks of `simplellm`,
+ * lab/tutorial_1b/primer/intro.py:17,28).  rstd [rows] is written by fwd and read by bwd; dw must be zeroed. */
+int ddl_rmsnorm_fwd(const float* x, const float* w, float* y, float* rstd, int64_t rows, int d, float eps, void* stream);
+int ddl_rmsnorm_bwd(const float* x, const float* w, const float* dy, const float* rstd, float* dx, float* dw, int64_t rows, int d,
+                    void* stream);
+
 #ifdef __cplusplus
 }
 #endif
