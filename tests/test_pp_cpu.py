@@ -90,3 +90,41 @@ def test_pp_x_dp_hybrid_completes_and_averages():
         ref = dict(ref_stages[sid].named_parameters())
         for n, g in grads.items():
             torch.testing.assert_close(g, ref[n].grad, rtol=1e-4, atol=1e-6)
+
+
+def _two_stage_worker(rank, world, which):
+    import torch.nn.functional as Fn
+    mesh = pp.Mesh(2, 1)
+    torch.manual_seed(0)
+    if which == "resnet":
+        from ddl25spring_b200.models.resnet import resnet18, split_resnet18_two_stage
+        full = resnet18().eval()                          # eval: BN uses running stats, so micro-batching is exact
+        stages = split_resnet18_two_stage(full)
+        x = torch.randn(4, 3, 32, 32, generator=torch.Generator().manual_seed(1))
+        y = torch.randint(0, 10, (4,), generator=torch.Generator().manual_seed(2))
+        act_shape, loss_fn = (2, 128, 4, 4), (lambda o, t: Fn.cross_entropy(o, t))
+    else:
+        from ddl25spring_b200.models.dcgan import Generator
+        full = Generator(nz=16, ngf=8).eval()
+        stages = full.stages(3)
+        x = torch.randn(4, 16, 1, 1, generator=torch.Generator().manual_seed(1))
+        y = torch.zeros(4, 3, 64, 64)
+        act_shape, loss_fn = (2, 16, 16, 16), (lambda o, t: Fn.mse_loss(o, t))
+    st = pp.PipelineStage(stages[rank], mesh, act_shape, schedule="1f1b", n_micro=2, loss_fn=loss_fn, device="cpu")
+    st.run(inputs=list(x.split(2)), targets=list(y.split(2)))
+    mine = {n: p.grad.clone() for n, p in stages[rank].named_parameters() if p.grad is not None}
+    for p in full.parameters():
+        p.grad = None
+    out = full(x)
+    (sum(loss_fn(o, t) for o, t in zip(out.split(2), y.split(2))) / 2).backward()
+    ref = {n: p.grad.clone() for n, p in stages[rank].named_parameters() if p.grad is not None}
+    return max(float((mine[n] - ref[n]).abs().max()) for n in mine), len(mine)
+
+
+@pytest.mark.timeout(200)
+@pytest.mark.parametrize("which", ["resnet", "dcgan"])
+def test_two_stage_model_parallel_split(which):
+    """BASELINE.json config 5: 2-stage model-parallel split (ResNet-18 / DCGAN generator) == unsplit model."""
+    outs = run_distributed(_two_stage_worker, 2, (which,), timeout=150)
+    for err, n in outs:
+        assert n > 0 and err < 1e-4, (err, n)
