@@ -70,11 +70,14 @@ class _RoundTimer:
 
 class Server(ABC):
     def __init__(self, lr: float, batch_size: int, seed: int, *, model_fn: Callable[[], nn.Module] = MnistCnn,
-                 test_set=None, device=None, include_buffers: bool = False, test_batch_size: int = 10_000) -> None:
+                 test_set=None, device=None, include_buffers: bool = False, test_batch_size: int = 10_000,
+                 loss_fn=nll_of_log_probs) -> None:
         self.clients: list[Client] = []
         self.lr, self.batch_size, self.seed = lr, batch_size, seed
         self.device = torch.device(device) if device is not None else default_device()
         self.model_fn = model_fn
+        self.loss_fn = loss_fn                       # nll for log-prob models (MnistCnn), cross-entropy for logit models
+        self.include_buffers = include_buffers
         torch.manual_seed(seed)                      # global-model init is seeded (hfl_complete.py:165)
         self.slot = ModelSlot(model_fn, self.device, include_buffers=include_buffers)
         self.model = self.slot.model
@@ -104,7 +107,7 @@ class Server(ABC):
             return float("nan")
         x, y = self._test_xy
         rank, world = (dist.get_rank(), dist.get_world_size()) if _dist_ready() else (0, 1)
-        xs, ys = x[rank::world], y[rank::world]
+        xs, ys = x[rank::world].contiguous(), y[rank::world].contiguous()   # the eval kernel reads raw pointers
         self.model.eval()
         correct = torch.zeros((), dtype=torch.int32, device=self.device)
         for lo in range(0, len(ys), self.test_batch_size):
@@ -124,7 +127,7 @@ class CentralizedServer(Server):
     def __init__(self, lr: float, batch_size: int, seed: int, *, train_set, **kw) -> None:
         super().__init__(lr, batch_size, seed, **kw)
         self.trainer = WeightClient(train_set, lr, batch_size, 1, model_fn=self.model_fn, device=self.device,
-                                    slot=self.slot, loss_fn=kw.get("loss_fn", nll_of_log_probs))
+                                    slot=self.slot, loss_fn=self.loss_fn)
         self.clients = []
 
     def run(self, nr_rounds: int) -> RunResult:
@@ -153,7 +156,7 @@ class DecentralizedServer(Server):
 
     def __init__(self, lr: float, batch_size: int, client_subsets: Sequence, client_fraction: float, seed: int, *,
                  aggregator: Aggregator | None = None, attack: Attack | None = None,
-                 malicious: np.ndarray | None = None, **kw) -> None:
+                 malicious: np.ndarray | None = None, collective=None, **kw) -> None:
         super().__init__(lr, batch_size, seed, **kw)
         self.nr_clients = len(client_subsets)
         self.client_fraction = client_fraction
@@ -166,8 +169,10 @@ class DecentralizedServer(Server):
         self.rank, self.world = (dist.get_rank(), dist.get_world_size()) if _dist_ready() else (0, 1)
         # one borrowed model slot for all of this rank's clients (they train one after another here;
         # the packed engine in fl/packed.py trains them concurrently with grouped kernels)
-        self.worker_slot = ModelSlot(self.model_fn, self.device, include_buffers=kw.get("include_buffers", False))
+        self.worker_slot = ModelSlot(self.model_fn, self.device, include_buffers=self.include_buffers)
         self._updates: torch.Tensor | None = None
+        # parallel.symm_impl.SymmetricAggregator(row_elems=arena.size): fused peer-memory aggregation across ranks
+        self.collective = collective
 
     # ------------------------------------------------------------------ helpers
     def _update_matrix(self, k: int) -> torch.Tensor:
@@ -178,8 +183,9 @@ class DecentralizedServer(Server):
     def _collect_updates(self, nr_round: int, chosen: np.ndarray, gflat: torch.Tensor):
         """Run the chosen clients (this rank's share) and return ``(updates[K, D], slowest_client_s)``."""
         K = len(chosen)
-        U = self._update_matrix(K)
-        if self.world > 1:
+        fused = self.collective is not None and self.world > 1
+        U = self.collective.row_buffer(-(-K // self.world)) if fused else self._update_matrix(K)
+        if self.world > 1 and not fused:
             U.zero_()
         slowest = 0.0
         for pos, c_i in enumerate(chosen):
@@ -190,12 +196,12 @@ class DecentralizedServer(Server):
             seed = client_round_seed(self.seed, ind, nr_round, self.nr_clients_per_round)
             client = self.clients[ind]
             client.bind(self.worker_slot)
-            client.update_flat(gflat, seed, out=U[pos])
+            row = U[pos // self.world] if fused else U[pos]      # fused: this rank's rows only, in symmetric memory
+            client.update_flat(gflat, seed, out=row)
             if self.attack is not None and self.malicious[ind]:
-                self.attack(U[pos], None if self.message_is_gradient else gflat, client=ind, nr_round=nr_round,
-                            out=U[pos])
+                self.attack(row, None if self.message_is_gradient else gflat, client=ind, nr_round=nr_round, out=row)
             slowest = max(slowest, perf_counter() - t0)
-        if self.world > 1:
+        if self.world > 1 and not fused:
             # rows trained elsewhere are zero here: a SUM all-reduce assembles the full matrix on
             # every rank (gloo/NCCL path; parallel/symm.py replaces this with peer-memory kernels)
             dist.all_reduce(U)
@@ -234,8 +240,14 @@ class DecentralizedServer(Server):
             elapsed += slowest
             t_agg = perf_counter()
             with torch.no_grad():
-                agg = self.aggregator(U, weights, out=agg_out,
-                                      global_flat=None if self.message_is_gradient else gflat)
+                if self.collective is not None and self.world > 1:
+                    mine_pos = [p for p in range(len(chosen)) if p % self.world == self.rank]
+                    base = torch.zeros_like(gflat) if self.message_is_gradient else gflat.clone()
+                    self.collective.aggregate(self.aggregator, U[:len(mine_pos)], mine_pos, weights, base)
+                    agg = agg_out.copy_(base)
+                else:
+                    agg = self.aggregator(U, weights, out=agg_out,
+                                          global_flat=None if self.message_is_gradient else gflat)
                 self._apply(agg)
             res.device_time_ms.append(timer.stop_ms())
             elapsed += perf_counter() - t_agg
@@ -254,7 +266,7 @@ class FedSgdGradientServer(DecentralizedServer):
 
     def __init__(self, lr: float, client_subsets, client_fraction: float, seed: int, **kw) -> None:
         super().__init__(lr, -1, client_subsets, client_fraction, seed, **kw)
-        ckw = dict(model_fn=self.model_fn, device=self.device, slot=self.worker_slot)
+        ckw = dict(model_fn=self.model_fn, device=self.device, slot=self.worker_slot, loss_fn=self.loss_fn)
         self.clients = [GradientClient(subset, **ckw) for subset in client_subsets]
 
     def _apply(self, aggregated):
@@ -271,7 +283,7 @@ class FedSgdWeightServer(DecentralizedServer):
 
     def __init__(self, lr: float, client_subsets, client_fraction: float, seed: int, **kw) -> None:
         super().__init__(lr, -1, client_subsets, client_fraction, seed, **kw)
-        ckw = dict(model_fn=self.model_fn, device=self.device, slot=self.worker_slot)
+        ckw = dict(model_fn=self.model_fn, device=self.device, slot=self.worker_slot, loss_fn=self.loss_fn)
         self.clients = [GradientClient(subset, **ckw) for subset in client_subsets]
 
     def _apply(self, aggregated):
@@ -289,7 +301,7 @@ class FedAvgServer(DecentralizedServer):
         super().__init__(lr, batch_size, client_subsets, client_fraction, seed, **kw)
         self.name = "FedAvg"
         self.nr_local_epochs = nr_local_epochs
-        ckw = dict(model_fn=self.model_fn, device=self.device, slot=self.worker_slot)
+        ckw = dict(model_fn=self.model_fn, device=self.device, slot=self.worker_slot, loss_fn=self.loss_fn)
         self.clients = [WeightClient(subset, lr, batch_size, nr_local_epochs, **ckw) for subset in client_subsets]
 
     def _apply(self, aggregated):

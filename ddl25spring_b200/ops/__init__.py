@@ -182,6 +182,8 @@ def eval_top1(logits: torch.Tensor, target: torch.Tensor, count: torch.Tensor | 
         return c if count is None else count.add_(c)
     if count is None:
         count = torch.zeros((), device=logits.device, dtype=torch.int32)
+    assert logits.stride(1) == 1
+    target = target.contiguous()
     L = _lib.lib()
     _lib.check(L.ddl_eval_top1(_lib.p(_lib.req_f32(logits)), _lib.i64(logits.stride(0)), _lib.p(target),
                                _lib.i64(logits.shape[0]), int(logits.shape[1]), _lib.p(count), _lib.stream()),

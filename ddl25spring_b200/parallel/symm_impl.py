@@ -132,7 +132,7 @@ class SymmetricAggregator:
 
     def row_buffer(self, G: int) -> torch.Tensor:
         """Symmetric storage for this rank's ``G`` client weight rows (the engine trains in place in it)."""
-        assert G <= self.G
+        assert G <= self.G, f"{G} rows per rank requested, arena was built for {self.G}"
         return self.rows[:G]
 
     def aggregate(self, aggregator, W_local: torch.Tensor, mine_pos, weights: torch.Tensor, gflat: torch.Tensor) -> None:

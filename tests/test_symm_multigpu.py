@@ -161,3 +161,46 @@ def test_vfl_fused_gather_gemm_equals_allgather_path():
         assert o["fused"][0] == pytest.approx(o["allgather"][0], rel=2e-4)
         torch.testing.assert_close(o["fused"][1], o["allgather"][1], rtol=1e-3, atol=1e-5)
         torch.testing.assert_close(o["fused"][2], o["allgather"][2], rtol=1e-3, atol=1e-5)
+
+
+def _generic_worker(rank, world, agg_name, with_bn):
+    import torch.nn.functional as Fn
+    from ddl25spring_b200.core.data import SyntheticMNIST, split
+    from ddl25spring_b200.fl.aggregators import make_aggregator
+    from ddl25spring_b200.fl.attacks import SignFlip
+    from ddl25spring_b200.fl.server import FedAvgServer
+    from ddl25spring_b200.parallel.symm_impl import SymmetricAggregator
+    import numpy as np
+
+    def model_fn():
+        layers = [torch.nn.Flatten(), torch.nn.Linear(784, 64)]
+        if with_bn:
+            layers.append(torch.nn.BatchNorm1d(64))
+        return torch.nn.Sequential(*layers, torch.nn.ReLU(), torch.nn.Linear(64, 10))
+    ds = SyntheticMNIST(n_train=1600, n_test=400, seed=2, noise=0.8)
+    subsets = split(ds.train, 8, True, 3)
+    mal = np.zeros(8, dtype=bool); mal[1] = True
+    kw = dict(n_byzantine=1, multi=4) if agg_name == "krum" else {}
+    outs = {}
+    coll = None
+    for name in ("fused", "nccl"):
+        srv = FedAvgServer(0.05, 50, subsets, 1.0, 1, 3, model_fn=model_fn, test_set=ds.test, device="cuda", include_buffers=with_bn,
+                           loss_fn=lambda o, t: Fn.cross_entropy(o, t), aggregator=make_aggregator(agg_name, **kw),
+                           attack=SignFlip(4.0), malicious=mal)
+        if name == "fused":
+            coll = SymmetricAggregator(max_rows_per_rank=4, row_elems=srv.arena.size)
+            srv.collective = coll
+        res = srv.run(2)
+        torch.cuda.synchronize()
+        outs[name] = (srv.arena.flat.clone().cpu(), res.test_accuracy)
+    return outs
+
+
+@pytest.mark.timeout(400)
+@pytest.mark.parametrize("agg_name,with_bn", [("mean", False), ("median", True), ("krum", True)])
+def test_generic_server_fused_equals_nccl_path(agg_name, with_bn):
+    world = min(torch.cuda.device_count(), 4)
+    outs = run_distributed(_generic_worker, world, (agg_name, with_bn), timeout=300, backend="nccl")
+    for o in outs:
+        assert torch.isfinite(o["fused"][0]).all()
+        torch.testing.assert_close(o["fused"][0], o["nccl"][0], rtol=1e-4, atol=1e-5)
