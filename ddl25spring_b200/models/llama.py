@@ -52,12 +52,13 @@ class Attention(nn.Module):
         cos, sin = rope_tables(self.hd, ctx_size)
         self.register_buffer("rope_cos", cos, persistent=False)
         self.register_buffer("rope_sin", sin, persistent=False)
+        self.attn_fn = None        # ops.nn.use_kernels() installs the hand-written causal attention here
 
     def forward(self, x):
         B, T, C = x.shape
         q, k, v = self.wqkv(x).view(B, T, 3, self.h, self.hd).permute(2, 0, 3, 1, 4)
         q, k = apply_rope(q, self.rope_cos, self.rope_sin), apply_rope(k, self.rope_cos, self.rope_sin)
-        o = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+        o = self.attn_fn(q, k, v) if self.attn_fn is not None else F.scaled_dot_product_attention(q, k, v, is_causal=True)
         return self.wo(o.transpose(1, 2).reshape(B, T, C))
 
 

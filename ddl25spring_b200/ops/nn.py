@@ -110,13 +110,91 @@ def kernel_rms_norm(x, w, eps: float = 1e-5):
     return _RMSNormFn.apply(x, w.contiguous(), eps)
 
 
+class _BatchNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, run_mean, run_var, training, momentum, eps):
+        xc = x.contiguous()
+        N, Cc = xc.shape[0], xc.shape[1]
+        S = xc.numel() // (N * Cc)
+        y = torch.empty_like(xc)
+        mean = torch.empty(Cc, device=x.device, dtype=torch.float32)
+        rstd = torch.empty_like(mean)
+        _lib.check(_lib.lib().ddl_batchnorm_fwd(_lib.p(xc), _lib.p(gamma), _lib.p(beta), _lib.p(y), _lib.p(mean), _lib.p(rstd),
+                                                _lib.p(run_mean), _lib.p(run_var), int(N), int(Cc), int(S), _lib.f32(eps),
+                                                _lib.f32(momentum), int(training), _lib.stream()), "ddl_batchnorm_fwd")
+        ctx.save_for_backward(xc, gamma, mean, rstd)
+        ctx.dims = (N, Cc, S)
+        ctx.training = training
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        xc, gamma, mean, rstd = ctx.saved_tensors
+        N, Cc, S = ctx.dims
+        assert ctx.training, "backward through eval-mode BatchNorm is not on a kernel path"
+        gyc = gy.contiguous()
+        dx = torch.empty_like(xc)
+        dg, db = torch.empty_like(mean), torch.empty_like(mean)
+        _lib.check(_lib.lib().ddl_batchnorm_bwd(_lib.p(xc), _lib.p(gyc), _lib.p(gamma), _lib.p(mean), _lib.p(rstd), _lib.p(dx), _lib.p(dg),
+                                                _lib.p(db), int(N), int(Cc), int(S), _lib.stream()), "ddl_batchnorm_bwd")
+        return dx, dg, db, None, None, None, None, None
+
+
+def kernel_batch_norm(x, bn: nn.modules.batchnorm._BatchNorm):
+    """BatchNorm1d/2d forward (+ backward) on the K11 kernels; falls back to torch off-GPU or in eval-with-grad."""
+    if not x.is_cuda or x.dtype != torch.float32 or bn.weight is None or not bn.track_running_stats or bn.momentum is None \
+            or (not bn.training and torch.is_grad_enabled() and x.requires_grad):
+        return F.batch_norm(x, bn.running_mean, bn.running_var, bn.weight, bn.bias, bn.training, bn.momentum or 0.0, bn.eps)
+    if bn.training and bn.num_batches_tracked is not None:
+        bn.num_batches_tracked.add_(1)
+    return _BatchNormFn.apply(x, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.training, bn.momentum, bn.eps)
+
+
+class _CausalAttnFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, scale):
+        B, H, T, D = q.shape
+        qc, kc, vc = q.contiguous(), k.contiguous(), v.contiguous()
+        o = torch.empty_like(qc)
+        lse = torch.empty(B * H, T, device=q.device, dtype=torch.float32)
+        _lib.check(_lib.lib().ddl_causal_attention_fwd(_lib.p(qc), _lib.p(kc), _lib.p(vc), _lib.p(o), _lib.p(lse), int(B * H), int(T),
+                                                       int(D), _lib.f32(scale), _lib.stream()), "ddl_causal_attention_fwd")
+        ctx.save_for_backward(qc, kc, vc, o, lse)
+        ctx.scale = scale
+        return o
+
+    @staticmethod
+    def backward(ctx, go):
+        q, k, v, o, lse = ctx.saved_tensors
+        B, H, T, D = q.shape
+        goc = go.contiguous()
+        dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+        delta = torch.empty_like(lse)
+        _lib.check(_lib.lib().ddl_causal_attention_bwd(_lib.p(q), _lib.p(k), _lib.p(v), _lib.p(o), _lib.p(goc), _lib.p(lse), _lib.p(dq),
+                                                       _lib.p(dk), _lib.p(dv), _lib.p(delta), int(B * H), int(T), int(D),
+                                                       _lib.f32(ctx.scale), _lib.stream()), "ddl_causal_attention_bwd")
+        return dq, dk, dv, None
+
+
+def kernel_causal_attention(q, k, v):
+    """softmax(q k^T / sqrt(D) + causal mask) v for [B, H, T, D] tensors (K16)."""
+    D = q.shape[-1]
+    if not q.is_cuda or q.dtype != torch.float32 or D not in (16, 32, 48, 64):
+        return F.scaled_dot_product_attention(q, k, v, is_causal=True)
+    return _CausalAttnFn.apply(q, k, v, 1.0 / (D ** 0.5))
+
+
 def use_kernels(model: nn.Module, precise: bool = True) -> nn.Module:
     """Route every ``nn.Linear`` (and RMSNorm of models/llama.py) of ``model`` through the kernels, in place."""
-    from ..models.llama import RMSNorm
+    from ..models.llama import Attention, RMSNorm
     for mod in model.modules():
         if type(mod) is nn.Linear:
             mod.__class__ = KernelLinear
             mod.precise = precise
         elif isinstance(mod, RMSNorm):
             mod.forward = (lambda m: (lambda x: kernel_rms_norm(x, m.weight, m.eps)))(mod)
+        elif isinstance(mod, (nn.BatchNorm1d, nn.BatchNorm2d)):
+            mod.forward = (lambda m: (lambda x: kernel_batch_norm(x, m)))(mod)
+        elif isinstance(mod, Attention):
+            mod.attn_fn = kernel_causal_attention
     return model

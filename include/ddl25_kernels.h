@@ -200,6 +200,23 @@ int ddl_rmsnorm_fwd(const float* x, const float* w, float* y, float* rstd, int64
 int ddl_rmsnorm_bwd(const float* x, const float* w, const float* dy, const float* rstd, float* dx, float* dw, int64_t rows, int d,
                     void* stream);
 
+/* ---- K11: BatchNorm 1d / 2d (ref: lab/tutorial_2a/generative-modeling.py:21-45, lab/tutorial_2b/exercise_3.py; ResNet-18 /
+ * DCGAN [north star]).  x, y, dy, dx: [N, C, S] (S = H*W or 1).  Training forward writes save_mean / save_rstd [C] and
+ * updates running_mean / running_var (may be NULL) like torch (momentum, unbiased running variance). */
+int ddl_batchnorm_fwd(const float* x, const float* gamma, const float* beta, float* y, float* save_mean, float* save_rstd,
+                      float* running_mean, float* running_var, int N, int C, int S, float eps, float momentum, int training,
+                      void* stream);
+int ddl_batchnorm_bwd(const float* x, const float* dy, const float* gamma, const float* save_mean, const float* save_rstd, float* dx,
+                      float* dgamma, float* dbeta, int N, int C, int S, void* stream);
+
+/* ---- K16: causal self-attention, flash-style on CUDA cores for the labs' shape (T = 256, head dim 48) (ref: the LLaMA blocks of
+ * `simplellm`, lab/tutorial_1b/primer/intro.py:17,28).  q, k, v, o, dO, dq, dk, dv: [BH, T, D] fp32, D in {16, 32, 48, 64};
+ * lse, delta_scratch: [BH, T].  Nothing of size T x T is materialised; backward recomputes probabilities from lse. */
+int ddl_causal_attention_fwd(const float* q, const float* k, const float* v, float* o, float* lse, int BH, int T, int D, float scale,
+                             void* stream);
+int ddl_causal_attention_bwd(const float* q, const float* k, const float* v, const float* o, const float* dO, const float* lse,
+                             float* dq, float* dk, float* dv, float* delta_scratch, int BH, int T, int D, float scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -53,3 +53,46 @@ def test_llama_on_kernels_matches_torch(cuda_lib):
     torch.testing.assert_close(lb, la, rtol=1e-4, atol=1e-4)
     for (n, p), q in zip(a.named_parameters(), b.parameters()):
         torch.testing.assert_close(q.grad, p.grad, rtol=5e-3, atol=5e-5, msg=n)
+
+
+@pytest.mark.parametrize("shape", [(64, 48), (32, 16, 8, 8), (5, 3, 4, 4)])
+def test_kernel_batchnorm_matches_torch(cuda_lib, shape):
+    torch.manual_seed(0)
+    C = shape[1]
+    Mod = torch.nn.BatchNorm1d if len(shape) == 2 else torch.nn.BatchNorm2d
+    a, b = Mod(C).to(DEV), Mod(C).to(DEV)
+    with torch.no_grad():
+        a.weight.uniform_(0.5, 1.5); a.bias.normal_()
+        b.load_state_dict(a.state_dict())
+    for step in range(2):
+        x = torch.randn(*shape, device=DEV) * 2 + 1
+        xa, xb = x.clone().requires_grad_(), x.clone().requires_grad_()
+        ya = a(xa); (ya * ya.detach().sign()).sum().backward()
+        yb = knn.kernel_batch_norm(xb, b); (yb * yb.detach().sign()).sum().backward()
+        torch.testing.assert_close(yb, ya, rtol=1e-4, atol=1e-5)
+        torch.testing.assert_close(xb.grad, xa.grad, rtol=1e-3, atol=1e-5)
+        torch.testing.assert_close(b.weight.grad, a.weight.grad, rtol=1e-3, atol=1e-4)
+        torch.testing.assert_close(b.bias.grad, a.bias.grad, rtol=1e-3, atol=1e-4)
+        torch.testing.assert_close(b.running_mean, a.running_mean, rtol=1e-4, atol=1e-6)
+        torch.testing.assert_close(b.running_var, a.running_var, rtol=1e-4, atol=1e-6)
+    a.eval(); b.eval()
+    x = torch.randn(*shape, device=DEV)
+    with torch.no_grad():
+        torch.testing.assert_close(knn.kernel_batch_norm(x, b), a(x), rtol=1e-4, atol=1e-5)
+
+
+@pytest.mark.parametrize("B,H,T,D", [(3, 6, 256, 48), (2, 2, 100, 32), (1, 4, 300, 64)])
+def test_kernel_causal_attention(cuda_lib, B, H, T, D):
+    torch.manual_seed(0)
+    q, k, v = (torch.randn(B, H, T, D, device=DEV, requires_grad=True) for _ in range(3))
+    ref = F.scaled_dot_product_attention(q.double(), k.double(), v.double(), is_causal=True)
+    w = torch.randn_like(ref)
+    (ref * w).sum().backward()
+    g = [t.grad.clone() for t in (q, k, v)]
+    for t in (q, k, v):
+        t.grad = None
+    out = knn.kernel_causal_attention(q, k, v)
+    (out * w.float()).sum().backward()
+    torch.testing.assert_close(out.double(), ref, rtol=1e-4, atol=1e-5)
+    for t, gg in zip((q, k, v), g):
+        torch.testing.assert_close(t.grad.double(), gg.double(), rtol=1e-3, atol=2e-5)
