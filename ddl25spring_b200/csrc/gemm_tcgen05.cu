@@ -261,8 +261,11 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
     // Transpose each 32x32 accumulator chunk through a per-warp shared-memory tile (the operand ring is
     // idle by now) so that every global access of the warp is one contiguous 128-byte row segment:
     // lane = column.  The C reads of the beta path are issued as a batch before they are consumed.
-    float* wsm = reinterpret_cast<float*>(stage_base) + (warp - 2) * (32 * 33);
+    constexpr int WP = 36;                                   // tile pitch in floats: 16-byte rows, conflict-free for float4
+    float* wsm = reinterpret_cast<float*>(stage_base) + (warp - 2) * (32 * WP);
     const int mrow0 = m0 + quarter * 32;
+    const bool vec_ok = (ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(Cg) & 15) == 0) && (N % 4 == 0);
+    const int lr = lane >> 3, lc = (lane & 7) * 4;           // this lane's row-in-group / first column in the read-back phase
 #pragma unroll 1
     for (int c0 = 0; c0 < BN; c0 += 32) {
       if (n0 + c0 >= N) break;
@@ -274,24 +277,53 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
         for (int i = 0; i < 32; ++i) v[i] = 0.f;
       }
 #pragma unroll
-      for (int i = 0; i < 32; ++i) wsm[lane * 33 + i] = v[i] * epi.alpha;
+      for (int i = 0; i < 32; i += 4)
+        *reinterpret_cast<float4*>(wsm + lane * WP + i) =
+            make_float4(v[i] * epi.alpha, v[i + 1] * epi.alpha, v[i + 2] * epi.alpha, v[i + 3] * epi.alpha);
       __syncwarp();
-      const int n = n0 + c0 + lane;
-      const bool ncol_ok = n < N;
-      const float bn = (bias && ncol_ok) ? bias[n] : 0.f;
-      float* cbase = Cg + (int64_t)mrow0 * ldc + n;
-      if (direct && epi.beta != 0.f) {
+      const int n = n0 + c0 + lc;
+      if (vec_ok) {
+        // 8 steps; each warp instruction touches 4 rows x 128 contiguous bytes
+        const bool nok = n < N;
+        float4 bn4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (bias && nok) bn4 = *reinterpret_cast<const float4*>(bias + n);
+        float4 old[8];
+        if (direct && epi.beta != 0.f) {
 #pragma unroll
-        for (int rr = 0; rr < 32; ++rr) v[rr] = (ncol_ok && mrow0 + rr < M) ? cbase[(int64_t)rr * ldc] : 0.f;
-      }
-#pragma unroll
-      for (int rr = 0; rr < 32; ++rr) {
-        float x = wsm[rr * 33 + lane];
-        if (direct) {
-          if (epi.beta != 0.f) x = fmaf(epi.beta, v[rr], x);
-          x = apply_act(x + bn, epi.act, epi.slope);
+          for (int it = 0; it < 8; ++it) {
+            const int m = mrow0 + it * 4 + lr;
+            old[it] = (nok && m < M) ? *reinterpret_cast<const float4*>(Cg + (int64_t)m * ldc + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
         }
-        if (ncol_ok && mrow0 + rr < M) cbase[(int64_t)rr * ldc] = x;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const int r = it * 4 + lr, m = mrow0 + r;
+          float4 x = *reinterpret_cast<const float4*>(wsm + r * WP + lc);
+          if (direct) {
+            if (epi.beta != 0.f) {
+              x.x = fmaf(epi.beta, old[it].x, x.x); x.y = fmaf(epi.beta, old[it].y, x.y);
+              x.z = fmaf(epi.beta, old[it].z, x.z); x.w = fmaf(epi.beta, old[it].w, x.w);
+            }
+            x.x = apply_act(x.x + bn4.x, epi.act, epi.slope); x.y = apply_act(x.y + bn4.y, epi.act, epi.slope);
+            x.z = apply_act(x.z + bn4.z, epi.act, epi.slope); x.w = apply_act(x.w + bn4.w, epi.act, epi.slope);
+          }
+          if (nok && m < M) *reinterpret_cast<float4*>(Cg + (int64_t)m * ldc + n) = x;
+        }
+      } else {
+        // unaligned output: lane = column, one row per step
+        const int nn = n0 + c0 + lane;
+        const bool ncol_ok = nn < N;
+        const float bn = (bias && ncol_ok) ? bias[nn] : 0.f;
+        float* cbase = Cg + (int64_t)mrow0 * ldc + nn;
+#pragma unroll 4
+        for (int rr = 0; rr < 32; ++rr) {
+          float x = wsm[rr * WP + lane];
+          if (direct) {
+            if (epi.beta != 0.f && ncol_ok && mrow0 + rr < M) x = fmaf(epi.beta, cbase[(int64_t)rr * ldc], x);
+            x = apply_act(x + bn, epi.act, epi.slope);
+          }
+          if (ncol_ok && mrow0 + rr < M) cbase[(int64_t)rr * ldc] = x;
+        }
       }
       __syncwarp();
     }
