@@ -63,6 +63,11 @@ struct GatherMaps {
   int kb_start[kMaxParts + 1];   // first k-block of part p (prefix sums of ceil(dims[p] / 32))
   int col_off[kMaxParts];        // column of W where part p's slab starts
   int n_parts;
+  // row mode (K3 fused all-gather + Gram): the parts are ROW blocks of one tall operand U = [part 0 rows; part 1 rows; ...]
+  // living on different GPUs; every k-block stages `rows_per_part` rows from each GPU into consecutive shared-memory rows
+  // and the tile is used as BOTH operands (SYRK), so U U^T is accumulated without U ever being gathered in HBM.
+  int row_mode;
+  int rows_per_part;
 };
 
 template <int BN, int EB /*element bytes*/, bool SPLIT3>
@@ -105,7 +110,7 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
   const int n_split = epi.n_split > 1 ? epi.n_split : 1;
   const int g = blockIdx.z / n_split;
   const int split = blockIdx.z % n_split;
-  const int total_kblocks = GATHER ? gm->kb_start[gm->n_parts] : (K + BK - 1) / BK;
+  const int total_kblocks = GATHER ? (gm->row_mode ? (K + BK - 1) / BK : gm->kb_start[gm->n_parts]) : (K + BK - 1) / BK;
   const int kb_begin = split * kblocks_per_split;
   int kb_end = kb_begin + kblocks_per_split;
   if (kb_end > total_kblocks) kb_end = total_kblocks;
@@ -139,6 +144,16 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
         mbar_wait(&empty_bar[s], phase ^ 1);
         uint8_t* a_dst = stage_base + s * Plan::STAGE_BYTES;
         uint8_t* b_dst = a_dst + Plan::A_BYTES;
+        if (GATHER && gm->row_mode) {
+          const int gkb = kb_begin + kb;
+          const uint32_t part_bytes = (uint32_t)gm->rows_per_part * ROW_BYTES;
+          mbar_arrive_expect_tx(&full_bar[s], part_bytes * gm->n_parts);
+#pragma unroll
+          for (int p = 0; p < kMaxParts; ++p)
+            if (p < gm->n_parts) tma_load_3d(a_dst + p * part_bytes, &gm->maps[p], &full_bar[s], gkb * BK, 0, 0);
+          if (++s == STAGES) { s = 0; phase ^= 1; }
+          continue;
+        }
         mbar_arrive_expect_tx(&full_bar[s], epi.same_ab ? Plan::A_BYTES : Plan::A_BYTES + Plan::B_BYTES);
         if constexpr (GATHER) {
           const int gkb = kb_begin + kb;
@@ -346,8 +361,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
 template <int BN, bool SPLIT3>
 __global__ void __launch_bounds__(kThreads, 1)
 gather_gemm_tcgen05_kernel(const __grid_constant__ GatherMaps gm, const __grid_constant__ CUtensorMap tma_b,
-                           const Epilogue epi, const int M, const int N, const int kblocks_per_split) {
-  gemm_tcgen05_body<BN, 4, false, false, SPLIT3, true>(tma_b, tma_b, &gm, epi, M, N, 0, kblocks_per_split);
+                           const Epilogue epi, const int M, const int N, const int K, const int kblocks_per_split) {
+  gemm_tcgen05_body<BN, 4, false, false, SPLIT3, true>(tma_b, tma_b, &gm, epi, M, N, K, kblocks_per_split);
 }
 
 // Sum split-K partial tiles in split order, add bias, apply activation.
@@ -495,6 +510,8 @@ int ddl_gather_gemm_tcgen05(const float* const* parts, const int* part_dims, con
   DDL_REQUIRE(M > 0 && N > 0, "empty GEMM");
   GatherMaps gm;
   gm.n_parts = n_parts;
+  gm.row_mode = 0;
+  gm.rows_per_part = 0;
   int kb = 0, col = 0;
   for (int p = 0; p < n_parts; ++p) {
     DDL_REQUIRE(part_dims[p] > 0 && (part_lds[p] * 4) % 16 == 0 && (reinterpret_cast<uintptr_t>(parts[p]) & 15) == 0,
@@ -533,7 +550,7 @@ int ddl_gather_gemm_tcgen05(const float* const* parts, const int* part_dims, con
     auto kern = gather_gemm_tcgen05_kernel<BN_, P_>;                                                           \
     using Plan = SmemPlan<BN_, 4, P_>;                                                                         \
     DDL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Plan::TOTAL));      \
-    kern<<<grid, kThreads, Plan::TOTAL, st>>>(gm, tb, epi, M, N, kbps);                                        \
+    kern<<<grid, kThreads, Plan::TOTAL, st>>>(gm, tb, epi, M, N, 0, kbps);                                     \
   }
   if (BN == 32) { if (precise) DDL_GATHER_CASE(32, true) else DDL_GATHER_CASE(32, false) }
   else if (BN == 64) { if (precise) DDL_GATHER_CASE(64, true) else DDL_GATHER_CASE(64, false) }
@@ -545,6 +562,59 @@ int ddl_gather_gemm_tcgen05(const float* const* parts, const int* part_dims, con
     int64_t blocks = (ge + 255) / 256;
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
     splitk_reduce_kernel<<<(int)blocks, 256, 0, st>>>(scratch, n_split, ge, 1, N, C, ldc, 0, bias, 0, act, slope);
+    DDL_LAUNCH_CHECK();
+  }
+  return DDL_OK;
+}
+
+// K3 fused: G = U U^T where the rows of U live on different GPUs (rows_per_part consecutive rows each, row stride ld) and only
+// the coordinate slice [d0, d1) is reduced here (every GPU owns one slice; the K x K partials are summed afterwards).
+int ddl_gram_rowgather_tcgen05(const float* const* part_ptrs, int n_parts, int rows_per_part, int64_t ld, int64_t d0, int64_t d1,
+                               float* gram, int64_t ldg, int precise, int n_split, float* scratch, void* stream) {
+  DDL_REQUIRE(n_parts >= 1 && n_parts <= kMaxParts, "n_parts=%d outside [1, %d]", n_parts, kMaxParts);
+  DDL_REQUIRE(rows_per_part >= 8 && rows_per_part % 8 == 0, "rows_per_part=%d must be a multiple of 8 (1024-byte swizzle atoms)", rows_per_part);
+  const int Kc = n_parts * rows_per_part;                      // clients = rows of U
+  DDL_REQUIRE(Kc <= BM, "at most %d rows in total", BM);
+  DDL_REQUIRE(d0 % 4 == 0 && d1 > d0 && (ld * 4) % 16 == 0, "coordinate slice must start on a float4 boundary");
+  const int Kdim = (int)(d1 - d0);
+  GatherMaps gm;
+  gm.n_parts = n_parts; gm.row_mode = 1; gm.rows_per_part = rows_per_part;
+  for (int p = 0; p <= kMaxParts; ++p) gm.kb_start[p] = 0;
+  for (int p = 0; p < kMaxParts; ++p) gm.col_off[p] = 0;
+  const int kd4 = (Kdim + 3) / 4 * 4;
+  for (int p = 0; p < n_parts; ++p) {
+    OperandDesc od{part_ptrs[p] + d0, rows_per_part, ld, 0, 0};
+    if (int e = make_operand_map(&gm.maps[p], od, kd4, 1, rows_per_part, 4)) return e;
+  }
+  const int total_kb = (Kdim + 31) / 32;
+  if (n_split < 1) n_split = 1;
+  if (n_split > total_kb) n_split = total_kb;
+  DDL_REQUIRE(n_split == 1 || scratch != nullptr, "split-K needs scratch of n_split * K * K floats");
+  const int kbps = (total_kb + n_split - 1) / n_split;
+  n_split = (total_kb + kbps - 1) / kbps;
+  const int BN = Kc <= 32 ? 32 : (Kc <= 64 ? 64 : 128);
+  Epilogue epi;
+  epi.C = n_split > 1 ? scratch : gram;
+  epi.ldc = ldg; epi.c_group_stride = 0; epi.bias = nullptr; epi.bias_group_stride = 0;
+  epi.act = 0; epi.slope = 0.f; epi.alpha = 1.f; epi.beta = 0.f; epi.n_split = n_split; epi.same_ab = 1;
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid(1, 1, n_split);
+#define DDL_ROWG_CASE2(BN_, P_)                                                                                \
+  {                                                                                                            \
+    auto kern = gather_gemm_tcgen05_kernel<BN_, P_>;                                                           \
+    using Plan = SmemPlan<BN_, 4, P_>;                                                                         \
+    DDL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Plan::TOTAL));      \
+    kern<<<grid, kThreads, Plan::TOTAL, st>>>(gm, gm.maps[0], epi, Kc, Kc, Kdim, kbps);                        \
+  }
+#define DDL_ROWG_CASE(BN_) { if (precise) DDL_ROWG_CASE2(BN_, true) else DDL_ROWG_CASE2(BN_, false) }
+  if (BN == 32) DDL_ROWG_CASE(32) else if (BN == 64) DDL_ROWG_CASE(64) else DDL_ROWG_CASE(128)
+#undef DDL_ROWG_CASE
+#undef DDL_ROWG_CASE2
+  DDL_LAUNCH_CHECK();
+  if (n_split > 1) {
+    const int64_t ge = (int64_t)Kc * Kc;
+    int64_t blocks = (ge + 255) / 256;
+    splitk_reduce_kernel<<<(int)blocks, 256, 0, st>>>(scratch, n_split, ge, 1, Kc, gram, ldg, 0, nullptr, 0, 0, 0.f);
     DDL_LAUNCH_CHECK();
   }
   return DDL_OK;

@@ -77,8 +77,11 @@ class Krum(Aggregator):
     """
     name = "krum"
 
-    def __init__(self, n_byzantine: int, multi: int = 1, precise: bool = False, score_dims: int | None = None):
+    def __init__(self, n_byzantine: int, multi: int = 1, precise: bool = False, score_dims: int | None = None,
+                 fused_gather: bool = False):
         self.f, self.multi, self.precise, self.score_dims = n_byzantine, multi, precise, score_dims
+        # multi-GPU only: one kernel does the all-gather of the updates AND the Gram GEMM (TMA k-blocks from peer HBM)
+        self.fused_gather = fused_gather
         self.last_selected: torch.Tensor | None = None
         self.last_scores: torch.Tensor | None = None
 

@@ -138,3 +138,20 @@ def gather_linear_ptrs(part_ptrs, part_dims, part_lds, M: int, w: torch.Tensor, 
                                             int(N), int(precise), 1, _lib.p(None), _lib.stream())
     _lib.check(rc, "ddl_gather_gemm_tcgen05")
     return out
+
+
+def gram_rowgather_ptrs(part_ptrs, rows_per_part: int, ld: int, d0: int, d1: int, out: torch.Tensor, n_split: int = 148,
+                        precise: bool = True):
+    """K3 fused all-gather + Gram: ``out = U[:, d0:d1] @ U[:, d0:d1].T`` with the rows of ``U`` on different GPUs
+    (``part_ptrs[p]`` = device pointer, possibly peer-mapped, of GPU p's ``rows_per_part`` rows).  Row order p-major."""
+    Kc = len(part_ptrs) * rows_per_part
+    kb = (d1 - d0 + 31) // 32
+    if precise:
+        n_split = max(n_split, -(-(d1 - d0) // PRECISE_CHAIN))
+    n_split = max(1, min(n_split, kb))
+    scratch = torch.empty(n_split * Kc * Kc, device=out.device, dtype=torch.float32) if n_split > 1 else None
+    rc = _lib.lib().ddl_gram_rowgather_tcgen05(_lib.host_ptrs(part_ptrs), len(part_ptrs), int(rows_per_part), _lib.i64(ld), _lib.i64(d0),
+                                               _lib.i64(d1), _lib.p(out), _lib.i64(out.stride(0)), int(precise), int(n_split),
+                                               _lib.p(scratch), _lib.stream())
+    _lib.check(rc, "ddl_gram_rowgather_tcgen05")
+    return out

@@ -179,14 +179,27 @@ class SymmetricAggregator:
                 self._gpart = a.alloc(f"gram_part_{K}", K * K * 4).view(K, K)
                 self._gsum = a.alloc(f"gram_sum_{K}", K * K * 4).view(K, K)
                 self._gpart_ptrs, self._gsum_ptrs = a.peer_ptrs(f"gram_part_{K}"), a.peer_ptrs(f"gram_sum_{K}")
-            a.reduce(2, ptrs, w, [U.data_ptr()], d0, d1, base=gflat.detach(), rank_lo=pad // 4)
-            gram_tcgen05(U, out=self._gpart, precise=aggregator.precise)
+            rows_per_rank = K // world
+            if getattr(aggregator, "fused_gather", False) and K == rows_per_rank * world and rows_per_rank % 8 == 0:
+                # ONE kernel: every k-block of U is TMA-loaded from the owning GPUs and used as both MMA operands (3xTF32,
+                # because raw weights cannot be shifted to small-norm deltas in flight); result rows are rank-major.
+                from ..ops.gemm import gram_rowgather_ptrs
+                g0, g1 = shard_bounds(self.P, world, a.rank, align=32)
+                a.barrier()
+                gram_rowgather_ptrs(self.row_ptrs, rows_per_rank, self.P, g0, g1, self._gpart, precise=True)
+                order = torch.tensor([(k % world) * rows_per_rank + k // world for k in range(K)], device="cuda")
+            else:
+                order = None
+                a.reduce(2, ptrs, w, [U.data_ptr()], d0, d1, base=gflat.detach(), rank_lo=pad // 4)
+                gram_tcgen05(U, out=self._gpart, precise=aggregator.precise)
             if (K * K) % 4 == 0:
                 a.reduce(0, self._gpart_ptrs, [1.0] * world, self._gsum_ptrs, 0, K * K)
                 G = self._gsum
             else:                                                 # odd K: K*K is not float4-divisible
                 dist.all_reduce(self._gpart)
                 G = self._gpart
+            if order is not None:
+                G = G[order][:, order].contiguous()                # back to client order
             sel, selw, scores = ops.krum_select(U, aggregator.f, aggregator.multi, gram_matrix=G)
             aggregator.last_selected, aggregator.last_scores = sel, scores
             # selection weights live on the device; every rank reduces its shard of the selected rows

@@ -217,6 +217,15 @@ int ddl_causal_attention_fwd(const float* q, const float* k, const float* v, flo
 int ddl_causal_attention_bwd(const float* q, const float* k, const float* v, const float* o, const float* dO, const float* lse,
                              float* dq, float* dk, float* dv, float* delta_scratch, int BH, int T, int D, float scale, void* stream);
 
+/* ---- K3 fused: all-gather of client updates + Gram GEMM in one kernel [north star] --------------------------------------
+ * gram[K x K] = U[:, d0:d1] U[:, d0:d1]^T with K = n_parts * rows_per_part and the rows of U spread over GPUs: part_ptrs[p]
+ * (HOST array of device pointers, may be peer-mapped) is the base of GPU p's rows_per_part rows (row stride ld floats).
+ * Every k-block is TMA-loaded straight from the owning GPUs into one shared-memory tile that serves as both MMA operands.
+ * Row order of the result: p * rows_per_part + i.  rows_per_part % 8 == 0, K <= 128; split-K scratch: n_split*K*K floats.
+ * precise != 0 (3xTF32) is recommended: raw weights cannot be shifted to small-norm deltas in flight. */
+int ddl_gram_rowgather_tcgen05(const float* const* part_ptrs, int n_parts, int rows_per_part, int64_t ld, int64_t d0, int64_t d1,
+                               float* gram, int64_t ldg, int precise, int n_split, float* scratch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -204,3 +204,61 @@ def test_generic_server_fused_equals_nccl_path(agg_name, with_bn):
     for o in outs:
         assert torch.isfinite(o["fused"][0]).all()
         torch.testing.assert_close(o["fused"][0], o["nccl"][0], rtol=1e-4, atol=1e-5)
+
+
+def _rowgather_worker(rank, world):
+    import torch.distributed as dist
+    from ddl25spring_b200.ops.gemm import gram_rowgather_ptrs
+    from ddl25spring_b200.parallel.symm_impl import SymmetricArena, shard_bounds
+    a = SymmetricArena()
+    G, n = 8, 200_000
+    rows = a.alloc("rows", G * n * 4).view(G, n)
+    g = torch.Generator(device="cuda").manual_seed(7 + rank)
+    rows.copy_(0.5 + 0.01 * torch.randn(G, n, generator=g, device="cuda"))      # large common offset: the hard case for TF32
+    allrows = [torch.empty(G, n, device="cuda") for _ in range(world)]
+    dist.all_gather(allrows, rows.contiguous())
+    U = torch.cat(allrows).double()                                            # p-major row order
+    d0, d1 = shard_bounds(n, world, rank, align=32)
+    out = torch.empty(G * world, G * world, device="cuda")
+    a.barrier()
+    gram_rowgather_ptrs(a.peer_ptrs("rows"), G, n, d0, d1, out, precise=True)
+    a.barrier()
+    torch.cuda.synchronize(); a.check()
+    exp = U[:, d0:d1] @ U[:, d0:d1].T
+    return float((out.double() - exp).abs().max() / exp.abs().max())
+
+
+@pytest.mark.timeout(300)
+def test_fused_allgather_gram_over_peers():
+    world = min(torch.cuda.device_count(), 8)
+    errs = run_distributed(_rowgather_worker, world, timeout=240, backend="nccl")
+    assert max(errs) < 5e-5, errs
+
+
+def _krum_fused_gather_worker(rank, world):
+    from ddl25spring_b200.core.data import SyntheticMNIST, split
+    from ddl25spring_b200.fl.aggregators import Krum
+    from ddl25spring_b200.fl.packed_server import PackedFedAvgServer
+    from ddl25spring_b200.parallel.symm import make_collective
+    K = 8 * world
+    ds = SyntheticMNIST(n_train=K * 100, n_test=200, seed=2, noise=0.8)
+    subsets = split(ds.train, K, True, 3)
+    sel = {}
+    coll = make_collective()
+    for name, fg in (("fused_gather", True), ("delta_path", False)):
+        agg = Krum(n_byzantine=2, multi=K - 4, fused_gather=fg)
+        srv = PackedFedAvgServer(0.05, 50, subsets, 1.0, 1, 3, test_set=ds.test, device="cuda", p_drop1=0.0, p_drop2=0.0,
+                                 aggregator=agg, collective=coll)
+        srv.run(1)
+        torch.cuda.synchronize()
+        sel[name] = (sorted(agg.last_selected.cpu().tolist()), srv.arena.flat.clone().cpu())
+    return sel
+
+
+@pytest.mark.timeout(400)
+def test_krum_fused_allgather_gram_selects_like_delta_path():
+    world = min(torch.cuda.device_count(), 8)
+    outs = run_distributed(_krum_fused_gather_worker, world, timeout=300, backend="nccl")
+    for o in outs:
+        assert o["fused_gather"][0] == o["delta_path"][0]
+        torch.testing.assert_close(o["fused_gather"][1], o["delta_path"][1], rtol=1e-5, atol=1e-6)
