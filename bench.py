@@ -104,7 +104,7 @@ def run_reference_arm(args):
 
 
 # ----------------------------------------------------------------------------------------- product arm
-def build_server(n_gpus: int, data_on_device: bool, aggregator: str, dataset):
+def build_server(n_gpus: int, data_on_device: bool, aggregator: str, dataset, prefetch: bool = True):
     from ddl25spring_b200.core.data import split
     from ddl25spring_b200.fl.aggregators import make_aggregator
     from ddl25spring_b200.fl.packed_server import PackedFedAvgServer
@@ -116,7 +116,7 @@ def build_server(n_gpus: int, data_on_device: bool, aggregator: str, dataset):
         kw = dict(n_byzantine=max(1, int(0.2 * CLIENTS_PER_GPU * n_gpus)))
     return PackedFedAvgServer(LR, BATCH, subsets, CLIENTS_PER_GPU * n_gpus / NR_CLIENTS, EPOCHS, SEED,
                               test_set=dataset.test, device="cuda", aggregator=make_aggregator(aggregator, **kw),
-                              data_on_device=data_on_device, collective=make_collective())
+                              data_on_device=data_on_device, collective=make_collective(), prefetch_next=prefetch)
 
 
 def timed_rounds(server, steps: int, warmup: int, device, flusher, sampler=None):
@@ -175,7 +175,8 @@ def run_ours(args):
 
     # ---- end-to-end number through the public API: shards in pinned host memory, copied H2D every round,
     #      accuracy read back D2H every round
-    server = build_server(n_gpus, False, args.aggregator, dataset)
+    # (no cross-round prefetch here: every round's own H2D copy and D2H read are inside that round's timed region)
+    server = build_server(n_gpus, False, args.aggregator, dataset, prefetch=False)
     e2e_ms, _ = timed_rounds(server, args.steps, args.warmup, device, flusher)
     h2d = server.h2d_bytes_last_round
     del server

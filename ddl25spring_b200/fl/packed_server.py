@@ -32,13 +32,22 @@ from .packed import MAX_G, P, PackedMnistEngine
 from .server import _RoundTimer, _dist_ready
 
 
+class _NullCtx:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
 class PackedFedAvgServer:
     algorithm = "FedAvg"
 
     def __init__(self, lr: float, batch_size: int, client_subsets, client_fraction: float, nr_local_epochs: int,
                  seed: int, *, test_set=None, device="cuda", aggregator: Aggregator | None = None, attack=None,
                  malicious: np.ndarray | None = None, data_on_device: bool = True, p_drop1: float = 0.25,
-                 p_drop2: float = 0.5, eval_chunk: int = 2048, collective=None) -> None:
+                 p_drop2: float = 0.5, eval_chunk: int = 2048, collective=None, prefetch_next: bool = True) -> None:
+        self.prefetch_next = prefetch_next
         self.lr, self.batch_size, self.seed = lr, batch_size, seed
         self.nr_local_epochs = nr_local_epochs
         self.device = torch.device(device)
@@ -83,6 +92,10 @@ class PackedFedAvgServer:
             self.set_test_data(test_set)
         self.clients = list(range(self.nr_clients))    # ids; data lives in X_all / Y_all
         self._agg_out = torch.empty(P, device=self.device)
+        self._copy_stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" else None
+        self._slot_free = [None, None]
+        self._next_slot = 0
+        self._prefetch = None            # (chosen, staged) of the round that will run next
 
     # ------------------------------------------------------------------ evaluation
     def set_test_data(self, test_set) -> None:
@@ -112,38 +125,68 @@ class PackedFedAvgServer:
         if G not in self._engines:
             self._engines[G] = PackedMnistEngine(G, self.batch_size, device=self.device, p_drop1=self.p1, p_drop2=self.p2)
             w_rows = self.collective.row_buffer(G) if self.collective is not None else torch.empty(G, P, device=self.device)
-            self._bufs[G] = (w_rows,
-                             torch.zeros(G, self.n_max, 784, device=self.device),
-                             torch.zeros(G, self.n_max, dtype=torch.int64, device=self.device),
-                             torch.zeros(G, self.nr_local_epochs * self.n_max, dtype=torch.int32).pin_memory()
-                             if self.device.type == "cuda" else torch.zeros(G, self.nr_local_epochs * self.n_max, dtype=torch.int32),
-                             torch.zeros(G, self.nr_local_epochs * self.n_max, dtype=torch.int32, device=self.device))
+            cuda = self.device.type == "cuda"
+            n_perm = self.nr_local_epochs * self.n_max
+
+            def staging():
+                ph = torch.zeros(G, n_perm, dtype=torch.int32)
+                return (torch.zeros(G, self.n_max, 784, device=self.device),
+                        torch.zeros(G, self.n_max, dtype=torch.int64, device=self.device),
+                        ph.pin_memory() if cuda else ph,
+                        torch.zeros(G, n_perm, dtype=torch.int32, device=self.device))
+            # two staging sets: while round r trains out of one, round r+1's shards / permutations are staged into the other
+            self._bufs[G] = (w_rows, [staging(), staging()])
         return self._engines[G]
 
-    def _train_local_clients(self, nr_round: int, mine: list[int]):
-        """Train this rank's clients of the round; returns their ``[G, P]`` weight rows."""
+    def _stage(self, nr_round: int, mine: list[int], slot: int):
+        """Host permutations + data movement for one round into staging set ``slot`` (on the copy stream on GPU)."""
         G = len(mine)
-        eng = self._engine(G)
-        W, Xg, Yg, perm_host, perm_dev = self._bufs[G]
-        gflat = self.arena.flat.detach()
-        W.copy_(gflat.unsqueeze(0).expand(G, P))                 # server -> clients broadcast (hfl_complete.py:356)
+        self._engine(G)
+        Xg, Yg, perm_host, perm_dev = self._bufs[G][1][slot]
         counts = [self.client_sample_counts[c] for c in mine]
-        self.h2d_bytes_last_round = 0
+        h2d = 0
         for i, c in enumerate(mine):
             seed = client_round_seed(self.seed, c, nr_round, self.nr_clients_per_round)
             for e, pm in enumerate(epoch_permutations(counts[i], seed, self.nr_local_epochs)):
                 perm_host[i, e * self.n_max:e * self.n_max + counts[i]] = pm.to(torch.int32)
-            if self.data_on_device:
-                Xg[i].copy_(self.X_all[c])
-                Yg[i].copy_(self.Y_all[c])
-            else:
-                Xg[i].copy_(self.X_all[c], non_blocking=True)    # pinned host -> device
+        cuda = self.device.type == "cuda"
+        ctx = torch.cuda.stream(self._copy_stream) if cuda else _NullCtx()
+        if cuda and self._slot_free[slot] is not None:
+            self._copy_stream.wait_event(self._slot_free[slot])     # the round that last trained out of this set is done
+        with ctx:
+            for i, c in enumerate(mine):
+                Xg[i].copy_(self.X_all[c], non_blocking=True)        # pinned host -> device in the end-to-end mode
                 Yg[i].copy_(self.Y_all[c], non_blocking=True)
-                self.h2d_bytes_last_round += self.X_all[c].numel() * 4 + self.Y_all[c].numel() * 8
-        perm_dev.copy_(perm_host, non_blocking=True)
-        self.h2d_bytes_last_round += perm_host.numel() * 4
-        eng.local_train(W, Xg, Yg, perm_dev, counts, self.batch_size, self.nr_local_epochs, self.lr,
+                if not self.data_on_device:
+                    h2d += self.X_all[c].numel() * 4 + self.Y_all[c].numel() * 8
+            perm_dev.copy_(perm_host, non_blocking=True)
+            h2d += perm_host.numel() * 4
+            ready = None
+            if cuda:
+                ready = torch.cuda.Event()
+                ready.record(self._copy_stream)
+        return {"round": nr_round, "mine": list(mine), "slot": slot, "ready": ready, "h2d": h2d, "counts": counts}
+
+    def _train_local_clients(self, nr_round: int, mine: list[int], staged=None):
+        """Train this rank's clients of the round; returns their ``[G, P]`` weight rows."""
+        G = len(mine)
+        eng = self._engine(G)
+        if staged is None or staged["round"] != nr_round or staged["mine"] != list(mine):
+            staged = self._stage(nr_round, mine, self._next_slot)
+            self._next_slot ^= 1
+        W = self._bufs[G][0]
+        Xg, Yg, _perm_host, perm_dev = self._bufs[G][1][staged["slot"]]
+        gflat = self.arena.flat.detach()
+        W.copy_(gflat.unsqueeze(0).expand(G, P))                 # server -> clients broadcast (hfl_complete.py:356)
+        self.h2d_bytes_last_round = staged["h2d"]
+        if staged["ready"] is not None:
+            torch.cuda.current_stream().wait_event(staged["ready"])
+        eng.local_train(W, Xg, Yg, perm_dev, staged["counts"], self.batch_size, self.nr_local_epochs, self.lr,
                         seed=self.seed * 1_000_003 + nr_round)
+        if self.device.type == "cuda":
+            ev = torch.cuda.Event()
+            ev.record()
+            self._slot_free[staged["slot"]] = ev
         if self.attack is not None:
             for i, c in enumerate(mine):
                 if self.malicious[c]:
@@ -185,15 +228,31 @@ class PackedFedAvgServer:
         for nr_round in range(nr_rounds):
             t0 = perf_counter()
             timer.start()
-            chosen = self.rng.choice(self.nr_clients, self.nr_clients_per_round, replace=False)
+            if self._prefetch is not None:
+                chosen, staged = self._prefetch                 # drawn (in rng order) and staged during the previous round
+                self._prefetch = None
+            else:
+                chosen, staged = self.rng.choice(self.nr_clients, self.nr_clients_per_round, replace=False), None
             counts = np.asarray([self.client_sample_counts[int(c)] for c in chosen], dtype=np.float64)
             weights = torch.tensor(counts / counts.sum(), dtype=torch.float32)
             mine_pos = [p for p in range(len(chosen)) if p % self.world == self.rank]
             mine = [int(chosen[p]) for p in mine_pos]
             W_local = None
-            for lo in range(0, len(mine), MAX_G):            # more clients than one engine group: chunk
-                assert lo == 0, "more than MAX_G clients per GPU per round: raise MAX_G or add ranks"
-                W_local = self._train_local_clients(nr_round, mine[lo:lo + MAX_G])
+            assert len(mine) <= MAX_G, "more than MAX_G clients per GPU per round: raise MAX_G or add ranks"
+            if mine:
+                W_local = self._train_local_clients(nr_round, mine, staged)
+            # While the GPU trains: draw the NEXT round's clients (same rng order as drawing them later) and stage their
+            # shards + permutations into the other staging set.  The next round is nr_round + 1 of this run(), or round 0
+            # of a following run() call; a wrong guess only costs a re-stage.
+            if self.prefetch_next:
+                nxt_round = nr_round + 1 if nr_round + 1 < nr_rounds else 0
+                nxt = self.rng.choice(self.nr_clients, self.nr_clients_per_round, replace=False)
+                nxt_mine = [int(nxt[p]) for p in range(len(nxt)) if p % self.world == self.rank]
+                st = None
+                if nxt_mine:
+                    st = self._stage(nxt_round, nxt_mine, self._next_slot)
+                    self._next_slot ^= 1
+                self._prefetch = (nxt, st)
             if W_local is None:
                 W_local = torch.empty(0, P, device=self.device)
             with torch.no_grad():
