@@ -21,12 +21,13 @@ namespace {
 using namespace mnist;
 
 constexpr int kHeadWarps = 8;
+constexpr int kHeadParts = 4;                         // CTAs per client (rows interleaved): a single CTA per client was latency-bound
 constexpr int kPartial = NCLS * FC1 + FC1 + NCLS;   // dW2 | db1 | db2 partial sums of one warp
 
 __global__ void __launch_bounds__(kHeadWarps * 32, 1)
 head_train_kernel(float* __restrict__ W, const float* __restrict__ h1, const int64_t* __restrict__ Y, int64_t y_client_stride,
                   const int* __restrict__ perm, int64_t perm_stride, int sample_off, float* __restrict__ dz1,
-                  float* __restrict__ loss_out, const StepInfo si) {
+                  float* __restrict__ part_out, const StepInfo si) {
   extern __shared__ float sm[];
   float* s_w2 = sm;                       // [10][128]
   float* s_b2 = s_w2 + NCLS * FC1;        // [10] (+6 pad)
@@ -50,7 +51,7 @@ head_train_kernel(float* __restrict__ W, const float* __restrict__ h1, const int
 #pragma unroll
     for (int jj = 0; jj < 4; ++jj) dw2[c][jj] = 0.f;
 
-  for (int b = warp; b < si.B; b += kHeadWarps) {
+  for (int b = blockIdx.y * kHeadWarps + warp; b < si.B; b += kHeadWarps * kHeadParts) {
     const int64_t row = (int64_t)g * si.B + b;
     float4* dz = reinterpret_cast<float4*>(dz1 + row * FC1) + lane;
     if (b >= n) {                      // rows beyond this client's minibatch must contribute nothing
@@ -113,18 +114,37 @@ head_train_kernel(float* __restrict__ W, const float* __restrict__ h1, const int
   if (lane < NCLS) part[NCLS * FC1 + FC1 + lane] = db2;
   if (lane == 0) s_loss[warp] = loss;
   __syncthreads();
+  // block partial -> global scratch [g][part][kPartial + 1]; head_apply_kernel sums the parts in a fixed order
+  float* gp = part_out + ((int64_t)g * kHeadParts + blockIdx.y) * (kPartial + 1);
   for (int i = threadIdx.x; i < kPartial; i += blockDim.x) {
     float s = 0.f;
 #pragma unroll
     for (int w = 0; w < kHeadWarps; ++w) s += s_part[w * kPartial + i];
-    float* dst = i < NCLS * FC1 ? Wg + OFF_F2W + i
-                                : (i < NCLS * FC1 + FC1 ? Wg + OFF_F1B + (i - NCLS * FC1) : Wg + OFF_F2B + (i - NCLS * FC1 - FC1));
-    *dst -= si.lr * s;
+    gp[i] = s;
   }
-  if (threadIdx.x == 0 && loss_out) {
+  if (threadIdx.x == 0) {
     float s = 0.f;
     for (int w = 0; w < kHeadWarps; ++w) s += s_loss[w];
-    loss_out[g] = s;
+    gp[kPartial] = s;
+  }
+}
+
+__global__ void __launch_bounds__(256) head_apply_kernel(float* __restrict__ W, const float* __restrict__ part, float* __restrict__ loss_out,
+                                                         float lr) {
+  const int g = blockIdx.x;
+  float* Wg = W + (int64_t)g * P;
+  const float* gp = part + (int64_t)g * kHeadParts * (kPartial + 1);
+  for (int i = threadIdx.x; i <= kPartial; i += blockDim.x) {
+    float s = 0.f;
+#pragma unroll
+    for (int q = 0; q < kHeadParts; ++q) s += gp[q * (kPartial + 1) + i];
+    if (i == kPartial) {
+      if (loss_out) loss_out[g] = s;
+      continue;
+    }
+    float* dst = i < NCLS * FC1 ? Wg + OFF_F2W + i
+                                : (i < NCLS * FC1 + FC1 ? Wg + OFF_F1B + (i - NCLS * FC1) : Wg + OFF_F2B + (i - NCLS * FC1 - FC1));
+    *dst -= lr * s;
   }
 }
 
@@ -162,9 +182,12 @@ __global__ void __launch_bounds__(256) head_eval_kernel(const float* __restrict_
 
 extern "C" {
 
+int ddl_mnist_head_scratch_floats(int G) { return G * kHeadParts * (kPartial + 1); }
+
 int ddl_mnist_head_train(float* W, const float* h1, const int64_t* Y, int64_t y_client_stride, const int* perm,
-                         int64_t perm_stride, int sample_off, float* dz1, float* loss_out, int G, int B,
+                         int64_t perm_stride, int sample_off, float* dz1, float* loss_out, float* scratch, int G, int B,
                          const int* bsz, float p_drop, uint32_t seed, float lr, void* stream) {
+  DDL_REQUIRE(scratch != nullptr, "head_train needs ddl_mnist_head_scratch_floats(G) floats of scratch");
   DDL_REQUIRE(G >= 1 && G <= MAX_G, "G=%d outside [1, %d]", G, MAX_G);
   DDL_REQUIRE(p_drop >= 0.f && p_drop < 1.f, "dropout probability must be in [0, 1)");
   StepInfo si = make_step(G, B, bsz, seed, 0.f, p_drop, lr);
@@ -174,8 +197,11 @@ int ddl_mnist_head_train(float* W, const float* h1, const int64_t* Y, int64_t y_
     DDL_CUDA_CHECK(cudaFuncSetAttribute(head_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  head_train_kernel<<<G, kHeadWarps * 32, smem, (cudaStream_t)stream>>>(W, h1, Y, y_client_stride, perm, perm_stride,
-                                                                        sample_off, dz1, loss_out, si);
+  dim3 grid(G, kHeadParts);
+  head_train_kernel<<<grid, kHeadWarps * 32, smem, (cudaStream_t)stream>>>(W, h1, Y, y_client_stride, perm, perm_stride,
+                                                                           sample_off, dz1, scratch, si);
+  DDL_LAUNCH_CHECK();
+  head_apply_kernel<<<G, 256, 0, (cudaStream_t)stream>>>(W, scratch, loss_out, lr);
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

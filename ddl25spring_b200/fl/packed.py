@@ -115,6 +115,7 @@ def _alloc_train_scratch(self) -> None:
         self.wg_part = torch.zeros(self.G * self.n_cta * 3 * 128 * 64, **f32)
         self.c2b_part = torch.zeros(self.G * self.B, 64, **f32)
         self.c1_part = torch.zeros(self.G * self.B, 320, **f32)
+        self.head_scratch = torch.zeros(int(self.L.ddl_mnist_head_scratch_floats(self.G)), **f32)
 
 
 def train_step(self, W, X, x_stride, Y, y_stride, perm, perm_stride, sample_off, bsz, lr: float, seed: int) -> None:
@@ -126,7 +127,7 @@ def train_step(self, W, X, x_stride, Y, y_stride, perm, perm_stride, sample_off,
     w1 = Wv[:, OFF["fc1.weight"]:OFF["fc1.weight"] + FC1 * FLAT].unflatten(1, (FC1, FLAT))
     self.forward_features(W, X, x_stride, perm, perm_stride, sample_off, bsz, True, seed)
     _lib.check(L.ddl_mnist_head_train(_lib.p(W), _lib.p(self.h1), _lib.p(Y), _lib.i64(y_stride), _lib.p(perm),
-                                      _lib.i64(perm_stride), int(sample_off), _lib.p(self.dz1), _lib.p(self.loss), G, B, cb,
+                                      _lib.i64(perm_stride), int(sample_off), _lib.p(self.dz1), _lib.p(self.loss), _lib.p(self.head_scratch), G, B, cb,
                                       _lib.f32(self.p2), int(seed) & 0xFFFFFFFF, _lib.f32(lr), st()), "head_train")
     # fc1 backward: dgrad first (reads the old weights), then wgrad with the SGD step fused in its epilogue
     gemm(self.dz1, w1, b_mn=True, precise=True, out=self.dpool)

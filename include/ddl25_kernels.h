@@ -125,8 +125,9 @@ int ddl_mnist_prep_conv2(const float* W, float* wt_fwd, float* wt_dgrad, int G, 
 /* K9 fprop on tcgen05: conv2 (implicit GEMM, TF32) + bias + ReLU + 2x2 max-pool (+ dropout) */
 int ddl_mnist_conv2_pool_fwd(const float* W, const float* wt_fwd, const float* a1, float* pooled, uint8_t* pmask,
                              int G, int B, const int* bsz, int train, float p_drop, uint32_t seed, void* stream);
+int ddl_mnist_head_scratch_floats(int G);
 int ddl_mnist_head_train(float* W, const float* h1, const int64_t* Y, int64_t y_client_stride, const int* perm,
-                         int64_t perm_stride, int sample_off, float* dz1, float* loss_out, int G, int B,
+                         int64_t perm_stride, int sample_off, float* dz1, float* loss_out, float* scratch, int G, int B,
                          const int* bsz, float p_drop, uint32_t seed, float lr, void* stream);
 int ddl_mnist_head_eval(const float* W, const float* h1, const int64_t* Y, int sample_off, int nrows, float* logits_out,
                         int* correct, void* stream);
