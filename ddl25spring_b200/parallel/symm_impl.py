@@ -120,8 +120,13 @@ class SymmetricAggregator:
     """Fused cross-GPU aggregation for the packed FedAvg server (weighted mean, median, trimmed mean; Krum
     gathers the rows it needs with peer copies and scores locally)."""
 
-    def __init__(self, arena: SymmetricArena | None = None, max_rows_per_rank: int = 16, row_elems: int = 1_200_000):
+    def __init__(self, arena: SymmetricArena | None = None, max_rows_per_rank: int = 16, row_elems: int = 1_200_000,
+                 use_nvls: bool = False):
         self.arena = arena or SymmetricArena()
+        self.nvls = None
+        if use_nvls:                       # in-switch reduction of the per-GPU partial sums (falls back when unsupported)
+            from .nvls import NvlsAllReduce
+            self.nvls = NvlsAllReduce.create(row_elems, self.arena)
         self.G, self.P = max_rows_per_rank, row_elems
         self.rows = self.arena.alloc("client_rows", self.G * self.P * 4).view(self.G, self.P)
         self.result = self.arena.alloc("agg_result", self.P * 4)
@@ -151,10 +156,15 @@ class SymmetricAggregator:
             # partial row per GPU crosses NVLink; the fused kernel then sums the W partials shard by shard.
             from .. import ops
             n_local = W_local.shape[0]
+            part = self.nvls.buf[:self.P] if self.nvls is not None else self.partial
             if n_local:
-                ops.weighted_sum(self.rows[:n_local], [w[p] for p in mine_pos], self.partial)
+                ops.weighted_sum(self.rows[:n_local], [w[p] for p in mine_pos], part)
             else:
-                self.partial.zero_()
+                part.zero_()
+            if self.nvls is not None:          # NVSwitch sums the W partials (multimem.ld_reduce) and multicasts the result
+                self.nvls.all_reduce_(0, self.P)
+                gflat.copy_(part)
+                return
             a.reduce(0, self.partial_ptrs, [1.0] * world, self.res_ptrs, d0, d1)
         elif isinstance(aggregator, (CoordinateMedian, TrimmedMean)) and K <= 64:
             if isinstance(aggregator, CoordinateMedian):

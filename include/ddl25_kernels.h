@@ -227,6 +227,12 @@ int ddl_causal_attention_bwd(const float* q, const float* k, const float* v, con
 int ddl_gram_rowgather_tcgen05(const float* const* part_ptrs, int n_parts, int rows_per_part, int64_t ld, int64_t d0, int64_t d1,
                                float* gram, int64_t ldg, int precise, int n_split, float* scratch, void* stream);
 
+/* ---- NVLS all-reduce: in-switch reduction through a multicast address (multimem.ld_reduce / multimem.st) -----------------
+ * (ref: gloo all_reduce, lab/tutorial_1b/DP/gradient_aggr/intro_DP_GA.py:63).  multicast_ptr addresses the same symmetric
+ * buffer on every GPU; this GPU reduces + re-broadcasts coordinates [d0, d1) (its shard), scaled by `scale`.  The caller
+ * orders the GPUs with barriers before (inputs written) and after (results visible). */
+int ddl_nvls_allreduce(float* multicast_ptr, int64_t d0, int64_t d1, float scale, int max_ctas, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

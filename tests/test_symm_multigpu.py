@@ -262,3 +262,47 @@ def test_krum_fused_allgather_gram_selects_like_delta_path():
     for o in outs:
         assert o["fused_gather"][0] == o["delta_path"][0]
         torch.testing.assert_close(o["fused_gather"][1], o["delta_path"][1], rtol=1e-5, atol=1e-6)
+
+
+def _nvls_worker(rank, world):
+    import torch.distributed as dist
+    from ddl25spring_b200.parallel.nvls import NvlsAllReduce
+    from ddl25spring_b200.parallel.symm_impl import SymmetricArena
+    arena = SymmetricArena()
+    n = 11_181_696
+    nv = NvlsAllReduce.create(n, arena)
+    if nv is None:
+        return {"supported": False}
+    g = torch.Generator(device="cuda").manual_seed(rank)
+    x = torch.randn(n, generator=g, device="cuda")
+    ref = x.clone()
+    dist.all_reduce(ref)
+    nv.buf[:n].copy_(x)
+    nv.all_reduce_(0, n)
+    torch.cuda.synchronize(); arena.check()
+    err = float((nv.buf[:n] - ref).abs().max())
+    out = {"supported": True, "err": err}
+    for name, fn in (("nvls", lambda: nv.all_reduce_(0, n)), ("nccl", lambda: dist.all_reduce(ref))):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize(); dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / 10], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out[name + "_ms"] = float(t)
+    return out
+
+
+@pytest.mark.timeout(300)
+def test_nvls_allreduce_matches_nccl():
+    world = min(torch.cuda.device_count(), 8)
+    outs = run_distributed(_nvls_worker, world, timeout=240, backend="nccl")
+    if not outs[0]["supported"]:
+        pytest.skip("multicast (NVLS) not available on this box")
+    for o in outs:
+        assert o["err"] < 1e-3, o
+    print("NVLS all-reduce 44.7 MB: ours %.3f ms, NCCL %.3f ms" % (outs[0]["nvls_ms"], outs[0]["nccl_ms"]))
