@@ -29,6 +29,7 @@ def lib() -> C.CDLL:
         _LIB.ddl_last_error.restype = C.c_char_p
         _LIB.ddl_arch.restype = C.c_char_p
         _LIB.ddl_launch_count.restype = C.c_int64
+        _LIB.ddl_bn_nhwc_ws_floats.restype = C.c_int64
     return _LIB
 
 

@@ -233,6 +233,42 @@ int ddl_gram_rowgather_tcgen05(const float* const* part_ptrs, int n_parts, int r
  * orders the GPUs with barriers before (inputs written) and after (results visible). */
 int ddl_nvls_allreduce(float* multicast_ptr, int64_t d0, int64_t d1, float scale, int max_ctas, void* stream);
 
+/* ---- K9 general: NHWC / OHWI convolutions as tap GEMMs on tcgen05 (csrc/conv_tcgen05.cu) -------------------------------
+ * (ref: nn.Conv2d via ATen/cuDNN, lab/tutorial_1a/hfl_complete.py:51,53; ResNet-18 / DCGAN convs of the north star.)
+ * A convolution is a list of taps; tap t reads activation map tap_map[t] (an NHWC tensor [N, Ha, Wa, Ca]) at spatial
+ * offset (tap_dh[t], tap_dw[t]) and multiplies by weight slice Wt[:, tap_w[t], :] of the OHWI weight [Cout, T, Cin].
+ * w_mn_major = 0: forward (reduce over Cin, produce Cout channels); 1: input gradient (reduce over Cout, produce Cin).
+ * Output pixel (n, i, j), n < N, i < Hh, j < Ww, is stored at out + o_off + n*o_sn + i*o_sh + j*o_sw (elements):
+ * out = act(alpha * conv + beta * out + bias).  act: 0 none, 1 relu, 2 leaky(slope), 3 tanh.
+ * Channel counts: multiples of 4, and of 32 when above 32.  scratch (optional) enables split-K on small grids. */
+int ddl_conv_tap_gemm(const float* const* acts, int n_maps, int N, int Ha, int Wa, int Ca, const float* Wt, int Cout, int T, int Cin,
+                      int w_mn_major, const int* tap_map, const int* tap_dh, const int* tap_dw, const int* tap_w, int n_taps,
+                      float* out, int Hh, int Ww, int64_t o_off, int64_t o_sn, int64_t o_sh, int64_t o_sw, const float* bias,
+                      float alpha, float beta, int act, float slope, float* scratch, int64_t scratch_floats, void* stream);
+/* dW[co, tap_w[t], ci] = alpha * sum_{n,i,j} dY[n,i,j,co] * X_{tap_map[t]}[n, i+dh, j+dw, ci] + beta * dW   (dY: [N,Ho,Wo,Cout]) */
+int ddl_conv_wgrad(const float* dY, int N, int Ho, int Wo, int Cout, const float* const* xs, int n_maps, int Hx, int Wx, int Cin,
+                   const int* tap_map, const int* tap_dh, const int* tap_dw, const int* tap_w, int n_taps, float* dW, int T,
+                   float alpha, float beta, float* scratch, int64_t scratch_floats, void* stream);
+
+/* ---- NHWC companions (csrc/nhwc.cu): BatchNorm(+ReLU+residual), stride-2 phase split, pools, stem im2col ------------------
+ * (ref: ATen batch_norm / relu / add / max_pool2d / adaptive_avg_pool2d of the north-star ResNet-18.)
+ * x, y, dy, ...: [R = N*H*W, C] fp32.  partial: ddl_bn_nhwc_ws_floats(R, C) floats; counters: (C+31)/32 zeroed unsigned. */
+int64_t ddl_bn_nhwc_ws_floats(int64_t R, int C);
+/* n_tracked (may be NULL): the module's int64 num_batches_tracked, incremented by one on the device */
+int ddl_bn_nhwc_stats(const float* x, int64_t R, int C, float* partial, unsigned* counters, float* mean, float* rstd, float* run_mean,
+                      float* run_var, long long* n_tracked, float eps, float momentum, void* stream);
+int ddl_bn_nhwc_apply(const float* x, const float* res, float* y, const float* mean, const float* rstd, const float* gamma,
+                      const float* beta, int64_t R, int C, int relu, void* stream);
+int ddl_bn_nhwc_bwd(const float* x, const float* y, const float* dy, float* dx, float* dres, const float* mean, const float* rstd,
+                    const float* gamma, float* dgamma, float* dbeta, float* partial, unsigned* counters, int64_t R, int C, int relu,
+                    void* stream);
+int ddl_phase_split(const float* x, float* ph, int N, int H, int W, int C, void* stream);      /* ph: [4][N,H/2,W/2,C] */
+int ddl_maxpool3x3s2_fwd(const float* x, float* y, unsigned char* code, int N, int H, int W, int C, void* stream);
+int ddl_maxpool3x3s2_bwd(const float* dy, const unsigned char* code, float* dx, int N, int H, int W, int C, void* stream);
+int ddl_avgpool_nhwc_fwd(const float* x, float* y, int N, int S, int C, void* stream);
+int ddl_avgpool_nhwc_bwd(const float* dy, float* dx, int N, int S, int C, void* stream);
+int ddl_im2col_stem7(const float* x, float* col, int N, int Cin, int H, int W, void* stream);  /* x NCHW -> col [N*Ho*Wo, 224] (196 + 28 zeros) */
+
 #ifdef __cplusplus
 }
 #endif
