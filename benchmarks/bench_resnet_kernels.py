@@ -35,10 +35,11 @@ def time_fn(fn, flusher, iters=20, warmup=5):
     return tot / iters
 
 
-def time_graphed(fn, flusher, iters=20):
-    """GPU time of ``fn`` when its launches are replayed from a CUDA graph (no host launch gaps)."""
-    g = GraphedStep(lambda: fn(), ())
-    return time_fn(g, flusher, iters=iters, warmup=3)
+def time_graphed(fn, flusher, iters=20, rep=1):
+    """GPU time of one ``fn()`` when its launches are replayed from a CUDA graph (no host launch gaps); ``rep`` > 1
+    captures that many back-to-back calls and divides (steady-state, L2-warm cost of a small op inside a step)."""
+    g = GraphedStep(lambda: [fn() for _ in range(rep)][-1], ())
+    return time_fn(g, flusher, iters=iters, warmup=3) / rep
 
 
 def main():
@@ -105,14 +106,45 @@ def main():
                 _, ph0 = ours_fwd()
                 cbw = lambda g, x_, w_: torch.ops.aten.convolution_backward(g, x_, w_, None, [s, s], [p, p], [1, 1], False, [0, 0], 1,
                                                                             [True, True, False])
-                r["fwd_ms"] = time_graphed(ours_fwd, fl)
-                r["fwd_cudnn_ms"] = time_graphed(lambda: F.conv2d(xc, wc, None, s, p), fl)
-                r["fwd_cudnn_cl_ms"] = time_graphed(lambda: F.conv2d(xcl, wcl, None, s, p), fl)
-                r["bwd_ms"] = time_graphed(lambda: ours_bwd(ph0), fl)
-                r["bwd_cudnn_ms"] = time_graphed(lambda: cbw(gyc, xc, wc), fl)
-                r["bwd_cudnn_cl_ms"] = time_graphed(lambda: cbw(gycl, xcl, wcl), fl)
+                r["fwd_ms"] = time_graphed(ours_fwd, fl, rep=8)
+                r["fwd_cudnn_ms"] = time_graphed(lambda: F.conv2d(xc, wc, None, s, p), fl, rep=8)
+                r["fwd_cudnn_cl_ms"] = time_graphed(lambda: F.conv2d(xcl, wcl, None, s, p), fl, rep=8)
+                r["bwd_ms"] = time_graphed(lambda: ours_bwd(ph0), fl, rep=8)
+                r["bwd_cudnn_ms"] = time_graphed(lambda: cbw(gyc, xc, wc), fl, rep=8)
+                r["bwd_cudnn_cl_ms"] = time_graphed(lambda: cbw(gycl, xcl, wcl), fl, rep=8)
             r["fwd_tflops"] = flops / r["fwd_ms"] / 1e9
             print(json.dumps(r))
+        # BatchNorm(+ReLU) forward / backward on [B*8*8, 64] and [B, 512] (layer1 / layer4 shapes)
+        for (R_, C_) in [(args.batch * 64, 64), (args.batch * 16, 128), (args.batch, 512)]:
+            xb = torch.randn(R_, C_, device=dev)
+            bn = torch.nn.BatchNorm2d(C_).to(dev)
+            with torch.no_grad():
+                yb = K._BnFn.apply(xb, bn.weight, bn.bias, None, bn.running_mean, bn.running_var, bn.num_batches_tracked, True, 0.1, 1e-5, True)
+            gb = torch.randn_like(yb)
+            mean = torch.zeros(C_, device=dev); rstd = torch.ones(C_, device=dev)
+            ws = K._workspace(dev)
+            from ddl25spring_b200.ops import _lib
+            L = _lib.lib()
+
+            def bn_f():
+                return K._BnFn.forward(_Ctx(), xb, bn.weight, bn.bias, None, bn.running_mean, bn.running_var, None, True, 0.1, 1e-5, True)
+
+            def bn_b():
+                dx = torch.empty_like(xb); dg = torch.empty_like(mean); db = torch.empty_like(mean)
+                _lib.check(L.ddl_bn_nhwc_bwd(_lib.p(xb), _lib.p(yb), _lib.p(gb), _lib.p(dx), None, _lib.p(mean), _lib.p(rstd), _lib.p(bn.weight),
+                                             _lib.p(dg), _lib.p(db), _lib.p(ws["bn_partial"]), _lib.p(ws["bn_counters"]), _lib.i64(R_), int(C_), 1,
+                                             _lib.stream()))
+                return dx
+
+            xn = xb.view(-1, 1, 1, C_).permute(0, 3, 1, 2)
+            with torch.no_grad():
+                print(json.dumps({"bn_shape": [R_, C_], "fwd_ms": time_graphed(bn_f, fl, rep=8), "bwd_ms": time_graphed(bn_b, fl, rep=8),
+                                  "fwd_aten_ms": time_graphed(lambda: F.relu(F.batch_norm(xb, None, None, bn.weight, bn.bias, True)), fl, rep=8)}))
+
+
+class _Ctx:
+    def save_for_backward(self, *a):
+        pass
 
 
 if __name__ == "__main__":

@@ -45,6 +45,31 @@ void ddl_count_launch(int n = 1);
 static constexpr int kNumSMs = 148;  // B200
 
 #ifdef __CUDACC__
+// Programmatic dependent launch: a step of the NHWC networks is ~200 dependent kernels of a few microseconds each, so the
+// launch / drain gap between two kernels costs as much as the kernels.  Kernels launched through ddl_launch_pdl may start
+// while their predecessor in the stream is still running; they execute pdl_wait() before touching global memory (it returns
+// once the predecessor has completed and its writes are visible) and call pdl_launch_dependents() as soon as their own
+// successor may begin its prologue.  Both are no-ops for a kernel launched the ordinary way.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t ddl_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
+#ifdef __CUDACC__
 namespace ddl {
 
 __device__ __forceinline__ float warp_sum(float v) {

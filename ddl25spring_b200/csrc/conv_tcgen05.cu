@@ -69,18 +69,26 @@ struct ConvParams {
   float alpha, beta;
   int act;
   float slope;
+  // fprop/dgrad with several output phases in one launch (stride-2 dgrad): phase f owns taps [ph_begin[f], ph_begin[f+1]) and
+  // writes at o_off + ph_off[f]; blockIdx.z = phase (n_split == 1 then).  n_phases == 1: all taps, offset 0.
+  int n_phases;
+  int ph_begin[5];
+  int64_t ph_off[4];
   int n_split;
   int kb_per_split;
   float* scratch;                    // n_split > 1: [split][rows][Nout] partial tiles (rows = tiles*128, or taps*Mout for wgrad)
   int64_t scratch_rows;
 };
 
-template <int BN>
+template <int BN, bool DEEP>
 struct ConvPlan {
   static constexpr int A_BYTES = BM * ROW_BYTES;
   static constexpr int B_BYTES = BN * ROW_BYTES;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = BN >= 128 ? 3 : 4;          // <= 98 KB: two CTAs per SM, one's epilogue hides under the other's main loop
+  // DEEP (grids of less than two waves): a CTA's k-loop is bound by the L2 -> shared-memory latency of its TMA loads, not by
+  // bandwidth or the tensor core (measured ~350 ns per k-block with 3-4 stages), so the ring is as deep as one CTA per SM
+  // allows.  Otherwise <= 98 KB so that two CTAs share an SM and one's epilogue hides under the other's main loop.
+  static constexpr int STAGES = DEEP ? (BN >= 128 ? 6 : 8) : (BN >= 128 ? 3 : 4);
   static constexpr int TOTAL = STAGES * STAGE_BYTES + 1024 /*barriers*/ + 1024 /*alignment slack*/;
 };
 
@@ -211,9 +219,9 @@ __device__ __forceinline__ void conv_mma_loop(const Bars& b, uint8_t* stage_base
 }
 
 // ---------------------------------------------------------------------------------------- fprop / dgrad
-template <int BN, bool B_MN>
-__global__ void __launch_bounds__(kThreads, 2) conv_tap_gemm_kernel(const __grid_constant__ ConvParams p) {
-  using Plan = ConvPlan<BN>;
+template <int BN, bool B_MN, bool DEEP>
+__global__ void __launch_bounds__(kThreads, DEEP ? 1 : 2) conv_tap_gemm_kernel(const __grid_constant__ ConvParams p) {
+  using Plan = ConvPlan<BN, DEEP>;
   constexpr int STAGES = Plan::STAGES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* stage_base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -223,8 +231,10 @@ __global__ void __launch_bounds__(kThreads, 2) conv_tap_gemm_kernel(const __grid
   const int tw = blockIdx.x % p.tiles_w, th = (blockIdx.x / p.tiles_w) % p.tiles_h, tn = blockIdx.x / (p.tiles_w * p.tiles_h);
   const int j0 = tw << p.bw_log2, i0 = th << p.bh_log2, n0 = tn << p.bn_log2;
   const int col0 = blockIdx.y * BN;
-  const int split = blockIdx.z;
-  const int total_kb = p.n_taps * p.cblocks;
+  const int phase = p.n_phases > 1 ? blockIdx.z : 0;
+  const int split = p.n_phases > 1 ? 0 : blockIdx.z;
+  const int tap0 = p.ph_begin[phase];
+  const int total_kb = (p.ph_begin[phase + 1] - tap0) * p.cblocks;
   const int kb_begin = split * p.kb_per_split;
   const int kb_end = min(total_kb, kb_begin + p.kb_per_split);
   const int num_kb = max(0, kb_end - kb_begin);
@@ -238,14 +248,16 @@ __global__ void __launch_bounds__(kThreads, 2) conv_tap_gemm_kernel(const __grid
   __syncthreads();
   fence_after_thread_sync();
   const uint32_t tmem_acc = *b.tmem_slot;
+  pdl_launch_dependents();     // the next kernel may set up while this one computes ...
+  pdl_wait();                  // ... and this one touches global memory only after its predecessor has finished
 
   if (warp == 0) {
     if (elect_one()) {
-      uint32_t phase = 0;
       int s = 0;
-      int tap = kb_begin / p.cblocks, cb = kb_begin % p.cblocks;
+      uint32_t par = 0;
+      int tap = tap0 + kb_begin / p.cblocks, cb = kb_begin % p.cblocks;
       for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(&b.empty[s], phase ^ 1);
+        mbar_wait(&b.empty[s], par ^ 1);
         uint8_t* a_dst = stage_base + s * Plan::STAGE_BYTES;
         uint8_t* b_dst = a_dst + Plan::A_BYTES;
         mbar_arrive_expect_tx(&b.full[s], Plan::STAGE_BYTES);
@@ -253,7 +265,7 @@ __global__ void __launch_bounds__(kThreads, 2) conv_tap_gemm_kernel(const __grid
         if constexpr (B_MN) tma_load_4d(b_dst, &p.bmap, &b.full[s], 0, cb * BK, col0 / BK, p.tap_w[tap]);
         else tma_load_3d(b_dst, &p.bmap, &b.full[s], cb * BK, p.tap_w[tap], col0);
         if (++cb == p.cblocks) { cb = 0; ++tap; }
-        if (++s == STAGES) { s = 0; phase ^= 1; }
+        if (++s == STAGES) { s = 0; par ^= 1; }
       }
     }
   } else if (warp == 1) {
@@ -273,7 +285,7 @@ __global__ void __launch_bounds__(kThreads, 2) conv_tap_gemm_kernel(const __grid
                         [=](int m) -> int64_t { return (row0 + m) * Nout; });
     } else {
       const int Nn = p.Nn, Hh = p.Hh, Ww = p.Ww;
-      const int64_t o_off = p.o_off, o_sn = p.o_sn, o_sh = p.o_sh, o_sw = p.o_sw;
+      const int64_t o_off = p.o_off + p.ph_off[phase], o_sn = p.o_sn, o_sh = p.o_sh, o_sw = p.o_sw;
       conv_epilogue<BN>(tmem_acc, wsm, warp, lane, num_kb > 0, p.out, col0, p.Nout, p.bias, p.alpha, p.beta, p.act, p.slope, false,
                         [=](int m) -> int64_t {
                           const int n = n0 + (m >> (bwl + bhl)), i = i0 + ((m >> bwl) & ((1 << bhl) - 1)), j = j0 + (m & ((1 << bwl) - 1));
@@ -291,6 +303,8 @@ __global__ void __launch_bounds__(kThreads, 2) conv_tap_gemm_kernel(const __grid
 
 // Sum the split-K partial tiles of conv_tap_gemm_kernel in split order and apply the epilogue (pixel mapping as above).
 __global__ void __launch_bounds__(256) conv_splitk_reduce_kernel(const __grid_constant__ ConvParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int nv = p.Nout >> 2;
   const int64_t total = p.scratch_rows * nv;
   const int bwl = p.bw_log2, bhl = p.bh_log2, bnl = p.bn_log2;
@@ -325,9 +339,9 @@ __global__ void __launch_bounds__(256) conv_splitk_reduce_kernel(const __grid_co
 // ---------------------------------------------------------------------------------------- wgrad
 // M = Cout (A = dY, M-major), N = Cin (B = X at the tap's offset, N-major), K = pixels in boxes of 32.
 // grid = (ceil(Cout/128), ceil(Cin/BN), n_taps * n_split)
-template <int BN>
-__global__ void __launch_bounds__(kThreads, 2) conv_wgrad_kernel(const __grid_constant__ ConvParams p) {
-  using Plan = ConvPlan<BN>;
+template <int BN, bool DEEP>
+__global__ void __launch_bounds__(kThreads, DEEP ? 1 : 2) conv_wgrad_kernel(const __grid_constant__ ConvParams p) {
+  using Plan = ConvPlan<BN, DEEP>;
   constexpr int STAGES = Plan::STAGES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* stage_base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -350,6 +364,8 @@ __global__ void __launch_bounds__(kThreads, 2) conv_wgrad_kernel(const __grid_co
   __syncthreads();
   fence_after_thread_sync();
   const uint32_t tmem_acc = *b.tmem_slot;
+  pdl_launch_dependents();     // the next kernel may set up while this one computes ...
+  pdl_wait();                  // ... and this one touches global memory only after its predecessor has finished
 
   if (warp == 0) {
     if (elect_one()) {
@@ -398,6 +414,8 @@ __global__ void __launch_bounds__(kThreads, 2) conv_wgrad_kernel(const __grid_co
 }
 
 __global__ void __launch_bounds__(256) conv_wgrad_reduce_kernel(const __grid_constant__ ConvParams p) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int nv = p.Nout >> 2;
   const int64_t total = p.scratch_rows * nv;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
@@ -455,16 +473,22 @@ int make_act_map5(CUtensorMap* m, const float* base, int N, int H, int W, int C,
 
 bool chan_ok(int C) { return C >= 4 && C % 4 == 0 && (C < BK || C % BK == 0); }
 
-// Copy the taps that can touch the image; returns their number.
+// Copy the taps that can touch the image (phase by phase); returns their number.
 int fill_taps(ConvParams& p, const int* tap_map, const int* tap_dh, const int* tap_dw, const int* tap_w, int n_taps, int Hsrc, int Wsrc,
-              int Hh, int Ww) {
+              int Hh, int Ww, int n_phases = 1, const int* phase_begin = nullptr) {
   int k = 0;
-  for (int t = 0; t < n_taps; ++t) {
-    if (tap_dh[t] >= Hsrc || tap_dh[t] <= -Hh || tap_dw[t] >= Wsrc || tap_dw[t] <= -Ww) continue;
-    p.tap_map[k] = (signed char)tap_map[t]; p.tap_dh[k] = (signed char)tap_dh[t];
-    p.tap_dw[k] = (signed char)tap_dw[t]; p.tap_w[k] = (signed char)tap_w[t];
-    ++k;
+  for (int f = 0; f < n_phases; ++f) {
+    const int t0 = phase_begin ? phase_begin[f] : 0, t1 = phase_begin ? phase_begin[f + 1] : n_taps;
+    p.ph_begin[f] = k;
+    for (int t = t0; t < t1; ++t) {
+      if (tap_dh[t] >= Hsrc || tap_dh[t] <= -Hh || tap_dw[t] >= Wsrc || tap_dw[t] <= -Ww) continue;
+      p.tap_map[k] = (signed char)tap_map[t]; p.tap_dh[k] = (signed char)tap_dh[t];
+      p.tap_dw[k] = (signed char)tap_dw[t]; p.tap_w[k] = (signed char)tap_w[t];
+      ++k;
+    }
   }
+  for (int f = n_phases; f <= 4; ++f) p.ph_begin[f] = k;
+  p.n_phases = n_phases;
   p.n_taps = k;
   return k;
 }
@@ -485,11 +509,13 @@ extern "C" {
 // out + o_off + n*o_sn + i*o_sh + j*o_sw (+ channel).
 int ddl_conv_tap_gemm(const float* const* acts, int n_maps, int N, int Ha, int Wa, int Ca, const float* Wt, int Cout, int T, int Cin,
                       int w_mn_major, const int* tap_map, const int* tap_dh, const int* tap_dw, const int* tap_w, int n_taps,
-                      float* out, int Hh, int Ww, int64_t o_off, int64_t o_sn, int64_t o_sh, int64_t o_sw, const float* bias,
+                      int n_phases, const int* phase_begin, const int64_t* phase_off, float* out, int Hh, int Ww, int64_t o_off, int64_t o_sn, int64_t o_sh, int64_t o_sw, const float* bias,
                       float alpha, float beta, int act, float slope, float* scratch, int64_t scratch_floats, void* stream) {
   DDL_REQUIRE(n_maps >= 1 && n_maps <= kMaxMaps && n_taps >= 1 && n_taps <= kMaxTaps, "n_maps=%d / n_taps=%d out of range", n_maps, n_taps);
   DDL_REQUIRE(chan_ok(Cin) && chan_ok(Cout), "channel counts (%d, %d) must be multiples of 4, and of 32 when above 32", Cin, Cout);
   DDL_REQUIRE(Ca == (w_mn_major ? Cout : Cin), "activation channels %d do not match the weight's reduced dimension", Ca);
+  if (n_phases < 1 || !phase_begin) n_phases = 1;
+  DDL_REQUIRE(n_phases <= 4 && (n_phases == 1 || phase_off), "n_phases=%d outside [1,4] or missing phase offsets", n_phases);
   const int Nout = w_mn_major ? Cin : Cout;
   DDL_REQUIRE(o_off % 4 == 0 && o_sn % 4 == 0 && o_sh % 4 == 0 && o_sw % 4 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0,
               "output rows must be 16-byte aligned");
@@ -506,12 +532,16 @@ int ddl_conv_tap_gemm(const float* const* acts, int n_maps, int N, int Ha, int W
   for (int t = 0; t < n_taps; ++t)
     DDL_REQUIRE(tap_map[t] >= 0 && tap_map[t] < n_maps && tap_w[t] >= 0 && tap_w[t] < T, "tap %d refers to map %d / weight tap %d", t,
                 tap_map[t], tap_w[t]);
-  fill_taps(p, tap_map, tap_dh, tap_dw, tap_w, n_taps, Ha, Wa, Hh, Ww);
+  fill_taps(p, tap_map, tap_dh, tap_dw, tap_w, n_taps, Ha, Wa, Hh, Ww, n_phases, n_phases > 1 ? phase_begin : nullptr);
   DDL_REQUIRE(p.n_taps > 0, "no tap touches the image");
+  for (int f = 0; f < 4; ++f) {
+    p.ph_off[f] = (n_phases > 1 && f < n_phases) ? phase_off[f] : 0;
+    DDL_REQUIRE(p.ph_off[f] % 4 == 0, "phase offsets must keep rows 16-byte aligned");
+  }
   p.cblocks = (Ca + BK - 1) / BK;
   const int tiles = p.tiles_w * p.tiles_h * p.tiles_n;
   int BN = Nout <= 32 ? 32 : (Nout <= 64 ? 64 : 128);
-  if (BN == 128 && tiles * ((Nout + 127) / 128) < kNumSMs / 2) BN = 64;       // small problems: more, narrower tiles
+  if (BN == 128 && tiles * n_phases * ((Nout + 127) / 128) < kNumSMs / 2) BN = 64;       // small problems: more, narrower tiles
   if (w_mn_major) {
     uint64_t dims[4] = {(uint64_t)(Cin < BK ? Cin : BK), (uint64_t)Cout, (uint64_t)((Cin + BK - 1) / BK), (uint64_t)T};
     uint64_t strides[3] = {(uint64_t)T * Cin * 4, (uint64_t)ROW_BYTES, (uint64_t)Cin * 4};
@@ -529,7 +559,7 @@ int ddl_conv_tap_gemm(const float* const* acts, int n_maps, int N, int Ha, int W
   const int total_kb = p.n_taps * p.cblocks;
   const int ctas = tiles * ((Nout + BN - 1) / BN);
   int n_split = 1;
-  if (2 * ctas <= kNumSMs && total_kb >= 8 && scratch) {      // less than half a wave: split the reduction across more SMs
+  if (n_phases == 1 && 2 * ctas <= kNumSMs && total_kb >= 8 && scratch) {      // less than half a wave: split the reduction across more SMs
     n_split = kNumSMs / ctas;
     if (n_split > total_kb / 4) n_split = total_kb / 4;
     const int64_t per_split = (int64_t)tiles * BM * Nout;
@@ -540,23 +570,26 @@ int ddl_conv_tap_gemm(const float* const* acts, int n_maps, int N, int Ha, int W
   n_split = (total_kb + p.kb_per_split - 1) / p.kb_per_split;
   p.n_split = n_split; p.scratch = scratch; p.scratch_rows = (int64_t)tiles * BM;
   cudaStream_t st = (cudaStream_t)stream;
-  dim3 grid(tiles, (Nout + BN - 1) / BN, n_split);
-#define DDL_CONV_CASE(BN_, MN_)                                                                   \
+  dim3 grid(tiles, (Nout + BN - 1) / BN, n_phases > 1 ? n_phases : n_split);
+  const bool deep = (int64_t)grid.x * grid.y * grid.z < 2 * kNumSMs;
+#define DDL_CONV_CASE3(BN_, MN_, DEEP_)                                                           \
   {                                                                                               \
-    auto kern = conv_tap_gemm_kernel<BN_, MN_>;                                                   \
+    auto kern = conv_tap_gemm_kernel<BN_, MN_, DEEP_>;                                            \
     static bool configured = false;                                                               \
-    if (!configured) { if (int e = set_smem(kern, ConvPlan<BN_>::TOTAL)) return e; configured = true; } \
-    kern<<<grid, kThreads, ConvPlan<BN_>::TOTAL, st>>>(p);                                        \
+    if (!configured) { if (int e = set_smem(kern, ConvPlan<BN_, DEEP_>::TOTAL)) return e; configured = true; } \
+    DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kThreads), ConvPlan<BN_, DEEP_>::TOTAL, st, p)); \
   }
+#define DDL_CONV_CASE(BN_, MN_) { if (deep) DDL_CONV_CASE3(BN_, MN_, true) else DDL_CONV_CASE3(BN_, MN_, false) }
   if (BN == 32) { if (w_mn_major) DDL_CONV_CASE(32, true) else DDL_CONV_CASE(32, false) }
   else if (BN == 64) { if (w_mn_major) DDL_CONV_CASE(64, true) else DDL_CONV_CASE(64, false) }
   else { if (w_mn_major) DDL_CONV_CASE(128, true) else DDL_CONV_CASE(128, false) }
 #undef DDL_CONV_CASE
+#undef DDL_CONV_CASE3
   DDL_LAUNCH_CHECK();
   if (n_split > 1) {
     int64_t blocks = (p.scratch_rows * (Nout / 4) + 255) / 256;
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    conv_splitk_reduce_kernel<<<(int)blocks, 256, 0, st>>>(p);
+    DDL_CUDA_CHECK(ddl_launch_pdl(conv_splitk_reduce_kernel, dim3((unsigned)blocks), dim3(256), 0, st, p));
     DDL_LAUNCH_CHECK();
   }
   return DDL_OK;
@@ -604,20 +637,23 @@ int ddl_conv_wgrad(const float* dY, int N, int Ho, int Wo, int Cout, const float
   n_split = (total_kb + p.kb_per_split - 1) / p.kb_per_split;
   p.n_split = n_split; p.scratch = scratch; p.scratch_rows = (int64_t)p.n_taps * Cout;
   dim3 grid((Cout + BM - 1) / BM, (Cin + BN - 1) / BN, p.n_taps * n_split);
-#define DDL_WGRAD_CASE(BN_)                                                                       \
+  const bool deep = (int64_t)grid.x * grid.y * grid.z < 2 * kNumSMs;
+#define DDL_WGRAD_CASE3(BN_, DEEP_)                                                               \
   {                                                                                               \
-    auto kern = conv_wgrad_kernel<BN_>;                                                           \
+    auto kern = conv_wgrad_kernel<BN_, DEEP_>;                                                    \
     static bool configured = false;                                                               \
-    if (!configured) { if (int e = set_smem(kern, ConvPlan<BN_>::TOTAL)) return e; configured = true; } \
-    kern<<<grid, kThreads, ConvPlan<BN_>::TOTAL, st>>>(p);                                        \
+    if (!configured) { if (int e = set_smem(kern, ConvPlan<BN_, DEEP_>::TOTAL)) return e; configured = true; } \
+    DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kThreads), ConvPlan<BN_, DEEP_>::TOTAL, st, p)); \
   }
+#define DDL_WGRAD_CASE(BN_) { if (deep) DDL_WGRAD_CASE3(BN_, true) else DDL_WGRAD_CASE3(BN_, false) }
   if (BN == 32) DDL_WGRAD_CASE(32) else if (BN == 64) DDL_WGRAD_CASE(64) else DDL_WGRAD_CASE(128)
 #undef DDL_WGRAD_CASE
+#undef DDL_WGRAD_CASE3
   DDL_LAUNCH_CHECK();
   if (n_split > 1) {
     int64_t blocks = (p.scratch_rows * (Cin / 4) + 255) / 256;
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    conv_wgrad_reduce_kernel<<<(int)blocks, 256, 0, st>>>(p);
+    DDL_CUDA_CHECK(ddl_launch_pdl(conv_wgrad_reduce_kernel, dim3((unsigned)blocks), dim3(256), 0, st, p));
     DDL_LAUNCH_CHECK();
   }
   return DDL_OK;

@@ -18,32 +18,51 @@
 
 namespace {
 
-constexpr int kBnThreads = 256;   // 32 channels (lanes) x 8 row lanes (warps)
+constexpr int kBnThreads = 256;
 
-// sum_a[c], sum_b[c] over rows of fa(row, c), fb(row, c); partial[(split * 2 + which) * C + c]
-template <typename FA>
-__device__ __forceinline__ void column_partials(int64_t R, int C, int n_split, float* __restrict__ partial, FA f) {
-  __shared__ float sa[8][33], sb[8][33];
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int c = blockIdx.x * 32 + lane;
-  const int split = blockIdx.y;
+// Column reductions over [R, C]: a CTA owns 4*L channels (L = min(C/4, 32) float4 lanes per row) and a slice of the rows;
+// thread (lx, ry) accumulates rows ry, ry + RL, ... of channel quad lx with four independent chains (loads in flight).
+struct ColGeom {
+  int L, RL, lx, ry, c;       // c = first channel of this thread's quad
+  int64_t r0, r1;
+};
+__device__ __forceinline__ ColGeom col_geom(int64_t R, int C, int n_split) {
+  ColGeom g;
+  g.L = min(C >> 2, 32);
+  g.RL = kBnThreads / g.L;
+  g.lx = threadIdx.x % g.L;
+  g.ry = threadIdx.x / g.L;
+  g.c = (blockIdx.x * g.L + g.lx) * 4;
   const int64_t chunk = (R + n_split - 1) / n_split;
-  const int64_t r0 = split * chunk, r1 = min(R, r0 + chunk);
-  float a = 0.f, b = 0.f;
-  if (c < C) {
-    float a1 = 0.f, b1 = 0.f, a2 = 0.f, b2 = 0.f, a3 = 0.f, b3 = 0.f;      // four independent chains: loads in flight
-    int64_t r = r0 + w;
-    for (; r + 24 < r1; r += 32) { f(r, c, a, b); f(r + 8, c, a1, b1); f(r + 16, c, a2, b2); f(r + 24, c, a3, b3); }
-    for (; r < r1; r += 8) f(r, c, a, b);
-    a += a1 + (a2 + a3); b += b1 + (b2 + b3);
+  g.r0 = blockIdx.y * chunk;
+  g.r1 = min(R, g.r0 + chunk);
+  return g;
+}
+
+__device__ __forceinline__ void add4(float4& a, const float4& v) { a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w; }
+
+// partial[(split * 2 + which) * C + c]; f(row, c, a, b) accumulates one row's contribution into the float4 pair (a, b)
+template <typename F>
+__device__ __forceinline__ void column_partials(int64_t R, int C, int n_split, float* __restrict__ partial, F f) {
+  __shared__ float4 sa[kBnThreads], sb[kBnThreads];
+  const ColGeom g = col_geom(R, C, n_split);
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+  if (g.c < C) {
+    float4 a1 = a, b1 = a, a2 = a, b2 = a, a3 = a, b3 = a;
+    int64_t r = g.r0 + g.ry;
+    const int st = g.RL;
+#pragma unroll 2
+    for (; r + 3 * st < g.r1; r += 4 * st) { f(r, g.c, a, b); f(r + st, g.c, a1, b1); f(r + 2 * st, g.c, a2, b2); f(r + 3 * st, g.c, a3, b3); }
+    for (; r < g.r1; r += st) f(r, g.c, a, b);
+    add4(a2, a3); add4(a, a1); add4(a, a2);
+    add4(b2, b3); add4(b, b1); add4(b, b2);
   }
-  sa[w][lane] = a; sb[w][lane] = b;
+  sa[threadIdx.x] = a; sb[threadIdx.x] = b;
   __syncthreads();
-  if (w == 0 && c < C) {
-#pragma unroll
-    for (int k = 1; k < 8; ++k) { a += sa[k][lane]; b += sb[k][lane]; }
-    partial[((int64_t)split * 2 + 0) * C + c] = a;
-    partial[((int64_t)split * 2 + 1) * C + c] = b;
+  if (g.ry == 0 && g.c < C) {
+    for (int k = 1; k < g.RL; ++k) { add4(a, sa[k * g.L + g.lx]); add4(b, sb[k * g.L + g.lx]); }
+    *reinterpret_cast<float4*>(partial + ((int64_t)blockIdx.y * 2 + 0) * C + g.c) = a;
+    *reinterpret_cast<float4*>(partial + ((int64_t)blockIdx.y * 2 + 1) * C + g.c) = b;
   }
 }
 
@@ -62,24 +81,30 @@ __device__ __forceinline__ bool last_block_of_group(unsigned* counters) {
   return is_last;
 }
 
-// Sum the per-split partials of this CTA's 32 channels in a fixed order: warp w adds splits w, w+8, ...; warp 0 adds the 8
-// warp sums.  Returns (sum_a, sum_b) in the threads of warp 0.
-__device__ __forceinline__ void combine_partials(const float* __restrict__ partial, int C, int n_split, double& a, double& b) {
-  __shared__ double da[8][33], db[8][33];
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int c = blockIdx.x * 32 + lane;
-  a = 0.0; b = 0.0;
-  if (c < C)
-    for (int k = w; k < n_split; k += 8) {
-      a += (double)__ldcg(&partial[((int64_t)k * 2 + 0) * C + c]);
-      b += (double)__ldcg(&partial[((int64_t)k * 2 + 1) * C + c]);
-    }
-  da[w][lane] = a; db[w][lane] = b;
-  __syncthreads();
-  if (w == 0) {
+// Sum the per-split partials of this CTA's channels in a fixed order: row lane ry adds splits ry, ry + RL, ...; lane 0 adds
+// the RL lane sums.  Valid in the threads with ry == 0: a[i], b[i] for channels c .. c+3.
+__device__ __forceinline__ bool combine_partials(const float* __restrict__ partial, int64_t R, int C, int n_split, double (&a)[4],
+                                                 double (&b)[4], int& c_out) {
+  __shared__ double da[kBnThreads][4], db[kBnThreads][4];
+  const ColGeom g = col_geom(R, C, n_split);
 #pragma unroll
-    for (int k = 1; k < 8; ++k) { a += da[k][lane]; b += db[k][lane]; }
-  }
+  for (int i = 0; i < 4; ++i) { a[i] = 0.0; b[i] = 0.0; }
+  if (g.c < C)
+    for (int k = g.ry; k < n_split; k += g.RL) {
+      const float4 va = __ldcg(reinterpret_cast<const float4*>(partial + ((int64_t)k * 2 + 0) * C + g.c));
+      const float4 vb = __ldcg(reinterpret_cast<const float4*>(partial + ((int64_t)k * 2 + 1) * C + g.c));
+      a[0] += va.x; a[1] += va.y; a[2] += va.z; a[3] += va.w;
+      b[0] += vb.x; b[1] += vb.y; b[2] += vb.z; b[3] += vb.w;
+    }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { da[threadIdx.x][i] = a[i]; db[threadIdx.x][i] = b[i]; }
+  __syncthreads();
+  c_out = g.c;
+  if (g.ry != 0 || g.c >= C) return false;
+  for (int k = 1; k < g.RL; ++k)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { a[i] += da[k * g.L + g.lx][i]; b[i] += db[k * g.L + g.lx][i]; }
+  return true;
 }
 
 __global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const float* __restrict__ x, int64_t R, int C, float* __restrict__ partial,
@@ -87,33 +112,39 @@ __global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const float* __res
                                                               float* __restrict__ rstd, float* __restrict__ run_mean,
                                                               float* __restrict__ run_var, long long* __restrict__ n_tracked, float eps,
                                                               float momentum) {
-  column_partials(R, C, gridDim.y, partial, [&](int64_t r, int c, float& a, float& b) {
-    const float v = x[r * C + c];
-    a += v; b = fmaf(v, v, b);
+  pdl_launch_dependents();
+  pdl_wait();
+  column_partials(R, C, gridDim.y, partial, [&](int64_t r, int c, float4& a, float4& b) {
+    const float4 v = *reinterpret_cast<const float4*>(x + r * C + c);
+    add4(a, v);
+    b.x = fmaf(v.x, v.x, b.x); b.y = fmaf(v.y, v.y, b.y); b.z = fmaf(v.z, v.z, b.z); b.w = fmaf(v.w, v.w, b.w);
   });
   if (!last_block_of_group(counters)) return;
-  double s, q;
-  combine_partials(partial, C, gridDim.y, s, q);
-  const int c = blockIdx.x * 32 + threadIdx.x;
-  if (threadIdx.x < 32 && c < C) {
-    const double m = s / (double)R;
-    double var = q / (double)R - m * m;
+  double s[4], q[4];
+  int c;
+  if (!combine_partials(partial, R, C, gridDim.y, s, q, c)) return;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const double m = s[i] / (double)R;
+    double var = q[i] / (double)R - m * m;
     if (var < 0.0) var = 0.0;
-    mean[c] = (float)m;
-    rstd[c] = (float)(1.0 / sqrt(var + (double)eps));
+    mean[c + i] = (float)m;
+    rstd[c + i] = (float)(1.0 / sqrt(var + (double)eps));
     if (run_mean) {
       const double unbiased = R > 1 ? var * (double)R / (double)(R - 1) : var;
-      run_mean[c] = (1.f - momentum) * run_mean[c] + momentum * (float)m;
-      run_var[c] = (1.f - momentum) * run_var[c] + momentum * (float)unbiased;
+      run_mean[c + i] = (1.f - momentum) * run_mean[c + i] + momentum * (float)m;
+      run_var[c + i] = (1.f - momentum) * run_var[c + i] + momentum * (float)unbiased;
     }
-    if (n_tracked && c == 0) *n_tracked += 1;
   }
+  if (n_tracked && c == 0) *n_tracked += 1;
 }
 
 __global__ void __launch_bounds__(256) bn_apply_kernel(const float4* __restrict__ x, const float4* __restrict__ res, float4* __restrict__ y,
                                                        const float* __restrict__ mean, const float* __restrict__ rstd,
                                                        const float* __restrict__ gamma, const float* __restrict__ beta, int64_t total4,
                                                        int C, int relu) {
+  pdl_launch_dependents();
+  pdl_wait();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)((i * 4) % C);
     const float4 v = x[i];
@@ -133,22 +164,31 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(const float* 
                                                                    const float* __restrict__ mean, const float* __restrict__ rstd,
                                                                    float* __restrict__ partial, unsigned* __restrict__ counters,
                                                                    float* __restrict__ dgamma, float* __restrict__ dbeta, int relu) {
-  const int cc = blockIdx.x * 32 + (threadIdx.x & 31);
-  const float m = cc < C ? mean[cc] : 0.f, s = cc < C ? rstd[cc] : 0.f;
-  column_partials(R, C, gridDim.y, partial, [&](int64_t r, int c, float& a, float& b) {
-    float g = dy[r * C + c];
-    if (relu && !(y[r * C + c] > 0.f)) g = 0.f;
-    a += g;
-    b = fmaf(g, (x[r * C + c] - m) * s, b);
+  pdl_launch_dependents();
+  pdl_wait();
+  const ColGeom g0 = col_geom(R, C, gridDim.y);
+  float4 m = make_float4(0.f, 0.f, 0.f, 0.f), s = m;
+  if (g0.c < C) { m = *reinterpret_cast<const float4*>(mean + g0.c); s = *reinterpret_cast<const float4*>(rstd + g0.c); }
+  column_partials(R, C, gridDim.y, partial, [&](int64_t r, int c, float4& a, float4& b) {
+    float4 g = *reinterpret_cast<const float4*>(dy + r * C + c);
+    if (relu) {
+      const float4 o = *reinterpret_cast<const float4*>(y + r * C + c);
+      if (!(o.x > 0.f)) g.x = 0.f;
+      if (!(o.y > 0.f)) g.y = 0.f;
+      if (!(o.z > 0.f)) g.z = 0.f;
+      if (!(o.w > 0.f)) g.w = 0.f;
+    }
+    const float4 v = *reinterpret_cast<const float4*>(x + r * C + c);
+    add4(a, g);
+    b.x = fmaf(g.x, (v.x - m.x) * s.x, b.x); b.y = fmaf(g.y, (v.y - m.y) * s.y, b.y);
+    b.z = fmaf(g.z, (v.z - m.z) * s.z, b.z); b.w = fmaf(g.w, (v.w - m.w) * s.w, b.w);
   });
   if (!last_block_of_group(counters)) return;
-  double a, b;
-  combine_partials(partial, C, gridDim.y, a, b);
-  const int c = blockIdx.x * 32 + threadIdx.x;
-  if (threadIdx.x < 32 && c < C) {
-    dbeta[c] = (float)a;
-    dgamma[c] = (float)b;
-  }
+  double a[4], b[4];
+  int c;
+  if (!combine_partials(partial, R, C, gridDim.y, a, b, c)) return;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { dbeta[c + i] = (float)a[i]; dgamma[c + i] = (float)b[i]; }
 }
 
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float4* __restrict__ x, const float4* __restrict__ y,
@@ -156,6 +196,8 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float4* __restr
                                                            const float* __restrict__ mean, const float* __restrict__ rstd,
                                                            const float* __restrict__ gamma, const float* __restrict__ dgamma,
                                                            const float* __restrict__ dbeta, int64_t total4, int C, float inv_rows, int relu) {
+  pdl_launch_dependents();
+  pdl_wait();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)((i * 4) % C);
     float4 g = dy[i];
@@ -182,6 +224,8 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float4* __restr
 
 // x [N, H, W, C] -> ph [4][N, H/2, W/2, C], ph[2a+b][n,i,j,:] = x[n, 2i+a, 2j+b, :]
 __global__ void __launch_bounds__(256) phase_split_kernel(const float4* __restrict__ x, float4* __restrict__ ph, int N, int H, int W, int C4) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int Ho = H / 2, Wo = W / 2;
   const int64_t per = (int64_t)N * Ho * Wo * C4, total = 4 * per;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
@@ -198,6 +242,8 @@ __global__ void __launch_bounds__(256) phase_split_kernel(const float4* __restri
 // 3x3 stride-2 pad-1 max pool, NHWC, four channels per thread.  code = r*3+s of the first maximum (row-major scan, like torch).
 __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const float4* __restrict__ x, float4* __restrict__ y, uchar4* __restrict__ code,
                                                           int N, int H, int W, int C4, int Ho, int Wo) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int64_t total = (int64_t)N * Ho * Wo * C4;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
     int64_t r = e;
@@ -227,6 +273,8 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const float4* __restri
 
 __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const float4* __restrict__ dy, const uchar4* __restrict__ code,
                                                           float4* __restrict__ dx, int N, int H, int W, int C4, int Ho, int Wo) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int64_t total = (int64_t)N * H * W * C4;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
     int64_t r = e;
@@ -257,6 +305,8 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const float4* __restri
 
 // y[n, c] = mean_s x[n, s, c]
 __global__ void __launch_bounds__(256) avgpool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int S, int C) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int n = blockIdx.x;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     float a = 0.f;
@@ -265,6 +315,8 @@ __global__ void __launch_bounds__(256) avgpool_fwd_kernel(const float* __restric
   }
 }
 __global__ void __launch_bounds__(256) avgpool_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, int64_t total, int S, int C) {
+  pdl_launch_dependents();
+  pdl_wait();
   const float inv = 1.f / (float)S;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)(e % C);
@@ -276,6 +328,8 @@ __global__ void __launch_bounds__(256) avgpool_bwd_kernel(const float* __restric
 // col[(n,i,j), (r*7+s)*4 + ci] = x[n, ci, 2i+r-3, 2j+s-3] (NCHW input, ci < Cin <= 4; zero elsewhere); row pitch 224 floats
 __global__ void __launch_bounds__(256) im2col_stem_kernel(const float* __restrict__ x, float4* __restrict__ col, int N, int Cin, int H, int W,
                                                           int Ho, int Wo) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int64_t total = (int64_t)N * Ho * Wo * 56;     // 49 taps + 7 zero float4s: rows of 224 floats (a multiple of 32)
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
     int64_t r = e;
@@ -297,11 +351,13 @@ int grid_for(int64_t work, int threads) {
   return (int)(b < 1 ? 1 : b);
 }
 
+int bn_groups(int C) { return (C / 4 + 31) / 32; }     // CTAs along the channel axis (128 channels each)
+
 int bn_splits(int64_t R, int C) {
-  const int groups = (C + 31) / 32;
+  const int groups = bn_groups(C);
   int64_t s = (2 * kNumSMs + groups - 1) / groups;       // about two CTAs per SM ...
-  if (s > (R + 127) / 128) s = (R + 127) / 128;          // ... of at least 128 rows each
-  if (s > 64) s = 64;
+  if (s > (R + 63) / 64) s = (R + 63) / 64;              // ... of at least 64 rows each (latency-bound: short chains, many CTAs)
+  if (s > 128) s = 128;
   return (int)(s < 1 ? 1 : s);
 }
 
@@ -314,9 +370,10 @@ int64_t ddl_bn_nhwc_ws_floats(int64_t R, int C) { return (int64_t)bn_splits(R, C
 
 int ddl_bn_nhwc_stats(const float* x, int64_t R, int C, float* partial, unsigned* counters, float* mean, float* rstd, float* run_mean,
                       float* run_var, long long* n_tracked, float eps, float momentum, void* stream) {
-  DDL_REQUIRE(R > 0 && C > 0 && C % 4 == 0, "bn_nhwc: need rows > 0 and C %% 4 == 0 (C=%d)", C);
-  dim3 grid((C + 31) / 32, bn_splits(R, C));
-  bn_stats_kernel<<<grid, kBnThreads, 0, (cudaStream_t)stream>>>(x, R, C, partial, counters, mean, rstd, run_mean, run_var, n_tracked, eps, momentum);
+  DDL_REQUIRE(R > 0 && C > 0 && C % 4 == 0 && (C < 128 || C % 128 == 0) && 256 % (C < 128 ? C / 4 : 32) == 0,
+              "bn_nhwc: need rows > 0 and C a multiple of 4 that divides 128 or is a multiple of 128 (C=%d)", C);
+  dim3 grid(bn_groups(C), bn_splits(R, C));
+  DDL_CUDA_CHECK(ddl_launch_pdl(bn_stats_kernel, dim3(grid), dim3(kBnThreads), 0, (cudaStream_t)stream, x, R, C, partial, counters, mean, rstd, run_mean, run_var, n_tracked, eps, momentum));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -325,9 +382,9 @@ int ddl_bn_nhwc_apply(const float* x, const float* res, float* y, const float* m
                       const float* beta, int64_t R, int C, int relu, void* stream) {
   DDL_REQUIRE(C % 4 == 0, "bn_nhwc: C %% 4 != 0");
   const int64_t total4 = R * C / 4;
-  bn_apply_kernel<<<grid_for(total4, 256), 256, 0, (cudaStream_t)stream>>>(
+  DDL_CUDA_CHECK(ddl_launch_pdl(bn_apply_kernel, dim3(grid_for(total4, 256)), dim3(256), 0, (cudaStream_t)stream, 
       reinterpret_cast<const float4*>(x), reinterpret_cast<const float4*>(res), reinterpret_cast<float4*>(y), mean, rstd, gamma, beta,
-      total4, C, relu);
+      total4, C, relu));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -335,15 +392,16 @@ int ddl_bn_nhwc_apply(const float* x, const float* res, float* y, const float* m
 int ddl_bn_nhwc_bwd(const float* x, const float* y, const float* dy, float* dx, float* dres, const float* mean, const float* rstd,
                     const float* gamma, float* dgamma, float* dbeta, float* partial, unsigned* counters, int64_t R, int C, int relu,
                     void* stream) {
-  DDL_REQUIRE(R > 0 && C > 0 && C % 4 == 0, "bn_nhwc: need rows > 0 and C %% 4 == 0 (C=%d)", C);
+  DDL_REQUIRE(R > 0 && C > 0 && C % 4 == 0 && (C < 128 || C % 128 == 0) && 256 % (C < 128 ? C / 4 : 32) == 0,
+              "bn_nhwc: need rows > 0 and C a multiple of 4 that divides 128 or is a multiple of 128 (C=%d)", C);
   cudaStream_t st = (cudaStream_t)stream;
-  dim3 grid((C + 31) / 32, bn_splits(R, C));
-  bn_bwd_reduce_kernel<<<grid, kBnThreads, 0, st>>>(x, y, dy, R, C, mean, rstd, partial, counters, dgamma, dbeta, relu);
+  dim3 grid(bn_groups(C), bn_splits(R, C));
+  DDL_CUDA_CHECK(ddl_launch_pdl(bn_bwd_reduce_kernel, dim3(grid), dim3(kBnThreads), 0, st, x, y, dy, R, C, mean, rstd, partial, counters, dgamma, dbeta, relu));
   DDL_LAUNCH_CHECK();
   const int64_t total4 = R * C / 4;
-  bn_bwd_apply_kernel<<<grid_for(total4, 256), 256, 0, st>>>(
+  DDL_CUDA_CHECK(ddl_launch_pdl(bn_bwd_apply_kernel, dim3(grid_for(total4, 256)), dim3(256), 0, st, 
       reinterpret_cast<const float4*>(x), reinterpret_cast<const float4*>(y), reinterpret_cast<const float4*>(dy),
-      reinterpret_cast<float4*>(dx), reinterpret_cast<float4*>(dres), mean, rstd, gamma, dgamma, dbeta, total4, C, 1.f / (float)R, relu);
+      reinterpret_cast<float4*>(dx), reinterpret_cast<float4*>(dres), mean, rstd, gamma, dgamma, dbeta, total4, C, 1.f / (float)R, relu));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -351,8 +409,8 @@ int ddl_bn_nhwc_bwd(const float* x, const float* y, const float* dy, float* dx, 
 int ddl_phase_split(const float* x, float* ph, int N, int H, int W, int C, void* stream) {
   DDL_REQUIRE(H % 2 == 0 && W % 2 == 0 && C % 4 == 0, "phase_split: H, W must be even and C %% 4 == 0");
   const int64_t total = (int64_t)N * H * W * (C / 4);
-  phase_split_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const float4*>(x),
-                                                                            reinterpret_cast<float4*>(ph), N, H, W, C / 4);
+  DDL_CUDA_CHECK(ddl_launch_pdl(phase_split_kernel, dim3(grid_for(total, 256)), dim3(256), 0, (cudaStream_t)stream, reinterpret_cast<const float4*>(x),
+                                                                            reinterpret_cast<float4*>(ph), N, H, W, C / 4));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -360,8 +418,8 @@ int ddl_phase_split(const float* x, float* ph, int N, int H, int W, int C, void*
 int ddl_maxpool3x3s2_fwd(const float* x, float* y, unsigned char* code, int N, int H, int W, int C, void* stream) {
   const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
   DDL_REQUIRE(C % 4 == 0, "maxpool: C %% 4 != 0");
-  maxpool_fwd_kernel<<<grid_for((int64_t)N * Ho * Wo * (C / 4), 256), 256, 0, (cudaStream_t)stream>>>(
-      reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y), reinterpret_cast<uchar4*>(code), N, H, W, C / 4, Ho, Wo);
+  DDL_CUDA_CHECK(ddl_launch_pdl(maxpool_fwd_kernel, dim3(grid_for((int64_t)N * Ho * Wo * (C / 4), 256)), dim3(256), 0, (cudaStream_t)stream, 
+      reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y), reinterpret_cast<uchar4*>(code), N, H, W, C / 4, Ho, Wo));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -369,21 +427,21 @@ int ddl_maxpool3x3s2_fwd(const float* x, float* y, unsigned char* code, int N, i
 int ddl_maxpool3x3s2_bwd(const float* dy, const unsigned char* code, float* dx, int N, int H, int W, int C, void* stream) {
   const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
   DDL_REQUIRE(C % 4 == 0, "maxpool: C %% 4 != 0");
-  maxpool_bwd_kernel<<<grid_for((int64_t)N * H * W * (C / 4), 256), 256, 0, (cudaStream_t)stream>>>(
-      reinterpret_cast<const float4*>(dy), reinterpret_cast<const uchar4*>(code), reinterpret_cast<float4*>(dx), N, H, W, C / 4, Ho, Wo);
+  DDL_CUDA_CHECK(ddl_launch_pdl(maxpool_bwd_kernel, dim3(grid_for((int64_t)N * H * W * (C / 4), 256)), dim3(256), 0, (cudaStream_t)stream, 
+      reinterpret_cast<const float4*>(dy), reinterpret_cast<const uchar4*>(code), reinterpret_cast<float4*>(dx), N, H, W, C / 4, Ho, Wo));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
 
 int ddl_avgpool_nhwc_fwd(const float* x, float* y, int N, int S, int C, void* stream) {
-  avgpool_fwd_kernel<<<N, 256, 0, (cudaStream_t)stream>>>(x, y, S, C);
+  DDL_CUDA_CHECK(ddl_launch_pdl(avgpool_fwd_kernel, dim3(N), dim3(256), 0, (cudaStream_t)stream, x, y, S, C));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
 
 int ddl_avgpool_nhwc_bwd(const float* dy, float* dx, int N, int S, int C, void* stream) {
   const int64_t total = (int64_t)N * S * C;
-  avgpool_bwd_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(dy, dx, total, S, C);
+  DDL_CUDA_CHECK(ddl_launch_pdl(avgpool_bwd_kernel, dim3(grid_for(total, 256)), dim3(256), 0, (cudaStream_t)stream, dy, dx, total, S, C));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -391,8 +449,8 @@ int ddl_avgpool_nhwc_bwd(const float* dy, float* dx, int N, int S, int C, void* 
 int ddl_im2col_stem7(const float* x, float* col, int N, int Cin, int H, int W, void* stream) {
   DDL_REQUIRE(Cin >= 1 && Cin <= 4, "im2col_stem7: Cin=%d outside [1,4]", Cin);
   const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;    // (H + 6 - 7) / 2 + 1
-  im2col_stem_kernel<<<grid_for((int64_t)N * Ho * Wo * 56, 256), 256, 0, (cudaStream_t)stream>>>(x, reinterpret_cast<float4*>(col), N, Cin,
-                                                                                             H, W, Ho, Wo);
+  DDL_CUDA_CHECK(ddl_launch_pdl(im2col_stem_kernel, dim3(grid_for((int64_t)N * Ho * Wo * 56, 256)), dim3(256), 0, (cudaStream_t)stream, x, reinterpret_cast<float4*>(col), N, Cin,
+                                                                                             H, W, Ho, Wo));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

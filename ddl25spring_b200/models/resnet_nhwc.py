@@ -33,8 +33,8 @@ class ConvNHWC(nn.Module):
         self.weight = nn.Parameter(torch.empty(cout, k, k, cin))
         nn.init.normal_(self.weight, 0.0, math.sqrt(2.0 / (cout * k * k)))           # kaiming_normal_, fan_out, relu
 
-    def forward(self, x):
-        return K.conv2d_nhwc(x, self.weight, self.stride, self.padding)
+    def forward(self, x, phases=None):
+        return K.conv2d_nhwc(x, self.weight, self.stride, self.padding, phases)
 
 
 class StemConv(nn.Module):
@@ -67,9 +67,10 @@ class BasicBlockNHWC(nn.Module):
 
     def forward(self, x):
         idt = x
+        ph = K.stride2_phases(x) if self.conv1.stride == 2 else None      # one phase split feeds conv1 and the shortcut conv
         if self.downsample is not None:
-            idt = K.batch_norm_nhwc(self.downsample[0](x), self.downsample[1])
-        y = K.batch_norm_nhwc(self.conv1(x), self.bn1, relu=True)
+            idt = K.batch_norm_nhwc(self.downsample[0](x, ph if self.downsample[0].stride == 2 else None), self.downsample[1])
+        y = K.batch_norm_nhwc(self.conv1(x, ph), self.bn1, relu=True)
         return K.batch_norm_nhwc(self.conv2(y), self.bn2, relu=True, residual=idt)
 
 

@@ -37,6 +37,8 @@ def _workspace(device) -> dict:
     ws = _WS.get(key)
     if ws is None:
         ws = {"scratch": torch.empty(16 << 20, device=device, dtype=torch.float32),      # split-K partial tiles (64 MB)
+              "scratch_side": torch.empty(8 << 20, device=device, dtype=torch.float32),  # ... of the weight-gradient branch
+              "side": torch.cuda.Stream(device=device),
               "bn_partial": torch.empty(1 << 19, device=device, dtype=torch.float32),
               "bn_counters": torch.zeros(64, device=device, dtype=torch.int32)}
         _WS[key] = ws
@@ -76,13 +78,15 @@ def dgrad_taps(kh: int, kw: int, stride: int, pad: int):
 
 
 def _tap_gemm(maps, N, Ha, Wa, Ca, w, w_mn, taps, out, Hh, Ww, o_off, o_sn, o_sh, o_sw, bias=None, alpha=1.0, beta=0.0, act=None,
-              slope=0.2):
+              slope=0.2, phase_begin=None, phase_off=None):
     Cout, T, Cin = w.shape[0], w.shape[1] * w.shape[2], w.shape[3]
     ws = _workspace(out.device)
     ptrs = _lib.host_ptrs([m.data_ptr() for m in maps])
+    n_phases = len(phase_off) if phase_off else 1
     _lib.check(_lib.lib().ddl_conv_tap_gemm(
         ptrs, len(maps), int(N), int(Ha), int(Wa), int(Ca), _lib.p(w), int(Cout), int(T), int(Cin), int(w_mn),
         _ints([t[0] for t in taps]), _ints([t[1] for t in taps]), _ints([t[2] for t in taps]), _ints([t[3] for t in taps]), len(taps),
+        n_phases, _ints(phase_begin) if phase_off else None, (C.c_int64 * n_phases)(*phase_off) if phase_off else None,
         _lib.p(out), int(Hh), int(Ww), _lib.i64(o_off), _lib.i64(o_sn), _lib.i64(o_sh), _lib.i64(o_sw), _lib.p(bias),
         _lib.f32(alpha), _lib.f32(beta), int(ACT[act]), _lib.f32(slope), _lib.p(ws["scratch"]), _lib.i64(ws["scratch"].numel()),
         _lib.stream()), "ddl_conv_tap_gemm")
@@ -121,24 +125,23 @@ def _dgrad(dy, w, stride, pad, H, W, bias=None, act=None, slope=0.2):
     Cout, kh, kw, Cin = w.shape
     N, Ho, Wo, _ = dy.shape
     phases = dgrad_taps(kh, kw, stride, pad)
-    need_zero = any(len(t) == 0 for t in phases)
-    dx = (torch.zeros if need_zero else torch.empty)((N, H, W, Cin), device=dy.device, dtype=torch.float32)
+    dx = torch.empty((N, H, W, Cin), device=dy.device, dtype=torch.float32)
     if stride == 1:
         _tap_gemm([dy], N, Ho, Wo, Cout, w, 1, phases[0], dx, H, W, 0, H * W * Cin, W * Cin, Cin, bias=bias, act=act, slope=slope)
         return dx
     assert H % 2 == 0 and W % 2 == 0
-    for idx, taps in enumerate(phases):
-        if not taps:
-            if bias is not None or act is not None:
-                raise NotImplementedError("transposed convolution with empty phases and an epilogue")
-            continue
-        a, b = idx >> 1, idx & 1
-        _tap_gemm([dy], N, Ho, Wo, Cout, w, 1, taps, dx, H // 2, W // 2, (a * W + b) * Cin, H * W * Cin, 2 * W * Cin, 2 * Cin, bias=bias,
-                  act=act, slope=slope)
+    # the four output phases (h%2, w%2) in ONE launch (grid.z = phase); a phase without taps is written as act(bias)
+    taps, begin = [], [0]
+    for t in phases:
+        taps += t
+        begin.append(len(taps))
+    offs = [((idx >> 1) * W + (idx & 1)) * Cin for idx in range(4)]
+    _tap_gemm([dy], N, Ho, Wo, Cout, w, 1, taps, dx, H // 2, W // 2, 0, H * W * Cin, 2 * W * Cin, 2 * Cin, bias=bias, act=act, slope=slope,
+              phase_begin=begin, phase_off=offs)
     return dx
 
 
-def _wgrad(dy, x, ph, wshape, stride, pad):
+def _wgrad(dy, x, ph, wshape, stride, pad, out=None, scratch="scratch"):
     Cout, kh, kw, Cin = wshape
     N, Ho, Wo, _ = dy.shape
     if stride == 1:
@@ -146,14 +149,29 @@ def _wgrad(dy, x, ph, wshape, stride, pad):
     else:
         maps, Hx, Wx = [ph[i] for i in range(4)], ph.shape[2], ph.shape[3]
     taps = fwd_taps(kh, kw, stride, pad)
-    dw = torch.empty(wshape, device=dy.device, dtype=torch.float32)
+    dw = out if out is not None else torch.empty(wshape, device=dy.device, dtype=torch.float32)
     ws = _workspace(dy.device)
     _lib.check(_lib.lib().ddl_conv_wgrad(
         _lib.p(dy), int(N), int(Ho), int(Wo), int(Cout), _lib.host_ptrs([m.data_ptr() for m in maps]), len(maps), int(Hx), int(Wx),
         int(Cin), _ints([t[0] for t in taps]), _ints([t[1] for t in taps]), _ints([t[2] for t in taps]), _ints([t[3] for t in taps]),
-        len(taps), _lib.p(dw), int(kh * kw), _lib.f32(1.0), _lib.f32(0.0), _lib.p(ws["scratch"]), _lib.i64(ws["scratch"].numel()),
+        len(taps), _lib.p(dw), int(kh * kw), _lib.f32(1.0), _lib.f32(0.0), _lib.p(ws[scratch]), _lib.i64(ws[scratch].numel()),
         _lib.stream()), "ddl_conv_wgrad")
     return dw
+
+
+def _dgrad_and_wgrad(gy, w, x, ph, stride, pad, H, W):
+    """Input and weight gradient of one convolution on two streams: they only share inputs, so the weight-gradient
+    kernels run on a side stream (a parallel branch when the step is captured into a CUDA graph) and leave the
+    backward critical path; both streams are joined before returning."""
+    ws = _workspace(gy.device)
+    main, side = torch.cuda.current_stream(), ws["side"]
+    gw = torch.empty(tuple(w.shape), device=gy.device, dtype=torch.float32)
+    side.wait_stream(main)
+    with torch.cuda.stream(side):
+        _wgrad(gy, x, ph, tuple(w.shape), stride, pad, out=gw, scratch="scratch_side")
+    gx = _dgrad(gy, w, stride, pad, H, W)
+    main.wait_stream(side)
+    return gx, gw
 
 
 # ------------------------------------------------------------------------------------------------ conv2d
@@ -164,9 +182,10 @@ def _torch_conv_nhwc(x, w, stride, pad, bias=None):
 
 class _ConvFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w, stride, pad):
+    def forward(ctx, x, w, stride, pad, ph=None):
         x = x.contiguous()
-        ph = _phase_split(x) if stride == 2 else None
+        if stride == 2 and ph is None:
+            ph = _phase_split(x)
         y = _fprop(x, ph, w, stride, pad)
         ctx.save_for_backward(x if stride == 1 else ph, w)
         ctx.cfg = (stride, pad, x.shape[1], x.shape[2])
@@ -178,11 +197,14 @@ class _ConvFn(torch.autograd.Function):
         stride, pad, H, W = ctx.cfg
         gy = gy.contiguous()
         gx = gw = None
-        if ctx.needs_input_grad[0]:
+        xs, phs = (saved, None) if stride == 1 else (None, saved)
+        if ctx.needs_input_grad[0] and ctx.needs_input_grad[1]:
+            gx, gw = _dgrad_and_wgrad(gy, w, xs, phs, stride, pad, H, W)
+        elif ctx.needs_input_grad[0]:
             gx = _dgrad(gy, w, stride, pad, H, W)
-        if ctx.needs_input_grad[1]:
-            gw = _wgrad(gy, saved if stride == 1 else None, saved if stride == 2 else None, tuple(w.shape), stride, pad)
-        return gx, gw, None, None
+        elif ctx.needs_input_grad[1]:
+            gw = _wgrad(gy, xs, phs, tuple(w.shape), stride, pad)
+        return gx, gw, None, None, None
 
 
 def _kernel_ok(x, w, stride):
@@ -192,11 +214,21 @@ def _kernel_ok(x, w, stride):
             and w.shape[1] * w.shape[2] <= 16 and (stride == 1 or (x.shape[1] % 2 == 0 and x.shape[2] % 2 == 0)))
 
 
-def conv2d_nhwc(x: torch.Tensor, w: torch.Tensor, stride: int = 1, padding: int = 0) -> torch.Tensor:
-    """``x`` [N,H,W,Cin], ``w`` [Cout,kh,kw,Cin] -> [N,Ho,Wo,Cout] (TF32 tensor-core math, fp32 accumulate)."""
+def conv2d_nhwc(x: torch.Tensor, w: torch.Tensor, stride: int = 1, padding: int = 0, phases: torch.Tensor | None = None) -> torch.Tensor:
+    """``x`` [N,H,W,Cin], ``w`` [Cout,kh,kw,Cin] -> [N,Ho,Wo,Cout] (TF32 tensor-core math, fp32 accumulate).
+
+    ``phases``: the result of ``stride2_phases(x)`` when several stride-2 convolutions read the same input."""
     if not _kernel_ok(x, w, stride):
         return _torch_conv_nhwc(x, w, stride, padding)
-    return _ConvFn.apply(x, w, stride, padding)
+    return _ConvFn.apply(x, w, stride, padding, phases)
+
+
+def stride2_phases(x: torch.Tensor) -> torch.Tensor | None:
+    """Even/odd sub-images ``[4, N, H/2, W/2, C]`` of ``x`` (input layout of the stride-2 kernels); None off the kernel path."""
+    if not (x.is_cuda and x.dtype == torch.float32 and x.shape[1] % 2 == 0 and x.shape[2] % 2 == 0 and x.shape[3] % 4 == 0):
+        return None
+    with torch.no_grad():
+        return _phase_split(x.contiguous())
 
 
 # ------------------------------------------------------------------------------------------------ conv_transpose2d
@@ -295,7 +327,8 @@ class _BnFn(torch.autograd.Function):
 
 def batch_norm_nhwc(x, bn: torch.nn.BatchNorm2d, relu: bool = False, residual: torch.Tensor | None = None):
     """``relu?(BatchNorm(x) + residual?)`` for channels-last ``x`` [..., C]; statistics over all leading dims."""
-    kernel = x.is_cuda and x.dtype == torch.float32 and x.shape[-1] % 4 == 0 and bn.track_running_stats and bn.momentum is not None \
+    Cc = x.shape[-1]
+    kernel = x.is_cuda and x.dtype == torch.float32 and (Cc % 128 == 0 or Cc in (4, 8, 16, 32, 64)) and bn.track_running_stats and bn.momentum is not None \
         and (bn.training or not (torch.is_grad_enabled() and x.requires_grad))
     if not kernel:
         Cc = x.shape[-1]

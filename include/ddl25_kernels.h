@@ -240,10 +240,12 @@ int ddl_nvls_allreduce(float* multicast_ptr, int64_t d0, int64_t d1, float scale
  * w_mn_major = 0: forward (reduce over Cin, produce Cout channels); 1: input gradient (reduce over Cout, produce Cin).
  * Output pixel (n, i, j), n < N, i < Hh, j < Ww, is stored at out + o_off + n*o_sn + i*o_sh + j*o_sw (elements):
  * out = act(alpha * conv + beta * out + bias).  act: 0 none, 1 relu, 2 leaky(slope), 3 tanh.
+ * n_phases > 1 (stride-2 input gradient / transposed conv): phase f uses taps [phase_begin[f], phase_begin[f+1]) and adds
+ * phase_off[f] to o_off; all phases run in one launch.  n_phases <= 1: pass NULL for both arrays.
  * Channel counts: multiples of 4, and of 32 when above 32.  scratch (optional) enables split-K on small grids. */
 int ddl_conv_tap_gemm(const float* const* acts, int n_maps, int N, int Ha, int Wa, int Ca, const float* Wt, int Cout, int T, int Cin,
                       int w_mn_major, const int* tap_map, const int* tap_dh, const int* tap_dw, const int* tap_w, int n_taps,
-                      float* out, int Hh, int Ww, int64_t o_off, int64_t o_sn, int64_t o_sh, int64_t o_sw, const float* bias,
+                      int n_phases, const int* phase_begin, const int64_t* phase_off, float* out, int Hh, int Ww, int64_t o_off, int64_t o_sn, int64_t o_sh, int64_t o_sw, const float* bias,
                       float alpha, float beta, int act, float slope, float* scratch, int64_t scratch_floats, void* stream);
 /* dW[co, tap_w[t], ci] = alpha * sum_{n,i,j} dY[n,i,j,co] * X_{tap_map[t]}[n, i+dh, j+dw, ci] + beta * dW   (dY: [N,Ho,Wo,Cout]) */
 int ddl_conv_wgrad(const float* dY, int N, int Ho, int Wo, int Cout, const float* const* xs, int n_maps, int Hx, int Wx, int Cin,
