@@ -6,8 +6,10 @@ Arms (same model, same data, same fused optimizer kernel):
   fused : DataParallel + SymmetricGradReducer  - bucketed all-reduce by the peer-memory kernel, overlapped with backward
   nccl  : DataParallel with torch.distributed all_reduce per bucket (async)              - "the baseline, not the product"
   ddp   : torch.nn.parallel.DistributedDataParallel + torch.optim.SGD                    - stock PyTorch
-ResNet-18's convolutions run through ATen/cuDNN here (they are not on a path the north star names for a
-hand-written kernel); what is measured is the communication design.  Device-timed, max over ranks."""
+  --model nhwc  : models/resnet_nhwc.py - channels-last tcgen05 tap-GEMM convolutions, fused NHWC BatchNorm (default)
+  --model aten  : models/resnet.py      - ATen/cuDNN (TF32) convolutions
+  --graph       : forward + backward replayed from a CUDA graph (fused / nccl arms)
+Device-timed, max over ranks."""
 import argparse, json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -20,8 +22,13 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--model", default="nhwc", choices=["nhwc", "aten"])
+    ap.add_argument("--graph", action="store_true")
     a = ap.parse_args()
-    from ddl25spring_b200.models.resnet import resnet18
+    if a.model == "nhwc":
+        from ddl25spring_b200.models.resnet_nhwc import resnet18_nhwc as resnet18
+    else:
+        from ddl25spring_b200.models.resnet import resnet18
     from ddl25spring_b200.parallel.dp import DataParallel
     from ddl25spring_b200.utils.timing import max_over_ranks
     world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0"))
@@ -32,7 +39,8 @@ def main():
     x = torch.randn(a.batch, 3, 32, 32, generator=g).cuda()
     y = torch.randint(0, 10, (a.batch,), generator=g).cuda()
     loss_fn = lambda m, xb, yb: F.cross_entropy(m(xb), yb)
-    out = {"world": world, "per_gpu_batch": a.batch, "model": "ResNet-18 (11.18M params)", "samples_per_s": {}, "ms_per_step": {}}
+    out = {"world": world, "per_gpu_batch": a.batch, "model": "ResNet-18 (11.18M params)", "convs": a.model, "graph": a.graph,
+           "samples_per_s": {}, "ms_per_step": {}}
 
     def run(step):
         for _ in range(a.warmup):
@@ -65,7 +73,7 @@ def main():
                 from ddl25spring_b200.parallel.symm_impl import SymmetricArena, SymmetricGradReducer
                 arena = SymmetricArena()
                 reducer = SymmetricGradReducer(arena, sum(p.numel() for p in model.parameters()) + 4096)
-            dp = DataParallel(model, bucket_mb=8.0, optimizer="sgd", lr=0.05, reducer=reducer)
+            dp = DataParallel(model, bucket_mb=8.0, optimizer="sgd", lr=0.05, reducer=reducer, graph=a.graph)
             step = lambda: dp.train_step(loss_fn, x, y)
         ms = run(step)
         out["ms_per_step"][arm] = round(ms, 3)

@@ -133,7 +133,7 @@ def main():
                 dx = torch.empty_like(xb); dg = torch.empty_like(mean); db = torch.empty_like(mean)
                 _lib.check(L.ddl_bn_nhwc_bwd(_lib.p(xb), _lib.p(yb), _lib.p(gb), _lib.p(dx), None, _lib.p(mean), _lib.p(rstd), _lib.p(bn.weight),
                                              _lib.p(dg), _lib.p(db), _lib.p(ws["bn_partial"]), _lib.p(ws["bn_counters"]), _lib.i64(R_), int(C_), 1,
-                                             _lib.stream()))
+                                             _lib.f32(0.0), _lib.stream()))
                 return dx
 
             xn = xb.view(-1, 1, 1, C_).permute(0, 3, 1, 2)

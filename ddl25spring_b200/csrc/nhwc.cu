@@ -3,7 +3,7 @@
 //
 //   bn_stats      per-channel sum / sum of squares in ordered partials; the last CTA of a channel group turns them into
 //                 mean / rstd and updates the running statistics (one launch, deterministic)
-//   bn_apply      y = act((x - mean) * rstd * gamma + beta [+ residual])         (BatchNorm + ReLU + shortcut add fused)
+//   bn_apply      y = act((x - mean) * rstd * gamma + beta [+ residual])         (BatchNorm + ReLU/LeakyReLU + shortcut add fused)
 //   bn_bwd_reduce dz = dy * [y > 0];  dbeta = sum dz, dgamma = sum dz * xhat      (same partial scheme)
 //   bn_bwd_apply  dx = gamma * rstd * (dz - dbeta/R - xhat * dgamma/R);  dres = dz
 //   phase_split   the four even/odd sub-images of x (input of a stride-2 convolution)
@@ -142,7 +142,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_stats_kernel(const float* __res
 __global__ void __launch_bounds__(256) bn_apply_kernel(const float4* __restrict__ x, const float4* __restrict__ res, float4* __restrict__ y,
                                                        const float* __restrict__ mean, const float* __restrict__ rstd,
                                                        const float* __restrict__ gamma, const float* __restrict__ beta, int64_t total4,
-                                                       int C, int relu) {
+                                                       int C, int relu, float slope) {
   pdl_launch_dependents();
   pdl_wait();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (int64_t)gridDim.x * blockDim.x) {
@@ -154,7 +154,11 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const float4* __restrict_
     o.x = (v.x - m.x) * s.x * g.x + b.x; o.y = (v.y - m.y) * s.y * g.y + b.y;
     o.z = (v.z - m.z) * s.z * g.z + b.z; o.w = (v.w - m.w) * s.w * g.w + b.w;
     if (res) { const float4 r = res[i]; o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w; }
-    if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+    if (relu == 1) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+    else if (relu == 2) {
+      o.x = o.x > 0.f ? o.x : o.x * slope; o.y = o.y > 0.f ? o.y : o.y * slope;
+      o.z = o.z > 0.f ? o.z : o.z * slope; o.w = o.w > 0.f ? o.w : o.w * slope;
+    }
     y[i] = o;
   }
 }
@@ -163,7 +167,8 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(const float* 
                                                                    const float* __restrict__ dy, int64_t R, int C,
                                                                    const float* __restrict__ mean, const float* __restrict__ rstd,
                                                                    float* __restrict__ partial, unsigned* __restrict__ counters,
-                                                                   float* __restrict__ dgamma, float* __restrict__ dbeta, int relu) {
+                                                                   float* __restrict__ dgamma, float* __restrict__ dbeta, int relu,
+                                                                   float slope) {
   pdl_launch_dependents();
   pdl_wait();
   const ColGeom g0 = col_geom(R, C, gridDim.y);
@@ -172,11 +177,12 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(const float* 
   column_partials(R, C, gridDim.y, partial, [&](int64_t r, int c, float4& a, float4& b) {
     float4 g = *reinterpret_cast<const float4*>(dy + r * C + c);
     if (relu) {
+      const float neg = relu == 2 ? slope : 0.f;      // leaky: y and the pre-activation have the same sign
       const float4 o = *reinterpret_cast<const float4*>(y + r * C + c);
-      if (!(o.x > 0.f)) g.x = 0.f;
-      if (!(o.y > 0.f)) g.y = 0.f;
-      if (!(o.z > 0.f)) g.z = 0.f;
-      if (!(o.w > 0.f)) g.w = 0.f;
+      if (!(o.x > 0.f)) g.x *= neg;
+      if (!(o.y > 0.f)) g.y *= neg;
+      if (!(o.z > 0.f)) g.z *= neg;
+      if (!(o.w > 0.f)) g.w *= neg;
     }
     const float4 v = *reinterpret_cast<const float4*>(x + r * C + c);
     add4(a, g);
@@ -195,18 +201,20 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float4* __restr
                                                            const float4* __restrict__ dy, float4* __restrict__ dx, float4* __restrict__ dres,
                                                            const float* __restrict__ mean, const float* __restrict__ rstd,
                                                            const float* __restrict__ gamma, const float* __restrict__ dgamma,
-                                                           const float* __restrict__ dbeta, int64_t total4, int C, float inv_rows, int relu) {
+                                                           const float* __restrict__ dbeta, int64_t total4, int C, float inv_rows, int relu,
+                                                           float slope) {
   pdl_launch_dependents();
   pdl_wait();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)((i * 4) % C);
     float4 g = dy[i];
     if (relu) {
+      const float neg = relu == 2 ? slope : 0.f;
       const float4 o = y[i];
-      if (!(o.x > 0.f)) g.x = 0.f;
-      if (!(o.y > 0.f)) g.y = 0.f;
-      if (!(o.z > 0.f)) g.z = 0.f;
-      if (!(o.w > 0.f)) g.w = 0.f;
+      if (!(o.x > 0.f)) g.x *= neg;
+      if (!(o.y > 0.f)) g.y *= neg;
+      if (!(o.z > 0.f)) g.z *= neg;
+      if (!(o.w > 0.f)) g.w *= neg;
     }
     if (dres) dres[i] = g;
     const float4 v = x[i];
@@ -379,29 +387,29 @@ int ddl_bn_nhwc_stats(const float* x, int64_t R, int C, float* partial, unsigned
 }
 
 int ddl_bn_nhwc_apply(const float* x, const float* res, float* y, const float* mean, const float* rstd, const float* gamma,
-                      const float* beta, int64_t R, int C, int relu, void* stream) {
+                      const float* beta, int64_t R, int C, int relu, float slope, void* stream) {
   DDL_REQUIRE(C % 4 == 0, "bn_nhwc: C %% 4 != 0");
   const int64_t total4 = R * C / 4;
   DDL_CUDA_CHECK(ddl_launch_pdl(bn_apply_kernel, dim3(grid_for(total4, 256)), dim3(256), 0, (cudaStream_t)stream, 
       reinterpret_cast<const float4*>(x), reinterpret_cast<const float4*>(res), reinterpret_cast<float4*>(y), mean, rstd, gamma, beta,
-      total4, C, relu));
+      total4, C, relu, slope));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
 
 int ddl_bn_nhwc_bwd(const float* x, const float* y, const float* dy, float* dx, float* dres, const float* mean, const float* rstd,
                     const float* gamma, float* dgamma, float* dbeta, float* partial, unsigned* counters, int64_t R, int C, int relu,
-                    void* stream) {
+                    float slope, void* stream) {
   DDL_REQUIRE(R > 0 && C > 0 && C % 4 == 0 && (C < 128 || C % 128 == 0) && 256 % (C < 128 ? C / 4 : 32) == 0,
               "bn_nhwc: need rows > 0 and C a multiple of 4 that divides 128 or is a multiple of 128 (C=%d)", C);
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(bn_groups(C), bn_splits(R, C));
-  DDL_CUDA_CHECK(ddl_launch_pdl(bn_bwd_reduce_kernel, dim3(grid), dim3(kBnThreads), 0, st, x, y, dy, R, C, mean, rstd, partial, counters, dgamma, dbeta, relu));
+  DDL_CUDA_CHECK(ddl_launch_pdl(bn_bwd_reduce_kernel, dim3(grid), dim3(kBnThreads), 0, st, x, y, dy, R, C, mean, rstd, partial, counters, dgamma, dbeta, relu, slope));
   DDL_LAUNCH_CHECK();
   const int64_t total4 = R * C / 4;
   DDL_CUDA_CHECK(ddl_launch_pdl(bn_bwd_apply_kernel, dim3(grid_for(total4, 256)), dim3(256), 0, st, 
       reinterpret_cast<const float4*>(x), reinterpret_cast<const float4*>(y), reinterpret_cast<const float4*>(dy),
-      reinterpret_cast<float4*>(dx), reinterpret_cast<float4*>(dres), mean, rstd, gamma, dgamma, dbeta, total4, C, 1.f / (float)R, relu));
+      reinterpret_cast<float4*>(dx), reinterpret_cast<float4*>(dres), mean, rstd, gamma, dgamma, dbeta, total4, C, 1.f / (float)R, relu, slope));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

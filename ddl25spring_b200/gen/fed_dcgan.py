@@ -20,8 +20,12 @@ from ..models.dcgan import Discriminator, Generator
 
 
 class DCGANPair:
-    def __init__(self, device, nz=100, ngf=64, ndf=64):
-        self.G, self.D = Generator(nz, ngf).to(device), Discriminator(ndf).to(device)
+    def __init__(self, device, nz=100, ngf=64, ndf=64, kernel_convs: bool = False):
+        if kernel_convs:      # channels-last tcgen05 (transposed) convolutions + fused NHWC BatchNorm (models/dcgan_nhwc.py)
+            from ..models.dcgan_nhwc import DiscriminatorNHWC, GeneratorNHWC
+            self.G, self.D = GeneratorNHWC(nz, ngf).to(device), DiscriminatorNHWC(ndf).to(device)
+        else:
+            self.G, self.D = Generator(nz, ngf).to(device), Discriminator(ndf).to(device)
         self.ga = FlatArena.from_module(self.G, include_buffers=True, with_grad=True)
         self.da = FlatArena.from_module(self.D, include_buffers=True, with_grad=True)
         self.nz, self.device = nz, device
@@ -63,7 +67,7 @@ def _pad4(n: int) -> int:
 
 class FederatedDCGAN:
     def __init__(self, client_images: list[torch.Tensor], client_fraction: float = 1.0, local_steps: int = 2, batch_size: int = 16,
-                 lr: float = 2e-4, seed: int = 0, device=None, ngf: int = 64, ndf: int = 64):
+                 lr: float = 2e-4, seed: int = 0, device=None, ngf: int = 64, ndf: int = 64, kernel_convs: bool | None = None):
         self.device = torch.device(device) if device is not None else torch.device("cuda" if torch.cuda.is_available() else "cpu")
         self.clients = client_images
         self.counts = [len(c) for c in client_images]
@@ -71,8 +75,11 @@ class FederatedDCGAN:
         self.local_steps, self.batch, self.lr, self.seed = local_steps, batch_size, lr, seed
         self.rng = np.random.default_rng(seed)
         torch.manual_seed(seed)
-        self.glob = DCGANPair(self.device, ngf=ngf, ndf=ndf)
-        self.work = DCGANPair(self.device, ngf=ngf, ndf=ndf)
+        if kernel_convs is None:
+            kernel_convs = self.device.type == "cuda"
+        self.kernel_convs = kernel_convs
+        self.glob = DCGANPair(self.device, ngf=ngf, ndf=ndf, kernel_convs=kernel_convs)
+        self.work = DCGANPair(self.device, ngf=ngf, ndf=ndf, kernel_convs=kernel_convs)
         self.rank, self.world = (dist.get_rank(), dist.get_world_size()) if dist.is_initialized() else (0, 1)
         pg, pd = self.glob.n_param_elems()
         z = lambda n: torch.zeros(_pad4(n), device=self.device)

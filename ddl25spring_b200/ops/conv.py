@@ -182,20 +182,20 @@ def _torch_conv_nhwc(x, w, stride, pad, bias=None):
 
 class _ConvFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w, stride, pad, ph=None):
+    def forward(ctx, x, w, stride, pad, ph=None, act=None, slope=0.2):
         x = x.contiguous()
         if stride == 2 and ph is None:
             ph = _phase_split(x)
-        y = _fprop(x, ph, w, stride, pad)
-        ctx.save_for_backward(x if stride == 1 else ph, w)
-        ctx.cfg = (stride, pad, x.shape[1], x.shape[2])
+        y = _fprop(x, ph, w, stride, pad, act=act, slope=slope)
+        ctx.save_for_backward(x if stride == 1 else ph, w, y if act is not None else None)
+        ctx.cfg = (stride, pad, x.shape[1], x.shape[2], act, slope)
         return y
 
     @staticmethod
     def backward(ctx, gy):
-        saved, w = ctx.saved_tensors
-        stride, pad, H, W = ctx.cfg
-        gy = gy.contiguous()
+        saved, w, y = ctx.saved_tensors
+        stride, pad, H, W, act, slope = ctx.cfg
+        gy = _act_backward(gy.contiguous(), y, act, slope)
         gx = gw = None
         xs, phs = (saved, None) if stride == 1 else (None, saved)
         if ctx.needs_input_grad[0] and ctx.needs_input_grad[1]:
@@ -204,7 +204,18 @@ class _ConvFn(torch.autograd.Function):
             gx = _dgrad(gy, w, stride, pad, H, W)
         elif ctx.needs_input_grad[1]:
             gw = _wgrad(gy, xs, phs, tuple(w.shape), stride, pad)
-        return gx, gw, None, None, None
+        return gx, gw, None, None, None, None, None
+
+
+def _act_backward(gy, y, act, slope):
+    """Gradient through the epilogue activation, from the saved OUTPUT y."""
+    if act == "relu":
+        return gy * (y > 0)
+    if act == "leaky_relu":
+        return torch.where(y > 0, gy, gy * slope)
+    if act == "tanh":
+        return gy * (1 - y * y)
+    return gy
 
 
 def _kernel_ok(x, w, stride):
@@ -214,13 +225,15 @@ def _kernel_ok(x, w, stride):
             and w.shape[1] * w.shape[2] <= 16 and (stride == 1 or (x.shape[1] % 2 == 0 and x.shape[2] % 2 == 0)))
 
 
-def conv2d_nhwc(x: torch.Tensor, w: torch.Tensor, stride: int = 1, padding: int = 0, phases: torch.Tensor | None = None) -> torch.Tensor:
+def conv2d_nhwc(x: torch.Tensor, w: torch.Tensor, stride: int = 1, padding: int = 0, phases: torch.Tensor | None = None,
+                act: str | None = None, slope: float = 0.2) -> torch.Tensor:
     """``x`` [N,H,W,Cin], ``w`` [Cout,kh,kw,Cin] -> [N,Ho,Wo,Cout] (TF32 tensor-core math, fp32 accumulate).
 
     ``phases``: the result of ``stride2_phases(x)`` when several stride-2 convolutions read the same input."""
     if not _kernel_ok(x, w, stride):
-        return _torch_conv_nhwc(x, w, stride, padding)
-    return _ConvFn.apply(x, w, stride, padding, phases)
+        y = _torch_conv_nhwc(x, w, stride, padding)
+        return {"relu": F.relu, "leaky_relu": lambda t: F.leaky_relu(t, slope), "tanh": torch.tanh, None: lambda t: t}[act](y)
+    return _ConvFn.apply(x, w, stride, padding, phases, act, slope)
 
 
 def stride2_phases(x: torch.Tensor) -> torch.Tensor | None:
@@ -250,13 +263,7 @@ class _ConvTFn(torch.autograd.Function):
     def backward(ctx, gy):
         x, w, y = ctx.saved_tensors
         stride, pad, act, slope, has_bias = ctx.cfg
-        gy = gy.contiguous()
-        if act == "relu":
-            gy = gy * (y > 0)
-        elif act == "leaky_relu":
-            gy = torch.where(y > 0, gy, gy * slope)
-        elif act == "tanh":
-            gy = gy * (1 - y * y)
+        gy = _act_backward(gy.contiguous(), y, act, slope)
         ph = _phase_split(gy) if stride == 2 else None
         gx = gw = gb = None
         if ctx.needs_input_grad[0]:
@@ -286,7 +293,7 @@ def conv_transpose2d_nhwc(x, w, bias=None, stride: int = 2, padding: int = 1, ac
 # ------------------------------------------------------------------------------------------------ BatchNorm (+ReLU +residual)
 class _BnFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, res, run_mean, run_var, n_tracked, training, momentum, eps, relu):
+    def forward(ctx, x, gamma, beta, res, run_mean, run_var, n_tracked, training, momentum, eps, relu, slope=0.0):
         x = x.contiguous()
         Cc = x.shape[-1]
         R = x.numel() // Cc
@@ -304,15 +311,15 @@ class _BnFn(torch.autograd.Function):
         y = torch.empty_like(x)
         resc = res.contiguous() if res is not None else None
         _lib.check(L.ddl_bn_nhwc_apply(_lib.p(x), _lib.p(resc), _lib.p(y), _lib.p(mean), _lib.p(rstd), _lib.p(gamma), _lib.p(beta),
-                                       _lib.i64(R), int(Cc), int(relu), _lib.stream()), "ddl_bn_nhwc_apply")
+                                       _lib.i64(R), int(Cc), int(relu), _lib.f32(slope), _lib.stream()), "ddl_bn_nhwc_apply")
         ctx.save_for_backward(x, y, gamma, mean, rstd)
-        ctx.cfg = (R, Cc, relu, res is not None, training)
+        ctx.cfg = (R, Cc, relu, res is not None, training, slope)
         return y
 
     @staticmethod
     def backward(ctx, gy):
         x, y, gamma, mean, rstd = ctx.saved_tensors
-        R, Cc, relu, has_res, training = ctx.cfg
+        R, Cc, relu, has_res, training, slope = ctx.cfg
         assert training, "backward through eval-mode BatchNorm is not on a kernel path"
         gy = gy.contiguous()
         ws = _workspace(x.device)
@@ -321,12 +328,13 @@ class _BnFn(torch.autograd.Function):
         dg, db = torch.empty_like(mean), torch.empty_like(mean)
         _lib.check(_lib.lib().ddl_bn_nhwc_bwd(_lib.p(x), _lib.p(y), _lib.p(gy), _lib.p(dx), _lib.p(dres), _lib.p(mean), _lib.p(rstd),
                                               _lib.p(gamma), _lib.p(dg), _lib.p(db), _lib.p(ws["bn_partial"]), _lib.p(ws["bn_counters"]),
-                                              _lib.i64(R), int(Cc), int(relu), _lib.stream()), "ddl_bn_nhwc_bwd")
-        return dx, dg, db, dres, None, None, None, None, None, None, None
+                                              _lib.i64(R), int(Cc), int(relu), _lib.f32(slope), _lib.stream()), "ddl_bn_nhwc_bwd")
+        return dx, dg, db, dres, None, None, None, None, None, None, None, None
 
 
-def batch_norm_nhwc(x, bn: torch.nn.BatchNorm2d, relu: bool = False, residual: torch.Tensor | None = None):
-    """``relu?(BatchNorm(x) + residual?)`` for channels-last ``x`` [..., C]; statistics over all leading dims."""
+def batch_norm_nhwc(x, bn: torch.nn.BatchNorm2d, relu: bool = False, residual: torch.Tensor | None = None, leaky: float | None = None):
+    """``act(BatchNorm(x) + residual?)`` for channels-last ``x`` [..., C]; statistics over all leading dims.
+    ``relu=True``: ReLU; ``leaky=s``: LeakyReLU(s)."""
     Cc = x.shape[-1]
     kernel = x.is_cuda and x.dtype == torch.float32 and (Cc % 128 == 0 or Cc in (4, 8, 16, 32, 64)) and bn.track_running_stats and bn.momentum is not None \
         and (bn.training or not (torch.is_grad_enabled() and x.requires_grad))
@@ -336,9 +344,11 @@ def batch_norm_nhwc(x, bn: torch.nn.BatchNorm2d, relu: bool = False, residual: t
                          bn.eps).view(x.shape)
         if residual is not None:
             y = y + residual
+        if leaky is not None:
+            return F.leaky_relu(y, leaky)
         return F.relu(y) if relu else y
     return _BnFn.apply(x, bn.weight, bn.bias, residual, bn.running_mean, bn.running_var, bn.num_batches_tracked, bn.training, bn.momentum,
-                       bn.eps, relu)
+                       bn.eps, 2 if leaky is not None else int(relu), float(leaky or 0.0))
 
 
 # ------------------------------------------------------------------------------------------------ pools

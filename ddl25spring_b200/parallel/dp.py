@@ -68,8 +68,12 @@ class DataParallel:
 
     def __init__(self, module: nn.Module, *, bucket_mb: float = 4.0, optimizer: str = "sgd", lr: float = 0.01,
                  weight_decay: float = 0.0, betas=(0.9, 0.999), eps: float = 1e-8, group=None, reducer=None,
-                 overlap: bool = True):
+                 overlap: bool = True, graph: bool = False):
         self.module = module
+        # graph=True: forward + backward of train_step() are captured once into a CUDA graph and replayed (utils/graphs.py);
+        # the bucket reductions and the fused optimizer step are issued right after the replay.
+        self.graph = graph and torch.cuda.is_available()
+        self._gstep = None
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.arena = FlatArena.from_module(module, with_grad=True)
@@ -101,6 +105,8 @@ class DataParallel:
 
     def _make_hook(self, bi: int):
         def hook(_param):
+            if self.graph:                       # captured backward: buckets are reduced after the replay
+                return
             b = self.buckets[bi]
             b.ready += 1
             if b.ready == b.n_params:
@@ -152,6 +158,25 @@ class DataParallel:
         self.zero_grad()
 
     def train_step(self, loss_fn, *batch) -> torch.Tensor:
+        if self.graph:
+            if self._gstep is None:
+                from ..utils.graphs import GraphedStep
+
+                def fwd_bwd(*b):
+                    loss = loss_fn(self.module, *b)
+                    loss.backward()                      # accumulates in place into the (static) flat gradient arena
+                    return loss.detach()
+
+                buffers = [(b, b.clone()) for b in self.module.buffers()]
+                self._gstep = GraphedStep(fwd_bwd, batch)
+                self.arena.grad.zero_()                  # warm-up and capture runs left gradients behind ...
+                with torch.no_grad():
+                    for b, saved in buffers:             # ... and advanced the BatchNorm running statistics
+                        b.copy_(saved)
+            loss = self._gstep(*batch)
+            self.finish()
+            self.step()
+            return loss
         loss = loss_fn(self.module, *batch)
         self.backward(loss)
         self.step()

@@ -260,10 +260,10 @@ int64_t ddl_bn_nhwc_ws_floats(int64_t R, int C);
 int ddl_bn_nhwc_stats(const float* x, int64_t R, int C, float* partial, unsigned* counters, float* mean, float* rstd, float* run_mean,
                       float* run_var, long long* n_tracked, float eps, float momentum, void* stream);
 int ddl_bn_nhwc_apply(const float* x, const float* res, float* y, const float* mean, const float* rstd, const float* gamma,
-                      const float* beta, int64_t R, int C, int relu, void* stream);
+                      const float* beta, int64_t R, int C, int relu /* 0 none, 1 relu, 2 leaky(slope) */, float slope, void* stream);
 int ddl_bn_nhwc_bwd(const float* x, const float* y, const float* dy, float* dx, float* dres, const float* mean, const float* rstd,
                     const float* gamma, float* dgamma, float* dbeta, float* partial, unsigned* counters, int64_t R, int C, int relu,
-                    void* stream);
+                    float slope, void* stream);
 int ddl_phase_split(const float* x, float* ph, int N, int H, int W, int C, void* stream);      /* ph: [4][N,H/2,W/2,C] */
 int ddl_maxpool3x3s2_fwd(const float* x, float* y, unsigned char* code, int N, int H, int W, int C, void* stream);
 int ddl_maxpool3x3s2_bwd(const float* dy, const unsigned char* code, float* dx, int N, int H, int W, int C, void* stream);

@@ -202,3 +202,80 @@ def test_resnet18_nhwc_gpu_training_step_matches_fp32_model():
         assert ours < 1.5 * yard + 2e-2, (name, ours, yard)
     for (n1, b1), (n2, b2) in zip(net.named_buffers(), ref.named_buffers()):
         assert n1 == n2 and torch.allclose(b1.float(), b2.float(), atol=1e-3, rtol=1e-2), n1
+
+
+@pytest.mark.gpu
+def test_graphed_dataparallel_step_matches_eager():
+    """CUDA-graph replay of forward + backward (parallel/dp.py graph=True) trains exactly like the eager step."""
+    from ddl25spring_b200.parallel.dp import DataParallel
+    torch.manual_seed(3)
+    m1, m2 = ResNet18NHWC(10).cuda(), ResNet18NHWC(10).cuda()
+    m2.load_state_dict(m1.state_dict())
+    dp1 = DataParallel(m1, optimizer="sgd", lr=0.05, graph=False)
+    dp2 = DataParallel(m2, optimizer="sgd", lr=0.05, graph=True)
+    loss_fn = lambda m, xb, yb: F.cross_entropy(m(xb), yb)
+    for i in range(4):
+        x = torch.randn(16, 3, 32, 32, device="cuda")
+        y = torch.randint(0, 10, (16,), device="cuda")
+        l1, l2 = dp1.train_step(loss_fn, x, y), dp2.train_step(loss_fn, x, y)
+        assert torch.allclose(l1, l2, atol=1e-5), (i, l1, l2)
+    assert torch.allclose(dp1.arena.flat, dp2.arena.flat, atol=1e-5)
+    for b1, b2 in zip(m1.buffers(), m2.buffers()):
+        assert torch.allclose(b1.float(), b2.float(), atol=1e-5)
+
+
+def _dcgan_pairs(device):
+    from ddl25spring_b200.models import dcgan, dcgan_nhwc
+    torch.manual_seed(5)
+    G, D = dcgan.Generator(100, 32).to(device), dcgan.Discriminator(32).to(device)
+    Gk, Dk = dcgan_nhwc.GeneratorNHWC(100, 32).to(device), dcgan_nhwc.DiscriminatorNHWC(32).to(device)
+    Gk.load_state_dict(dcgan_nhwc.from_torch_layout(G.state_dict(), "G"))
+    Dk.load_state_dict(dcgan_nhwc.from_torch_layout(D.state_dict(), "D"))
+    return G, D, Gk, Dk
+
+
+def test_dcgan_nhwc_matches_nchw_model_on_cpu():
+    G, D, Gk, Dk = _dcgan_pairs("cpu")
+    z = torch.randn(3, 100)
+    img, imgk = G(z), Gk(z)
+    assert img.shape == imgk.shape == (3, 3, 64, 64)
+    assert torch.allclose(img, imgk, atol=1e-5)
+    d, dk = D(img), Dk(imgk)
+    assert torch.allclose(d, dk, atol=1e-4)
+    d.sum().backward(); dk.sum().backward()
+    assert torch.allclose(G.blocks[1][0].weight.grad.permute(0, 2, 3, 1), Gk.blocks[1][0].weight.grad, atol=1e-4)
+    assert torch.allclose(D.blocks[1][0].weight.grad.permute(0, 2, 3, 1), Dk.blocks[1][0].weight.grad, atol=1e-4)
+
+
+@pytest.mark.gpu
+def test_dcgan_nhwc_gpu_forward_backward_vs_fp32():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    G, D, Gk, Dk = _dcgan_pairs("cuda")
+    z = torch.randn(16, 100, device="cuda")
+    img, imgk = G(z), Gk(z)
+    assert _rel(imgk, img) < 1e-2
+    d, dk = D(img.detach()), Dk(img.detach())
+    assert _rel(dk, d) < 2e-2
+    F.binary_cross_entropy_with_logits(D(img), torch.ones(16, device="cuda")).backward()
+    F.binary_cross_entropy_with_logits(Dk(imgk), torch.ones(16, device="cuda")).backward()
+    # TF32 products + ReLU / LeakyReLU mask flips through nine BatchNorm'd layers at batch 16: ~5e-2 relative (cf. the ResNet test)
+    for i in (1, 2, 3):
+        assert _rel(Gk.blocks[i][0].weight.grad, G.blocks[i][0].weight.grad.permute(0, 2, 3, 1)) < 1.5e-1, i
+        assert _rel(Dk.blocks[i][0].weight.grad, D.blocks[i][0].weight.grad.permute(0, 2, 3, 1)) < 1.5e-1, i
+
+
+@pytest.mark.gpu
+def test_federated_dcgan_round_on_kernel_convs():
+    from ddl25spring_b200 import ops
+    from ddl25spring_b200.gen.fed_dcgan import FederatedDCGAN
+    torch.manual_seed(0)
+    clients = [torch.rand(24, 3, 64, 64) * 2 - 1 for _ in range(2)]
+    fed = FederatedDCGAN(clients, client_fraction=1.0, local_steps=2, batch_size=8, device="cuda", ngf=32, ndf=32)
+    assert fed.kernel_convs
+    ops.reset_launch_count()
+    hist = fed.run(2)
+    assert ops.launch_count() > 100                      # the convolutions really ran on the library's kernels
+    assert len(hist) == 2 and all(torch.isfinite(torch.tensor(h)).all() for h in hist)
+    img = fed.sample(4)
+    assert img.shape == (4, 3, 64, 64) and torch.isfinite(img).all() and img.abs().max() <= 1
