@@ -4,7 +4,8 @@ attackers, defended by Krum / coordinate-wise median / trimmed mean.
   [torchrun --nproc-per-node N] python benchmarks/bench_robust_fedavg.py [--rounds 3 --samples 256 --batch 64]
 
 Reports rounds/s, samples/s and the aggregation latency per round (device-timed, max over ranks).  Client-local training
-of ResNet-18 runs through autograd/ATen (its convolutions are not on a named hand-written path); the attack, the robust
+of ResNet-18 runs on the channels-last tcgen05 convolution stack (models/resnet_nhwc.py) with every local SGD step replayed
+from a CUDA graph (--model aten --no-graph: the autograd/ATen/cuDNN path); the attack, the robust
 aggregation (incl. BN running statistics, `include_buffers=True`), the optimizer step and the evaluation count are this
 framework's kernels; across GPUs the aggregation is the fused peer-memory kernel."""
 import argparse, json, os, sys, time
@@ -21,12 +22,17 @@ def main():
     ap.add_argument("--samples", type=int, default=256, help="samples per client")
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--aggregators", default="mean,krum,median,trimmed_mean")
+    ap.add_argument("--model", default="nhwc", choices=["nhwc", "aten"])
+    ap.add_argument("--no-graph", action="store_true")
     a = ap.parse_args()
     from ddl25spring_b200.core.data import SyntheticCIFAR, split
     from ddl25spring_b200.fl.aggregators import make_aggregator
     from ddl25spring_b200.fl.attacks import SignFlip, choose_malicious
     from ddl25spring_b200.fl.server import FedAvgServer
-    from ddl25spring_b200.models.resnet import resnet18
+    if a.model == "nhwc":
+        from ddl25spring_b200.models.resnet_nhwc import resnet18_nhwc as resnet18
+    else:
+        from ddl25spring_b200.models.resnet import resnet18
     from ddl25spring_b200.utils.timing import max_over_ranks
     world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0"))
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
@@ -37,11 +43,11 @@ def main():
     subsets = split(ds.train, K, True, 1)
     mal = choose_malicious(K, 0.2, 0)
     coll = None
-    out = {"world": world, "clients_per_round": K, "attackers": int(mal.sum()), "model": "ResNet-18", "samples_per_client": a.samples, "results": {}}
+    out = {"world": world, "clients_per_round": K, "attackers": int(mal.sum()), "model": "ResNet-18", "convs": a.model, "graph": not a.no_graph, "samples_per_client": a.samples, "results": {}}
     for name in a.aggregators.split(","):
         kw = dict(n_byzantine=int(mal.sum()), multi=K - 2 * int(mal.sum())) if name == "krum" else {}
         srv = FedAvgServer(0.05, a.batch, subsets, 1.0, 1, 10, model_fn=resnet18, test_set=ds.test, device="cuda",
-                           loss_fn=lambda o, t: F.cross_entropy(o, t), include_buffers=True,
+                           loss_fn=F.cross_entropy, include_buffers=True, graph=not a.no_graph,
                            aggregator=make_aggregator(name, **kw), attack=SignFlip(4.0), malicious=mal, test_batch_size=1000)
         if world > 1:
             if coll is None:

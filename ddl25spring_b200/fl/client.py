@@ -53,10 +53,39 @@ def cross_entropy(output: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
 class ModelSlot:
     """A model whose parameters (and optionally float buffers) live in one flat arena."""
 
-    def __init__(self, model_fn: Callable[[], nn.Module], device, include_buffers: bool = False):
+    def __init__(self, model_fn: Callable[[], nn.Module], device, include_buffers: bool = False, graph: bool = False):
         self.model = model_fn().to(device)
         self.arena = FlatArena.from_module(self.model, include_buffers=include_buffers, with_grad=True)
         self.device = torch.device(device)
+        # graph=True: a full local SGD step (zero grads, forward, backward, fused SGD) is captured once per batch shape
+        # into a CUDA graph and replayed for every client that borrows this slot (utils/graphs.py)
+        self.graph = graph and self.device.type == "cuda"
+        self._graphs: dict = {}
+
+    def sgd_step_graphed(self, loss_fn, lr: float, data: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        from ..utils.graphs import GraphedStep
+        key = (tuple(data.shape), tuple(target.shape), float(lr), loss_fn)
+        g = self._graphs.get(key)
+        if g is None:
+            saved = self.arena.flat.detach().clone()
+            buffers = [(b, b.clone()) for b in self.model.buffers()]
+            n = self.arena.size
+
+            def step(x, y):
+                self.zero_grad()
+                loss = loss_fn(self.model(x), y)
+                loss.backward()
+                with torch.no_grad():
+                    ops.sgd_step(self.arena.flat[:n], self.arena.grad[:n], lr)
+                return loss.detach()
+
+            g = GraphedStep(step, (data, target))
+            with torch.no_grad():                 # undo the warm-up / capture steps
+                self.arena.flat.copy_(saved)
+                for b, v in buffers:
+                    b.copy_(v)
+            self._graphs[key] = g
+        return g(data, target)
 
     @property
     def flat(self) -> torch.Tensor:
@@ -171,6 +200,9 @@ class WeightClient(Client):
         n_params = slot.arena.size
         for perm in epoch_permutations(self.n, seed, self.nr_epochs):
             for data, target in self.batches(perm):
+                if slot.graph and len(target) == self.batch_size:
+                    slot.sgd_step_graphed(self.loss_fn, self.lr, data, target)
+                    continue
                 slot.zero_grad()
                 self.loss_fn(slot.model(data), target).backward()
                 with torch.no_grad():

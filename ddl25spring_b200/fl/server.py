@@ -71,13 +71,14 @@ class _RoundTimer:
 class Server(ABC):
     def __init__(self, lr: float, batch_size: int, seed: int, *, model_fn: Callable[[], nn.Module] = MnistCnn,
                  test_set=None, device=None, include_buffers: bool = False, test_batch_size: int = 10_000,
-                 loss_fn=nll_of_log_probs) -> None:
+                 loss_fn=nll_of_log_probs, graph: bool = False) -> None:
         self.clients: list[Client] = []
         self.lr, self.batch_size, self.seed = lr, batch_size, seed
         self.device = torch.device(device) if device is not None else default_device()
         self.model_fn = model_fn
         self.loss_fn = loss_fn                       # nll for log-prob models (MnistCnn), cross-entropy for logit models
         self.include_buffers = include_buffers
+        self.graph = graph                           # replay each local SGD step from a CUDA graph (ModelSlot.sgd_step_graphed)
         torch.manual_seed(seed)                      # global-model init is seeded (hfl_complete.py:165)
         self.slot = ModelSlot(model_fn, self.device, include_buffers=include_buffers)
         self.model = self.slot.model
@@ -169,7 +170,7 @@ class DecentralizedServer(Server):
         self.rank, self.world = (dist.get_rank(), dist.get_world_size()) if _dist_ready() else (0, 1)
         # one borrowed model slot for all of this rank's clients (they train one after another here;
         # the packed engine in fl/packed.py trains them concurrently with grouped kernels)
-        self.worker_slot = ModelSlot(self.model_fn, self.device, include_buffers=self.include_buffers)
+        self.worker_slot = ModelSlot(self.model_fn, self.device, include_buffers=self.include_buffers, graph=self.graph)
         self._updates: torch.Tensor | None = None
         # parallel.symm_impl.SymmetricAggregator(row_elems=arena.size): fused peer-memory aggregation across ranks
         self.collective = collective

@@ -279,3 +279,22 @@ def test_federated_dcgan_round_on_kernel_convs():
     assert len(hist) == 2 and all(torch.isfinite(torch.tensor(h)).all() for h in hist)
     img = fed.sample(4)
     assert img.shape == (4, 3, 64, 64) and torch.isfinite(img).all() and img.abs().max() <= 1
+
+
+@pytest.mark.gpu
+def test_fedavg_resnet_nhwc_graphed_clients_match_eager():
+    """Generic FedAvg server, ResNet-18 on the NHWC kernels: local SGD steps replayed from a CUDA graph == eager steps."""
+    from ddl25spring_b200.core.data import SyntheticCIFAR, split
+    from ddl25spring_b200.fl.server import FedAvgServer
+    from ddl25spring_b200.models.resnet_nhwc import resnet18_nhwc
+    ds = SyntheticCIFAR(n_train=96, n_test=64, seed=0)
+    subsets = split(ds.train, 3, True, 1)
+    flats = []
+    for graph in (False, True):
+        srv = FedAvgServer(0.05, 16, subsets, 1.0, 1, 10, model_fn=resnet18_nhwc, test_set=ds.test, device="cuda",
+                           loss_fn=F.cross_entropy, include_buffers=True, graph=graph, test_batch_size=64)
+        res = srv.run(2)
+        assert len(res.test_accuracy) == 2
+        flats.append(srv.arena.flat.detach().clone())
+    assert torch.isfinite(flats[0]).all()
+    assert torch.allclose(flats[0], flats[1], atol=1e-5), (flats[0] - flats[1]).abs().max()
