@@ -70,23 +70,27 @@ struct GatherMaps {
   int rows_per_part;
 };
 
-template <int BN, int EB /*element bytes*/, bool SPLIT3>
+// SHORT: GEMMs whose K loop is only a few k-blocks long but whose grid is several waves (the per-client fc1 input- and
+// weight-gradient GEMMs of the packed engine: K = 100..128, 576 tiles) spend their time in prologue and epilogue, so the
+// ring is cut to two stages (<= 98 KB) and two CTAs share an SM: one's epilogue runs under the other's loads.
+template <int BN, int EB /*element bytes*/, bool SPLIT3, bool SHORT = false>
 struct SmemPlan {
   static constexpr int A_BYTES = BM * ROW_BYTES;
   static constexpr int B_BYTES = BN * ROW_BYTES;
   static constexpr int STAGE_BYTES = (A_BYTES + B_BYTES) * (SPLIT3 ? 2 : 1);
-  static constexpr int BUDGET = 200 * 1024;
+  static constexpr int BUDGET = SHORT ? 98 * 1024 : 200 * 1024;
   static constexpr int RAW_STAGES = BUDGET / STAGE_BYTES;
   static constexpr int STAGES = RAW_STAGES > 8 ? 8 : RAW_STAGES;
+  static_assert(STAGES >= 1, "tile does not fit the shared-memory budget");
   static constexpr int BAR_BYTES = 1024;
   static constexpr int TOTAL = STAGES * STAGE_BYTES + BAR_BYTES + 1024 /*alignment slack*/;
 };
 
-template <int BN, int EB, bool A_MN, bool B_MN, bool SPLIT3, bool GATHER>
+template <int BN, int EB, bool A_MN, bool B_MN, bool SPLIT3, bool GATHER, bool SHORT = false>
 __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, const CUtensorMap& tma_b, const GatherMaps* gm,
                                                   const Epilogue& epi, const int M, const int N, const int K,
                                                   const int kblocks_per_split) {
-  using Plan = SmemPlan<BN, EB, SPLIT3>;
+  using Plan = SmemPlan<BN, EB, SPLIT3, SHORT>;
   constexpr int STAGES = Plan::STAGES;
   constexpr int BK = ROW_BYTES / EB;         // elements per k-block (32 tf32 / 64 bf16)
   constexpr int UMMA_K = 32 / EB;            // elements per MMA instruction along K (8 tf32 / 16 bf16)
@@ -134,6 +138,8 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
   __syncthreads();
   fence_after_thread_sync();
   const uint32_t tmem_acc = *tmem_slot;
+  pdl_launch_dependents();     // programmatic dependent launch (common.cuh): the successor may set up now ...
+  pdl_wait();                  // ... and this kernel reads / writes global memory only after its predecessor completed
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -358,6 +364,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
   gemm_tcgen05_body<BN, EB, A_MN, B_MN, SPLIT3, false>(tma_a, tma_b, nullptr, epi, M, N, K, kblocks_per_split);
 }
 
+template <int BN, bool A_MN, bool B_MN, bool SPLIT3>
+__global__ void __launch_bounds__(kThreads, 2)
+gemm_tcgen05_short_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                          const Epilogue epi, const int M, const int N, const int K, const int kblocks_per_split) {
+  gemm_tcgen05_body<BN, 4, A_MN, B_MN, SPLIT3, false, true>(tma_a, tma_b, nullptr, epi, M, N, K, kblocks_per_split);
+}
+
 template <int BN, bool SPLIT3>
 __global__ void __launch_bounds__(kThreads, 1)
 gather_gemm_tcgen05_kernel(const __grid_constant__ GatherMaps gm, const __grid_constant__ CUtensorMap tma_b,
@@ -370,6 +383,8 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restr
                                                             int64_t group_elems /*M*N*/, int G, int N, float* __restrict__ C,
                                                             int64_t ldc, int64_t c_group_stride, const float* __restrict__ bias,
                                                             int64_t bias_group_stride, int act, float slope) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int64_t total = group_elems * G;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     float acc = 0.f;
@@ -420,9 +435,35 @@ int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const Epilogue& ep
     configured = true;
   }
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, G * n_split);
-  kern<<<grid, kThreads, Plan::TOTAL, st>>>(ta, tb, epi, M, N, K, kb_per_split);
+  DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kThreads), Plan::TOTAL, st, ta, tb, epi, M, N, K, kb_per_split));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
+}
+
+template <int BN, bool A_MN, bool B_MN, bool SPLIT3>
+int launch_gemm_short(const CUtensorMap& ta, const CUtensorMap& tb, const Epilogue& epi, int M, int N, int K, int G, cudaStream_t st) {
+  using Plan = SmemPlan<BN, 4, SPLIT3, true>;
+  auto kern = gemm_tcgen05_short_kernel<BN, A_MN, B_MN, SPLIT3>;
+  static bool configured = false;
+  if (!configured) {
+    DDL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Plan::TOTAL));
+    configured = true;
+  }
+  dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, G);
+  DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kThreads), Plan::TOTAL, st, ta, tb, epi, M, N, K, (K + 31) / 32));
+  DDL_LAUNCH_CHECK();
+  return DDL_OK;
+}
+
+// short-K fp32 GEMMs with many tiles: BN = 64 (3xTF32) or 128 (TF32), two CTAs per SM
+template <bool SPLIT3>
+int dispatch_short(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const Epilogue& epi, int M, int N, int K, int G,
+                   cudaStream_t st) {
+  constexpr int BN = SPLIT3 ? 64 : 128;
+  if (!a_mn && !b_mn) return launch_gemm_short<BN, false, false, SPLIT3>(ta, tb, epi, M, N, K, G, st);
+  if (!a_mn && b_mn) return launch_gemm_short<BN, false, true, SPLIT3>(ta, tb, epi, M, N, K, G, st);
+  if (a_mn && !b_mn) return launch_gemm_short<BN, true, false, SPLIT3>(ta, tb, epi, M, N, K, G, st);
+  return launch_gemm_short<BN, true, true, SPLIT3>(ta, tb, epi, M, N, K, G, st);
 }
 
 template <int BN, int EB, bool SPLIT3>
@@ -462,7 +503,12 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
   const int kbps = (total_kb + n_split - 1) / n_split;
   n_split = (total_kb + kbps - 1) / kbps;
 
-  const int BN = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
+  int BN = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
+  // short K, several waves of tiles, no split: prologue/epilogue-bound -> two co-resident CTAs per SM (see SmemPlan)
+  const int short_bn = precise ? 64 : 128;
+  const bool use_short = eb == 4 && n_split == 1 && total_kb <= 6 && N >= short_bn &&
+                         (int64_t)((M + BM - 1) / BM) * ((N + short_bn - 1) / short_bn) * G >= 2 * kNumSMs;
+  if (use_short) BN = short_bn;
   if (a_mn_major) DDL_REQUIRE(M % bk == 0, "MN-major A needs M %% %d == 0", bk);
   if (b_mn_major) DDL_REQUIRE(N % bk == 0, "MN-major B needs N %% %d == 0", bk);
 
@@ -482,6 +528,10 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
   cudaStream_t st = (cudaStream_t)stream;
   int rc;
   const bool amn = a_mn_major != 0, bmn = b_mn_major != 0;
+  if (use_short) {
+    epi.same_ab = 0;
+    return precise ? dispatch_short<true>(amn, bmn, ta, tb, epi, M, N, K, G, st) : dispatch_short<false>(amn, bmn, ta, tb, epi, M, N, K, G, st);
+  }
 #define DDL_GEMM_CASE(BN_)                                                                                     \
   if (eb == 4 && precise) rc = dispatch_major<BN_, 4, true>(amn, bmn, ta, tb, epi, M, N, K, G, n_split, kbps, st);   \
   else if (eb == 4) rc = dispatch_major<BN_, 4, false>(amn, bmn, ta, tb, epi, M, N, K, G, n_split, kbps, st);        \
@@ -495,8 +545,8 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
     const int64_t ge = (int64_t)M * N;
     int64_t blocks = (ge * G + 255) / 256;
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    splitk_reduce_kernel<<<(int)blocks, 256, 0, st>>>(scratch, n_split, ge, G, N, C, ldc, c_group_stride, bias,
-                                                      bias_group_stride, act, slope);
+    DDL_CUDA_CHECK(ddl_launch_pdl(splitk_reduce_kernel, dim3((unsigned)blocks), dim3(256), 0, st, scratch, n_split, ge, G, N, C, ldc,
+                                  c_group_stride, bias, bias_group_stride, act, slope));
     DDL_LAUNCH_CHECK();
   }
   return DDL_OK;

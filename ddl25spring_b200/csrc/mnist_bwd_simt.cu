@@ -24,6 +24,8 @@ constexpr int CH_PITCH = 145;   // padded channel stride of the staged pooled-gr
 __global__ void __launch_bounds__(256) pool_relu_bwd_kernel(const float* __restrict__ dpool, const uint8_t* __restrict__ pmask,
                                                             float* __restrict__ dy2, float* __restrict__ c2b_part,
                                                             const StepInfo si) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float s_dp[C2 * CH_PITCH];
   __shared__ uint8_t s_mk[C2 * CH_PITCH];
   __shared__ float s_red[8 * C2];
@@ -83,6 +85,8 @@ __global__ void __launch_bounds__(256) conv1_wgrad_kernel(const float* __restric
                                                           const int* __restrict__ perm, int64_t perm_stride, int sample_off,
                                                           const float* __restrict__ da1, float* __restrict__ c1_part,
                                                           const StepInfo si) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float img[IMG * IMG];
   __shared__ float s_red[256 * 41];
   const int row = blockIdx.x;
@@ -141,6 +145,8 @@ __global__ void __launch_bounds__(256) small_update_kernel(float* __restrict__ W
                                                            const float* __restrict__ c2b_part, const float* __restrict__ c1_part,
                                                            float* __restrict__ wt_fwd, float* __restrict__ wt_dgrad,
                                                            const StepInfo si) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int g = blockIdx.y;
   const int n = si.bsz[g];
   float* Wg = W + (int64_t)g * P;
@@ -195,7 +201,7 @@ int ddl_mnist_pool_bwd(const float* dpool, const uint8_t* pmask, float* dy2, flo
                        const int* bsz, float p_drop, void* stream) {
   DDL_REQUIRE(G >= 1 && G <= MAX_G, "G=%d outside [1, %d]", G, MAX_G);
   StepInfo si = make_step(G, B, bsz, 0, p_drop, 0.f, 0.f);
-  pool_relu_bwd_kernel<<<G * B, 256, 0, (cudaStream_t)stream>>>(dpool, pmask, dy2, c2b_part, si);
+  DDL_CUDA_CHECK(ddl_launch_pdl(pool_relu_bwd_kernel, dim3(G * B), dim3(256), 0, (cudaStream_t)stream, dpool, pmask, dy2, c2b_part, si));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -204,7 +210,7 @@ int ddl_mnist_conv1_wgrad(const float* X, int64_t x_client_stride, const int* pe
                           const float* da1, float* c1_part, int G, int B, const int* bsz, void* stream) {
   DDL_REQUIRE(G >= 1 && G <= MAX_G, "G=%d outside [1, %d]", G, MAX_G);
   StepInfo si = make_step(G, B, bsz, 0, 0.f, 0.f, 0.f);
-  conv1_wgrad_kernel<<<G * B, 256, 0, (cudaStream_t)stream>>>(X, x_client_stride, perm, perm_stride, sample_off, da1, c1_part, si);
+  DDL_CUDA_CHECK(ddl_launch_pdl(conv1_wgrad_kernel, dim3(G * B), dim3(256), 0, (cudaStream_t)stream, X, x_client_stride, perm, perm_stride, sample_off, da1, c1_part, si));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -214,7 +220,7 @@ int ddl_mnist_small_update(float* W, const float* wg_part, int n_cta, const floa
   DDL_REQUIRE(G >= 1 && G <= MAX_G, "G=%d outside [1, %d]", G, MAX_G);
   StepInfo si = make_step(G, B, bsz, 0, 0.f, 0.f, lr);
   dim3 grid(72, G);          // one conv2 weight per thread: the 18-partial reduction is latency-bound, so go wide
-  small_update_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(W, wg_part, n_cta, c2b_part, c1_part, wt_fwd, wt_dgrad, si);
+  DDL_CUDA_CHECK(ddl_launch_pdl(small_update_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, W, wg_part, n_cta, c2b_part, c1_part, wt_fwd, wt_dgrad, si));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

@@ -47,6 +47,8 @@ struct DgradParams {
 
 __global__ void __launch_bounds__(DG_THREADS, 1)
 conv2_dgrad_kernel(const __grid_constant__ CUtensorMap tm_dy2, const __grid_constant__ CUtensorMap tm_w, const DgradParams prm) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* s_w = smem;
@@ -197,7 +199,7 @@ extern "C" int ddl_mnist_conv2_dgrad(const float* wt_dgrad, const float* dy2, co
     DDL_CUDA_CHECK(cudaFuncSetAttribute(conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DG_SMEM));
     configured = true;
   }
-  conv2_dgrad_kernel<<<prm.ctas_per_client * G, DG_THREADS, DG_SMEM, (cudaStream_t)stream>>>(tm_d, tm_w, prm);
+  DDL_CUDA_CHECK(ddl_launch_pdl(conv2_dgrad_kernel, dim3(prm.ctas_per_client * G), dim3(DG_THREADS), DG_SMEM, (cudaStream_t)stream, tm_d, tm_w, prm));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

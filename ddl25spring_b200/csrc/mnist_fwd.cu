@@ -29,6 +29,8 @@ __global__ void __launch_bounds__(256) conv1_relu_kernel(const float* __restrict
                                                          int64_t x_client_stride, const int* __restrict__ perm,
                                                          int64_t perm_stride, int sample_off, float* __restrict__ a1,
                                                          const StepInfo si) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float img[IMG * IMG];
   const int row = blockIdx.x;
   const int g = row / si.B, b = row % si.B;
@@ -70,6 +72,8 @@ __global__ void __launch_bounds__(256) conv1_relu_kernel(const float* __restrict
 // ------------------------------------------------------------------------------------------ prep
 __global__ void __launch_bounds__(256) prep_conv2_kernel(const float* __restrict__ W, float* __restrict__ wt_fwd,
                                                          float* __restrict__ wt_dgrad) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int g = blockIdx.x;
   const float* w2 = W + (int64_t)g * P + OFF_C2W;            // [co][ci][tap]
   float* f = wt_fwd + (int64_t)g * 9 * C2 * C1;              // [tap][co][ci]
@@ -117,6 +121,8 @@ template <bool TRAIN>
 __global__ void __launch_bounds__(kConv2Threads, 1)
 conv2_pool_fwd_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__ CUtensorMap tm_w,
                       const Conv2Params prm) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* s_w = smem;
@@ -313,14 +319,14 @@ int ddl_mnist_conv1_fwd(const float* W, const float* X, int64_t x_client_stride,
                         int sample_off, float* a1, int G, int B, const int* bsz, void* stream) {
   StepInfo si = make_step(G, B, bsz, 0, 0.f, 0.f, 0.f);
   if (int e = check_step(si)) return e;
-  conv1_relu_kernel<<<G * B, 256, 0, (cudaStream_t)stream>>>(W, X, x_client_stride, perm, perm_stride, sample_off, a1, si);
+  DDL_CUDA_CHECK(ddl_launch_pdl(conv1_relu_kernel, dim3(G * B), dim3(256), 0, (cudaStream_t)stream, W, X, x_client_stride, perm, perm_stride, sample_off, a1, si));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
 
 int ddl_mnist_prep_conv2(const float* W, float* wt_fwd, float* wt_dgrad, int G, void* stream) {
   DDL_REQUIRE(G >= 1 && G <= MAX_G, "G=%d outside [1, %d]", G, MAX_G);
-  prep_conv2_kernel<<<G, 256, 0, (cudaStream_t)stream>>>(W, wt_fwd, wt_dgrad);
+  DDL_CUDA_CHECK(ddl_launch_pdl(prep_conv2_kernel, dim3(G), dim3(256), 0, (cudaStream_t)stream, W, wt_fwd, wt_dgrad));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -353,8 +359,8 @@ int ddl_mnist_conv2_pool_fwd(const float* W, const float* wt_fwd, const float* a
     configured = true;
   }
   const int grid = prm.ctas_per_client * G;
-  if (train) conv2_pool_fwd_kernel<true><<<grid, kConv2Threads, CONV2_SMEM, (cudaStream_t)stream>>>(tm_a, tm_w, prm);
-  else conv2_pool_fwd_kernel<false><<<grid, kConv2Threads, CONV2_SMEM, (cudaStream_t)stream>>>(tm_a, tm_w, prm);
+  if (train) DDL_CUDA_CHECK(ddl_launch_pdl(conv2_pool_fwd_kernel<true>, dim3(grid), dim3(kConv2Threads), CONV2_SMEM, (cudaStream_t)stream, tm_a, tm_w, prm));
+  else DDL_CUDA_CHECK(ddl_launch_pdl(conv2_pool_fwd_kernel<false>, dim3(grid), dim3(kConv2Threads), CONV2_SMEM, (cudaStream_t)stream, tm_a, tm_w, prm));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

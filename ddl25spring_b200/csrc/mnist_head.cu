@@ -28,6 +28,8 @@ __global__ void __launch_bounds__(kHeadWarps * 32, 1)
 head_train_kernel(float* __restrict__ W, const float* __restrict__ h1, const int64_t* __restrict__ Y, int64_t y_client_stride,
                   const int* __restrict__ perm, int64_t perm_stride, int sample_off, float* __restrict__ dz1,
                   float* __restrict__ part_out, const StepInfo si) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float sm[];
   float* s_w2 = sm;                       // [10][128]
   float* s_b2 = s_w2 + NCLS * FC1;        // [10] (+6 pad)
@@ -131,6 +133,8 @@ head_train_kernel(float* __restrict__ W, const float* __restrict__ h1, const int
 
 __global__ void __launch_bounds__(256) head_apply_kernel(float* __restrict__ W, const float* __restrict__ part, float* __restrict__ loss_out,
                                                          float lr) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int g = blockIdx.x;
   float* Wg = W + (int64_t)g * P;
   const float* gp = part + (int64_t)g * kHeadParts * (kPartial + 1);
@@ -152,6 +156,8 @@ __global__ void __launch_bounds__(256) head_apply_kernel(float* __restrict__ W, 
 __global__ void __launch_bounds__(256) head_eval_kernel(const float* __restrict__ W, const float* __restrict__ h1,
                                                         const int64_t* __restrict__ Y, int sample_off, int nrows,
                                                         float* __restrict__ logits_out, int* __restrict__ correct) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float s_w2[NCLS * FC1];
   __shared__ float s_b2[16];
   for (int i = threadIdx.x; i < NCLS * FC1; i += blockDim.x) s_w2[i] = W[OFF_F2W + i];
@@ -198,10 +204,10 @@ int ddl_mnist_head_train(float* W, const float* h1, const int64_t* Y, int64_t y_
     configured = true;
   }
   dim3 grid(G, kHeadParts);
-  head_train_kernel<<<grid, kHeadWarps * 32, smem, (cudaStream_t)stream>>>(W, h1, Y, y_client_stride, perm, perm_stride,
-                                                                           sample_off, dz1, scratch, si);
+  DDL_CUDA_CHECK(ddl_launch_pdl(head_train_kernel, dim3(grid), dim3(kHeadWarps * 32), smem, (cudaStream_t)stream, W, h1, Y, y_client_stride, perm, perm_stride,
+                                                                           sample_off, dz1, scratch, si));
   DDL_LAUNCH_CHECK();
-  head_apply_kernel<<<G, 256, 0, (cudaStream_t)stream>>>(W, scratch, loss_out, lr);
+  DDL_CUDA_CHECK(ddl_launch_pdl(head_apply_kernel, dim3(G), dim3(256), 0, (cudaStream_t)stream, W, scratch, loss_out, lr));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -211,7 +217,7 @@ int ddl_mnist_head_eval(const float* W, const float* h1, const int64_t* Y, int s
   if (nrows <= 0) return DDL_OK;
   int blocks = (nrows + 7) / 8;
   if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
-  head_eval_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(W, h1, Y, sample_off, nrows, logits_out, correct);
+  DDL_CUDA_CHECK(ddl_launch_pdl(head_eval_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, W, h1, Y, sample_off, nrows, logits_out, correct));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

@@ -37,6 +37,8 @@ struct WgradParams {
 
 __global__ void __launch_bounds__(192, 1)
 conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tm_a1, const __grid_constant__ CUtensorMap tm_dy2, const WgradParams prm) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + WG_STAGES * WG_STAGE_BYTES);
@@ -173,7 +175,7 @@ extern "C" int ddl_mnist_conv2_wgrad(const float* a1, const float* dy2, float* w
     DDL_CUDA_CHECK(cudaFuncSetAttribute(conv2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
     configured = true;
   }
-  conv2_wgrad_kernel<<<prm.ctas_per_client * G, 192, WG_SMEM, (cudaStream_t)stream>>>(tm_a, tm_d, prm);
+  DDL_CUDA_CHECK(ddl_launch_pdl(conv2_wgrad_kernel, dim3(prm.ctas_per_client * G), dim3(192), WG_SMEM, (cudaStream_t)stream, tm_a, tm_d, prm));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
