@@ -1,9 +1,10 @@
 // K16: causal self-attention forward + backward for the labs' LLaMA shape (T = 256, head dim 48, 6 heads, B <= 3).
 //
 // q, k, v, o: [B*H, T, D] fp32.  The problem is tiny (18 heads x 256 x 256 scores), far below one tensor-core tile
-// per SM, so this is a CUDA-core flash-style kernel: one THREAD per query row (forward, dQ) or per key row (dK, dV);
-// K/V (resp. Q/dO) tiles are staged in shared memory and every thread of a warp reads the same row -> broadcast,
-// no bank conflicts; online softmax keeps the running max / sum in registers; nothing of size T x T is stored.
+// per SM, so this is a CUDA-core flash-style kernel: FOUR LANES per query row (forward, dQ) or per key row (dK + dV in
+// one pass), each holding a quarter of the head dimension; K/V (resp. Q/dO) tiles are staged in shared memory and the
+// lanes of a warp read the same row -> broadcast, no bank conflicts; online softmax keeps the running max / sum in
+// registers; nothing of size T x T is stored.
 // Backward recomputes the probabilities from the saved log-sum-exp.
 // Replaces (reference): the attention inside simplellm's LLaMA blocks (lab/tutorial_1b/primer/intro.py:17,28).
 #include "common.cuh"
@@ -11,163 +12,185 @@
 
 namespace {
 
-constexpr int kRows = 128;   // query (or key) rows per CTA = threads per CTA
-constexpr int kTile = 32;    // rows of the other operand staged per step
+// Work split: a QUERY (forward, dQ) or KEY (dK/dV) row is owned by 4 adjacent lanes, each holding D/4 of the head dimension;
+// dot products are finished with two xor-shuffles.  A CTA of 128 threads covers 32 rows, so the lab shape (18 heads x 256
+// tokens) launches 144 CTAs - one per SM - and a thread's serial work per key is D/4 FMAs instead of D.  (The first version
+// used one thread per row and 36 CTAs: 90 us per kernel; see DESIGN.md.)
+constexpr int kThreads = 128;
+constexpr int kRows = kThreads / 4;   // rows (queries or keys) per CTA
+constexpr int kTile = 32;             // rows of the other operand staged in shared memory per step
+
+__device__ __forceinline__ float quad_sum(float v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  return v;
+}
 
 template <int D>
-__global__ void __launch_bounds__(kRows) attn_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k,
-                                                         const float* __restrict__ v, float* __restrict__ o, float* __restrict__ lse,
-                                                         int T, float scale) {
-  __shared__ float Ks[kTile][D], Vs[kTile][D];
-  const int bh = blockIdx.y;
-  const int i = blockIdx.x * kRows + threadIdx.x;
-  const float* qb = q + (int64_t)bh * T * D;
-  const float* kb = k + (int64_t)bh * T * D;
-  const float* vb = v + (int64_t)bh * T * D;
-  float qr[D], acc[D];
+__device__ __forceinline__ void load_tile(float (*dst)[D], const float* __restrict__ src, int row0, int T, float mul) {
+  for (int e = threadIdx.x; e < kTile * D / 4; e += kThreads) {
+    const int r = e / (D / 4), d = (e % (D / 4)) * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (row0 + r < T) v = *reinterpret_cast<const float4*>(src + (int64_t)(row0 + r) * D + d);
+    v.x *= mul; v.y *= mul; v.z *= mul; v.w *= mul;
+    *reinterpret_cast<float4*>(&dst[r][d]) = v;
+  }
+}
+
+template <int D>
+__global__ void __launch_bounds__(kThreads) attn_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k,
+                                                            const float* __restrict__ v, float* __restrict__ o, float* __restrict__ lse,
+                                                            int T, float scale) {
+  constexpr int D4 = D / 4;
+  __shared__ __align__(16) float Ks[kTile][D], Vs[kTile][D];
+  const int bh = blockIdx.y, g = threadIdx.x & 3;
+  const int i = blockIdx.x * kRows + (threadIdx.x >> 2);
+  const int i_warp_last = blockIdx.x * kRows + ((threadIdx.x >> 5) << 3) + 7;       // last query handled by this warp
+  const int64_t base = (int64_t)bh * T * D;
+  float qr[D4], acc[D4];
 #pragma unroll
-  for (int d = 0; d < D; ++d) { qr[d] = i < T ? qb[(int64_t)i * D + d] * scale : 0.f; acc[d] = 0.f; }
+  for (int d = 0; d < D4; ++d) { qr[d] = i < T ? q[base + (int64_t)i * D + g * D4 + d] * scale : 0.f; acc[d] = 0.f; }
   float m = -INFINITY, l = 0.f;
   const int last = min(T, (blockIdx.x + 1) * kRows);          // causal: keys beyond this CTA's last query are never needed
   for (int j0 = 0; j0 < last; j0 += kTile) {
     __syncthreads();
-    for (int e = threadIdx.x; e < kTile * D; e += kRows) {
-      const int r = e / D, d = e % D;
-      const bool ok = j0 + r < T;
-      Ks[r][d] = ok ? kb[(int64_t)(j0 + r) * D + d] : 0.f;
-      Vs[r][d] = ok ? vb[(int64_t)(j0 + r) * D + d] : 0.f;
-    }
+    load_tile<D>(Ks, k + base, j0, T, 1.f);
+    load_tile<D>(Vs, v + base, j0, T, 1.f);
     __syncthreads();
-    const int jn = min(kTile, i - j0 + 1);                    // keys j0 .. min(j0+kTile-1, i)
+    const int jn = min(kTile, min(i_warp_last, T - 1) - j0 + 1);   // uniform per warp (shuffles inside the loop)
     for (int r = 0; r < jn; ++r) {
       float s = 0.f;
 #pragma unroll
-      for (int d = 0; d < D; ++d) s = fmaf(qr[d], Ks[r][d], s);
+      for (int d = 0; d < D4; ++d) s = fmaf(qr[d], Ks[r][g * D4 + d], s);
+      s = quad_sum(s);
+      if (j0 + r > i) continue;                                 // masked for this query (all 4 lanes of the query agree)
       const float mn = fmaxf(m, s);
       const float corr = __expf(m - mn), p = __expf(s - mn);
       l = l * corr + p;
 #pragma unroll
-      for (int d = 0; d < D; ++d) acc[d] = fmaf(acc[d], corr, p * Vs[r][d]);
+      for (int d = 0; d < D4; ++d) acc[d] = fmaf(acc[d], corr, p * Vs[r][g * D4 + d]);
       m = mn;
     }
   }
   if (i < T) {
     const float inv = 1.f / l;
-    float* ob = o + ((int64_t)bh * T + i) * D;
 #pragma unroll
-    for (int d = 0; d < D; ++d) ob[d] = acc[d] * inv;
-    lse[(int64_t)bh * T + i] = m + __logf(l);
+    for (int d = 0; d < D4; ++d) o[base + (int64_t)i * D + g * D4 + d] = acc[d] * inv;
+    if (g == 0) lse[(int64_t)bh * T + i] = m + __logf(l);
   }
 }
 
-// dQ: one thread per query row.  delta_i = sum_d dO_i,d * O_i,d is computed here and stored for the dK/dV kernels.
+// dQ: 4 lanes per query row.  delta_i = sum_d dO_i,d * O_i,d is computed here and stored for the dK/dV kernel.
 template <int D>
-__global__ void __launch_bounds__(kRows) attn_bwd_dq_kernel(const float* __restrict__ q, const float* __restrict__ k,
-                                                            const float* __restrict__ v, const float* __restrict__ o,
-                                                            const float* __restrict__ dO, const float* __restrict__ lse,
-                                                            float* __restrict__ dq, float* __restrict__ delta, int T, float scale) {
-  __shared__ float Ks[kTile][D], Vs[kTile][D];
-  const int bh = blockIdx.y;
-  const int i = blockIdx.x * kRows + threadIdx.x;
+__global__ void __launch_bounds__(kThreads) attn_bwd_dq_kernel(const float* __restrict__ q, const float* __restrict__ k,
+                                                               const float* __restrict__ v, const float* __restrict__ o,
+                                                               const float* __restrict__ dO, const float* __restrict__ lse,
+                                                               float* __restrict__ dq, float* __restrict__ delta, int T, float scale) {
+  constexpr int D4 = D / 4;
+  __shared__ __align__(16) float Ks[kTile][D], Vs[kTile][D];
+  const int bh = blockIdx.y, g = threadIdx.x & 3;
+  const int i = blockIdx.x * kRows + (threadIdx.x >> 2);
+  const int i_warp_last = blockIdx.x * kRows + ((threadIdx.x >> 5) << 3) + 7;
   const int64_t base = (int64_t)bh * T * D;
-  float qr[D], go[D], acc[D];
+  float qr[D4], go[D4], acc[D4];
   float dl = 0.f;
 #pragma unroll
-  for (int d = 0; d < D; ++d) {
-    qr[d] = i < T ? q[base + (int64_t)i * D + d] * scale : 0.f;
-    go[d] = i < T ? dO[base + (int64_t)i * D + d] : 0.f;
-    dl = fmaf(go[d], i < T ? o[base + (int64_t)i * D + d] : 0.f, dl);
+  for (int d = 0; d < D4; ++d) {
+    const int64_t off = base + (int64_t)i * D + g * D4 + d;
+    qr[d] = i < T ? q[off] * scale : 0.f;
+    go[d] = i < T ? dO[off] : 0.f;
+    dl = fmaf(go[d], i < T ? o[off] : 0.f, dl);
     acc[d] = 0.f;
   }
+  dl = quad_sum(dl);
   const float li = i < T ? lse[(int64_t)bh * T + i] : 0.f;
-  if (i < T) delta[(int64_t)bh * T + i] = dl;
+  if (i < T && g == 0) delta[(int64_t)bh * T + i] = dl;
   const int last = min(T, (blockIdx.x + 1) * kRows);
   for (int j0 = 0; j0 < last; j0 += kTile) {
     __syncthreads();
-    for (int e = threadIdx.x; e < kTile * D; e += kRows) {
-      const int r = e / D, d = e % D;
-      const bool ok = j0 + r < T;
-      Ks[r][d] = ok ? k[base + (int64_t)(j0 + r) * D + d] : 0.f;
-      Vs[r][d] = ok ? v[base + (int64_t)(j0 + r) * D + d] : 0.f;
-    }
+    load_tile<D>(Ks, k + base, j0, T, 1.f);
+    load_tile<D>(Vs, v + base, j0, T, 1.f);
     __syncthreads();
-    const int jn = min(kTile, i - j0 + 1);
+    const int jn = min(kTile, min(i_warp_last, T - 1) - j0 + 1);
     for (int r = 0; r < jn; ++r) {
       float s = 0.f, dp = 0.f;
 #pragma unroll
-      for (int d = 0; d < D; ++d) { s = fmaf(qr[d], Ks[r][d], s); dp = fmaf(go[d], Vs[r][d], dp); }
+      for (int d = 0; d < D4; ++d) { s = fmaf(qr[d], Ks[r][g * D4 + d], s); dp = fmaf(go[d], Vs[r][g * D4 + d], dp); }
+      s = quad_sum(s);
+      dp = quad_sum(dp);
+      if (j0 + r > i) continue;
       const float ds = __expf(s - li) * (dp - dl) * scale;
 #pragma unroll
-      for (int d = 0; d < D; ++d) acc[d] = fmaf(ds, Ks[r][d], acc[d]);
+      for (int d = 0; d < D4; ++d) acc[d] = fmaf(ds, Ks[r][g * D4 + d], acc[d]);
     }
   }
   if (i < T) {
 #pragma unroll
-    for (int d = 0; d < D; ++d) dq[base + (int64_t)i * D + d] = acc[d];
+    for (int d = 0; d < D4; ++d) dq[base + (int64_t)i * D + g * D4 + d] = acc[d];
   }
 }
 
-// dK (WHICH = 0) or dV (WHICH = 1): one thread per key row, looping over the queries at or after it.
-template <int D, int WHICH>
-__global__ void __launch_bounds__(kRows) attn_bwd_dkv_kernel(const float* __restrict__ q, const float* __restrict__ k,
-                                                             const float* __restrict__ v, const float* __restrict__ dO,
-                                                             const float* __restrict__ lse, const float* __restrict__ delta,
-                                                             float* __restrict__ out, int T, float scale) {
-  __shared__ float Qs[kTile][D], Gs[kTile][D];
+// dK and dV in one pass: 4 lanes per key row, looping over the queries at or after it.
+template <int D>
+__global__ void __launch_bounds__(kThreads) attn_bwd_dkv_kernel(const float* __restrict__ q, const float* __restrict__ k,
+                                                                const float* __restrict__ v, const float* __restrict__ dO,
+                                                                const float* __restrict__ lse, const float* __restrict__ delta,
+                                                                float* __restrict__ dk, float* __restrict__ dv, int T, float scale) {
+  constexpr int D4 = D / 4;
+  __shared__ __align__(16) float Qs[kTile][D], Gs[kTile][D];
   __shared__ float Ls[kTile], Ds[kTile];
-  const int bh = blockIdx.y;
-  const int j = blockIdx.x * kRows + threadIdx.x;
+  const int bh = blockIdx.y, g = threadIdx.x & 3;
+  const int j = blockIdx.x * kRows + (threadIdx.x >> 2);
+  const int j_warp_first = blockIdx.x * kRows + ((threadIdx.x >> 5) << 3);            // first key handled by this warp
   const int64_t base = (int64_t)bh * T * D;
-  float kr[D], vr[D], acc[D];
+  float kr[D4], vr[D4], acck[D4], accv[D4];
 #pragma unroll
-  for (int d = 0; d < D; ++d) {
-    kr[d] = j < T ? k[base + (int64_t)j * D + d] : 0.f;
-    vr[d] = (WHICH == 0 && j < T) ? v[base + (int64_t)j * D + d] : 0.f;
-    acc[d] = 0.f;
+  for (int d = 0; d < D4; ++d) {
+    const int64_t off = base + (int64_t)j * D + g * D4 + d;
+    kr[d] = j < T ? k[off] : 0.f;
+    vr[d] = j < T ? v[off] : 0.f;
+    acck[d] = 0.f; accv[d] = 0.f;
   }
   const int first = blockIdx.x * kRows;                       // queries before this CTA's first key never attend to it
   for (int i0 = first; i0 < T; i0 += kTile) {
     __syncthreads();
-    for (int e = threadIdx.x; e < kTile * D; e += kRows) {
-      const int r = e / D, d = e % D;
-      const bool ok = i0 + r < T;
-      Qs[r][d] = ok ? q[base + (int64_t)(i0 + r) * D + d] * scale : 0.f;
-      Gs[r][d] = ok ? dO[base + (int64_t)(i0 + r) * D + d] : 0.f;
-    }
+    load_tile<D>(Qs, q + base, i0, T, scale);
+    load_tile<D>(Gs, dO + base, i0, T, 1.f);
     if (threadIdx.x < kTile) {
       const bool ok = i0 + threadIdx.x < T;
       Ls[threadIdx.x] = ok ? lse[(int64_t)bh * T + i0 + threadIdx.x] : INFINITY;   // p = exp(s - inf) = 0 for padding rows
       Ds[threadIdx.x] = ok ? delta[(int64_t)bh * T + i0 + threadIdx.x] : 0.f;
     }
     __syncthreads();
-    for (int r = max(0, j - i0); r < kTile; ++r) {            // only queries i >= j
-      float s = 0.f;
+    for (int r = max(0, j_warp_first - i0); r < kTile; ++r) {  // uniform per warp; only queries i >= j contribute
+      float s = 0.f, dp = 0.f;
 #pragma unroll
-      for (int d = 0; d < D; ++d) s = fmaf(Qs[r][d], kr[d], s);
+      for (int d = 0; d < D4; ++d) { s = fmaf(Qs[r][g * D4 + d], kr[d], s); dp = fmaf(Gs[r][g * D4 + d], vr[d], dp); }
+      s = quad_sum(s);
+      dp = quad_sum(dp);
+      if (i0 + r < j) continue;
       const float p = __expf(s - Ls[r]);
-      if (WHICH == 1) {
+      const float ds = p * (dp - Ds[r]);                        // Qs already carries `scale`
 #pragma unroll
-        for (int d = 0; d < D; ++d) acc[d] = fmaf(p, Gs[r][d], acc[d]);
-      } else {
-        float dp = 0.f;
-#pragma unroll
-        for (int d = 0; d < D; ++d) dp = fmaf(Gs[r][d], vr[d], dp);
-        const float ds = p * (dp - Ds[r]);                    // Qs already carries `scale`
-#pragma unroll
-        for (int d = 0; d < D; ++d) acc[d] = fmaf(ds, Qs[r][d], acc[d]);
+      for (int d = 0; d < D4; ++d) {
+        accv[d] = fmaf(p, Gs[r][g * D4 + d], accv[d]);
+        acck[d] = fmaf(ds, Qs[r][g * D4 + d], acck[d]);
       }
     }
   }
   if (j < T) {
 #pragma unroll
-    for (int d = 0; d < D; ++d) out[base + (int64_t)j * D + d] = acc[d];
+    for (int d = 0; d < D4; ++d) {
+      dk[base + (int64_t)j * D + g * D4 + d] = acck[d];
+      dv[base + (int64_t)j * D + g * D4 + d] = accv[d];
+    }
   }
 }
 
 template <int D>
 int launch_fwd(const float* q, const float* k, const float* v, float* o, float* lse, int BH, int T, float scale, cudaStream_t st) {
   dim3 grid((T + kRows - 1) / kRows, BH);
-  attn_fwd_kernel<D><<<grid, kRows, 0, st>>>(q, k, v, o, lse, T, scale);
+  attn_fwd_kernel<D><<<grid, kThreads, 0, st>>>(q, k, v, o, lse, T, scale);
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -176,11 +199,9 @@ template <int D>
 int launch_bwd(const float* q, const float* k, const float* v, const float* o, const float* dO, const float* lse, float* dq, float* dk,
                float* dv, float* delta, int BH, int T, float scale, cudaStream_t st) {
   dim3 grid((T + kRows - 1) / kRows, BH);
-  attn_bwd_dq_kernel<D><<<grid, kRows, 0, st>>>(q, k, v, o, dO, lse, dq, delta, T, scale);
+  attn_bwd_dq_kernel<D><<<grid, kThreads, 0, st>>>(q, k, v, o, dO, lse, dq, delta, T, scale);
   DDL_LAUNCH_CHECK();
-  attn_bwd_dkv_kernel<D, 0><<<grid, kRows, 0, st>>>(q, k, v, dO, lse, delta, dk, T, scale);
-  DDL_LAUNCH_CHECK();
-  attn_bwd_dkv_kernel<D, 1><<<grid, kRows, 0, st>>>(q, k, v, dO, lse, delta, dv, T, scale);
+  attn_bwd_dkv_kernel<D><<<grid, kThreads, 0, st>>>(q, k, v, dO, lse, delta, dk, dv, T, scale);
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

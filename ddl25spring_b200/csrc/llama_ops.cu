@@ -1,0 +1,121 @@
+// K16 (element-wise part of the LLaMA block): fused QKV split + head transpose + rotary embedding, and SwiGLU.
+//
+//   rope_qkv_fwd : qkv [B, T, 3, H, hd] (the output of the fused QKV GEMM) -> q, k, v [B, H, T, hd], with q and k rotated pair-wise
+//                  by (cos, sin)[t, p]:  y_even = x_even c - x_odd s,  y_odd = x_even s + x_odd c       (one pass instead of
+//                  view/permute/contiguous + two 6-kernel apply_rope chains)
+//   rope_qkv_bwd : the transpose: d(qkv) from dq, dk, dv (inverse rotation for q and k)
+//   swiglu_fwd/bwd: h = silu(g) * u;  dg = dh u silu'(g),  du = dh silu(g)
+//
+// Replaces (reference): simplellm's LLaMA block internals (lab/tutorial_1b/primer/intro.py:17,28 via `LLama`), which run as a
+// dozen ATen element-wise kernels per layer.
+#include "common.cuh"
+#include "ddl25_kernels.h"
+
+namespace {
+
+template <bool BWD>
+__global__ void __launch_bounds__(256) rope_qkv_kernel(float* __restrict__ qkv, const float* __restrict__ cs, const float* __restrict__ sn,
+                                                       float* __restrict__ q, float* __restrict__ k, float* __restrict__ v, int B, int T,
+                                                       int H, int hd) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int P = hd / 2;
+  const int64_t total = (int64_t)B * T * 3 * H * P;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = e;
+    const int p = (int)(r % P); r /= P;
+    const int h = (int)(r % H); r /= H;
+    const int w = (int)(r % 3); r /= 3;
+    const int t = (int)(r % T);
+    const int b = (int)(r / T);
+    float2* src = reinterpret_cast<float2*>(qkv) + e;                                   // [b, t, w, h, p] pairs are contiguous
+    float* dstbase = w == 0 ? q : (w == 1 ? k : v);
+    float2* dst = reinterpret_cast<float2*>(dstbase + (((int64_t)b * H + h) * T + t) * hd) + p;
+    const float c = w < 2 ? cs[t * P + p] : 1.f, s = w < 2 ? sn[t * P + p] : 0.f;
+    if (!BWD) {
+      const float2 x = *src;
+      *dst = make_float2(x.x * c - x.y * s, x.x * s + x.y * c);
+    } else {
+      const float2 g = *dst;
+      *src = make_float2(g.x * c + g.y * s, -g.x * s + g.y * c);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) swiglu_fwd_kernel(const float4* __restrict__ g, const float4* __restrict__ u, float4* __restrict__ h,
+                                                         int64_t n4) {
+  pdl_launch_dependents();
+  pdl_wait();
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 a = g[i], b = u[i];
+    float4 o;
+    o.x = a.x / (1.f + __expf(-a.x)) * b.x; o.y = a.y / (1.f + __expf(-a.y)) * b.y;
+    o.z = a.z / (1.f + __expf(-a.z)) * b.z; o.w = a.w / (1.f + __expf(-a.w)) * b.w;
+    h[i] = o;
+  }
+}
+
+__device__ __forceinline__ void swiglu_grad(float g, float u, float dh, float& dg, float& du) {
+  const float sig = 1.f / (1.f + __expf(-g));
+  const float silu = g * sig;
+  du = dh * silu;
+  dg = dh * u * (sig + silu * (1.f - sig));
+}
+
+__global__ void __launch_bounds__(256) swiglu_bwd_kernel(const float4* __restrict__ g, const float4* __restrict__ u,
+                                                         const float4* __restrict__ dh, float4* __restrict__ dg, float4* __restrict__ du,
+                                                         int64_t n4) {
+  pdl_launch_dependents();
+  pdl_wait();
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 a = g[i], b = u[i], d = dh[i];
+    float4 x, y;
+    swiglu_grad(a.x, b.x, d.x, x.x, y.x); swiglu_grad(a.y, b.y, d.y, x.y, y.y);
+    swiglu_grad(a.z, b.z, d.z, x.z, y.z); swiglu_grad(a.w, b.w, d.w, x.w, y.w);
+    dg[i] = x;
+    du[i] = y;
+  }
+}
+
+int blocks_for(int64_t work) {
+  int64_t b = (work + 255) / 256;
+  if (b > kNumSMs * 16) b = kNumSMs * 16;
+  return (int)(b < 1 ? 1 : b);
+}
+
+}  // namespace
+
+extern "C" {
+
+int ddl_rope_qkv(float* qkv, const float* cos_tab, const float* sin_tab, float* q, float* k, float* v, int B, int T, int H, int hd,
+                 int backward, void* stream) {
+  DDL_REQUIRE(hd % 2 == 0 && B > 0 && T > 0 && H > 0, "rope_qkv: head dim must be even");
+  const int64_t total = (int64_t)B * T * 3 * H * (hd / 2);
+  if (backward)
+    DDL_CUDA_CHECK(ddl_launch_pdl(rope_qkv_kernel<true>, dim3(blocks_for(total)), dim3(256), 0, (cudaStream_t)stream, qkv, cos_tab, sin_tab,
+                                  q, k, v, B, T, H, hd));
+  else
+    DDL_CUDA_CHECK(ddl_launch_pdl(rope_qkv_kernel<false>, dim3(blocks_for(total)), dim3(256), 0, (cudaStream_t)stream, qkv, cos_tab, sin_tab,
+                                  q, k, v, B, T, H, hd));
+  DDL_LAUNCH_CHECK();
+  return DDL_OK;
+}
+
+int ddl_swiglu_fwd(const float* g, const float* u, float* h, int64_t n, void* stream) {
+  DDL_REQUIRE(n % 4 == 0, "swiglu: n %% 4 != 0");
+  DDL_CUDA_CHECK(ddl_launch_pdl(swiglu_fwd_kernel, dim3(blocks_for(n / 4)), dim3(256), 0, (cudaStream_t)stream,
+                                reinterpret_cast<const float4*>(g), reinterpret_cast<const float4*>(u), reinterpret_cast<float4*>(h), n / 4));
+  DDL_LAUNCH_CHECK();
+  return DDL_OK;
+}
+
+int ddl_swiglu_bwd(const float* g, const float* u, const float* dh, float* dg, float* du, int64_t n, void* stream) {
+  DDL_REQUIRE(n % 4 == 0, "swiglu: n %% 4 != 0");
+  DDL_CUDA_CHECK(ddl_launch_pdl(swiglu_bwd_kernel, dim3(blocks_for(n / 4)), dim3(256), 0, (cudaStream_t)stream,
+                                reinterpret_cast<const float4*>(g), reinterpret_cast<const float4*>(u), reinterpret_cast<const float4*>(dh),
+                                reinterpret_cast<float4*>(dg), reinterpret_cast<float4*>(du), n / 4));
+  DDL_LAUNCH_CHECK();
+  return DDL_OK;
+}
+
+}  // extern "C"

@@ -53,11 +53,15 @@ class Attention(nn.Module):
         self.register_buffer("rope_cos", cos, persistent=False)
         self.register_buffer("rope_sin", sin, persistent=False)
         self.attn_fn = None        # ops.nn.use_kernels() installs the hand-written causal attention here
+        self.qkv_fn = None         # ... and the fused QKV split + transpose + rotary embedding
 
     def forward(self, x):
         B, T, C = x.shape
-        q, k, v = self.wqkv(x).view(B, T, 3, self.h, self.hd).permute(2, 0, 3, 1, 4)
-        q, k = apply_rope(q, self.rope_cos, self.rope_sin), apply_rope(k, self.rope_cos, self.rope_sin)
+        if self.qkv_fn is not None and x.is_cuda and x.dtype == torch.float32:
+            q, k, v = self.qkv_fn(self.wqkv(x), self.rope_cos, self.rope_sin, self.h)
+        else:
+            q, k, v = self.wqkv(x).view(B, T, 3, self.h, self.hd).permute(2, 0, 3, 1, 4)
+            q, k = apply_rope(q, self.rope_cos, self.rope_sin), apply_rope(k, self.rope_cos, self.rope_sin)
         o = self.attn_fn(q, k, v) if self.attn_fn is not None else F.scaled_dot_product_attention(q, k, v, is_causal=True)
         return self.wo(o.transpose(1, 2).reshape(B, T, C))
 
@@ -69,8 +73,11 @@ class GatedMLP(nn.Module):
         self.w_gate = nn.Linear(dmodel, hidden, bias=False)
         self.w_up = nn.Linear(dmodel, hidden, bias=False)
         self.w_down = nn.Linear(hidden, dmodel, bias=False)
+        self.act_fn = None         # ops.nn.use_kernels() installs the fused SwiGLU here
 
     def forward(self, x):
+        if self.act_fn is not None:
+            return self.w_down(self.act_fn(self.w_gate(x), self.w_up(x)))
         return self.w_down(F.silu(self.w_gate(x)) * self.w_up(x))
 
 

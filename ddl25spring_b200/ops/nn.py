@@ -184,9 +184,63 @@ def kernel_causal_attention(q, k, v):
     return _CausalAttnFn.apply(q, k, v, 1.0 / (D ** 0.5))
 
 
+class _RopeQkvFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, cos, sin, H):
+        B, T, C3 = qkv.shape
+        hd = C3 // (3 * H)
+        qkv = qkv.contiguous()
+        q = torch.empty((B, H, T, hd), device=qkv.device, dtype=torch.float32)
+        k, v = torch.empty_like(q), torch.empty_like(q)
+        _lib.check(_lib.lib().ddl_rope_qkv(_lib.p(qkv), _lib.p(cos), _lib.p(sin), _lib.p(q), _lib.p(k), _lib.p(v), int(B), int(T), int(H),
+                                           int(hd), 0, _lib.stream()), "ddl_rope_qkv")
+        ctx.save_for_backward(cos, sin)
+        ctx.dims = (B, T, H, hd)
+        return q, k, v
+
+    @staticmethod
+    def backward(ctx, gq, gk, gv):
+        cos, sin = ctx.saved_tensors
+        B, T, H, hd = ctx.dims
+        g = torch.empty((B, T, 3 * H * hd), device=gq.device, dtype=torch.float32)
+        _lib.check(_lib.lib().ddl_rope_qkv(_lib.p(g), _lib.p(cos), _lib.p(sin), _lib.p(gq.contiguous()), _lib.p(gk.contiguous()),
+                                           _lib.p(gv.contiguous()), int(B), int(T), int(H), int(hd), 1, _lib.stream()), "ddl_rope_qkv")
+        return g, None, None, None
+
+
+def kernel_rope_qkv(qkv, cos, sin, n_heads: int):
+    """``qkv`` [B, T, 3*H*hd] -> rotary-embedded q, k and v, each [B, H, T, hd] contiguous (one kernel each way)."""
+    return _RopeQkvFn.apply(qkv, cos.contiguous(), sin.contiguous(), n_heads)
+
+
+class _SwiGluFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, g, u):
+        g, u = g.contiguous(), u.contiguous()
+        h = torch.empty_like(g)
+        _lib.check(_lib.lib().ddl_swiglu_fwd(_lib.p(g), _lib.p(u), _lib.p(h), _lib.i64(g.numel()), _lib.stream()), "ddl_swiglu_fwd")
+        ctx.save_for_backward(g, u)
+        return h
+
+    @staticmethod
+    def backward(ctx, dh):
+        g, u = ctx.saved_tensors
+        dg, du = torch.empty_like(g), torch.empty_like(u)
+        _lib.check(_lib.lib().ddl_swiglu_bwd(_lib.p(g), _lib.p(u), _lib.p(dh.contiguous()), _lib.p(dg), _lib.p(du), _lib.i64(g.numel()),
+                                             _lib.stream()), "ddl_swiglu_bwd")
+        return dg, du
+
+
+def kernel_swiglu(g, u):
+    """``silu(g) * u`` (the gated-MLP activation) in one kernel each way."""
+    if not g.is_cuda or g.dtype != torch.float32 or g.numel() % 4:
+        return F.silu(g) * u
+    return _SwiGluFn.apply(g, u)
+
+
 def use_kernels(model: nn.Module, precise: bool = True) -> nn.Module:
     """Route every ``nn.Linear`` (and RMSNorm of models/llama.py) of ``model`` through the kernels, in place."""
-    from ..models.llama import Attention, RMSNorm
+    from ..models.llama import Attention, GatedMLP, RMSNorm
     for mod in model.modules():
         if type(mod) is nn.Linear:
             mod.__class__ = KernelLinear
@@ -197,4 +251,7 @@ def use_kernels(model: nn.Module, precise: bool = True) -> nn.Module:
             mod.forward = (lambda m: (lambda x: kernel_batch_norm(x, m)))(mod)
         elif isinstance(mod, Attention):
             mod.attn_fn = kernel_causal_attention
+            mod.qkv_fn = kernel_rope_qkv
+        elif isinstance(mod, GatedMLP):
+            mod.act_fn = kernel_swiglu
     return model

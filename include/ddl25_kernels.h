@@ -233,6 +233,15 @@ int ddl_gram_rowgather_tcgen05(const float* const* part_ptrs, int n_parts, int r
  * orders the GPUs with barriers before (inputs written) and after (results visible). */
 int ddl_nvls_allreduce(float* multicast_ptr, int64_t d0, int64_t d1, float scale, int max_ctas, void* stream);
 
+/* ---- K16 element-wise: fused QKV split + head transpose + rotary embedding, SwiGLU (csrc/llama_ops.cu) ---------------------
+ * (ref: simplellm LLaMA block internals used by lab/tutorial_1b/primer/intro.py:17,28.)
+ * qkv: [B, T, 3, H, hd]; q, k, v: [B, H, T, hd]; cos/sin: [>= T, hd/2].  backward == 0: qkv -> q, k, v (q, k rotated);
+ * backward != 0: dq, dk, dv (passed as q, k, v) -> d(qkv) written into `qkv`. */
+int ddl_rope_qkv(float* qkv, const float* cos_tab, const float* sin_tab, float* q, float* k, float* v, int B, int T, int H, int hd,
+                 int backward, void* stream);
+int ddl_swiglu_fwd(const float* g, const float* u, float* h, int64_t n, void* stream);               /* h = silu(g) * u */
+int ddl_swiglu_bwd(const float* g, const float* u, const float* dh, float* dg, float* du, int64_t n, void* stream);
+
 /* ---- K9 general: NHWC / OHWI convolutions as tap GEMMs on tcgen05 (csrc/conv_tcgen05.cu) -------------------------------
  * (ref: nn.Conv2d via ATen/cuDNN, lab/tutorial_1a/hfl_complete.py:51,53; ResNet-18 / DCGAN convs of the north star.)
  * A convolution is a list of taps; tap t reads activation map tap_map[t] (an NHWC tensor [N, Ha, Wa, Ca]) at spatial

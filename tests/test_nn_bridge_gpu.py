@@ -96,3 +96,29 @@ def test_kernel_causal_attention(cuda_lib, B, H, T, D):
     torch.testing.assert_close(out.double(), ref, rtol=1e-4, atol=1e-5)
     for t, gg in zip((q, k, v), g):
         torch.testing.assert_close(t.grad.double(), gg.double(), rtol=1e-3, atol=2e-5)
+
+
+@pytest.mark.gpu
+def test_kernel_rope_qkv_and_swiglu_match_torch(cuda_lib):
+    from ddl25spring_b200.models.llama import apply_rope, rope_tables
+    from ddl25spring_b200.ops.nn import kernel_rope_qkv, kernel_swiglu
+    torch.manual_seed(0)
+    B, T, H, hd = 3, 100, 6, 48
+    cos, sin = rope_tables(hd, 256, device="cuda")
+    qkv = torch.randn(B, T, 3 * H * hd, device="cuda", requires_grad=True)
+    q, k, v = kernel_rope_qkv(qkv, cos, sin, H)
+    qr, kr, vr = qkv.view(B, T, 3, H, hd).permute(2, 0, 3, 1, 4)
+    qr, kr = apply_rope(qr, cos, sin), apply_rope(kr, cos, sin)
+    for a, b in ((q, qr), (k, kr), (v, vr)):
+        assert torch.allclose(a, b, atol=1e-6)
+    gq, gk, gv = torch.randn_like(q), torch.randn_like(k), torch.randn_like(v)
+    g1 = torch.autograd.grad((q * gq).sum() + (k * gk).sum() + (v * gv).sum(), qkv)[0]
+    g2 = torch.autograd.grad((qr * gq).sum() + (kr * gk).sum() + (vr * gv).sum(), qkv)[0]
+    assert torch.allclose(g1, g2, atol=1e-5)
+    g = torch.randn(5, 77, 768, device="cuda", requires_grad=True)
+    u = torch.randn(5, 77, 768, device="cuda", requires_grad=True)
+    h, hr = kernel_swiglu(g, u), F.silu(g) * u
+    assert torch.allclose(h, hr, atol=1e-5, rtol=1e-5)
+    dh = torch.randn_like(h)
+    for a, b in zip(torch.autograd.grad(h, (g, u), dh), torch.autograd.grad(hr, (g, u), dh)):
+        assert torch.allclose(a, b, atol=1e-5, rtol=1e-4)
