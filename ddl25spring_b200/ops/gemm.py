@@ -63,6 +63,14 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         # grows ~linearly in K (measured on B200: 2e-6 at K=128, 8e-5 at K=9216).  Cap each
         # accumulation chain at PRECISE_CHAIN products and finish the sum in fp32 on the CUDA cores.
         n_split = max(n_split, -(-K // PRECISE_CHAIN))
+    if n_split == 1 and beta == 0.0 and eb == 4:
+        # a grid that covers less than half the SMs with a long K loop (LLaMA's 768-wide projections on 768 tokens: 18 tiles x
+        # 24 k-blocks) is latency-bound per CTA: spread the reduction over more SMs, partials summed in a fixed order
+        bn = 32 if N <= 32 else (64 if N <= 64 else 128)
+        ctas = -(-M // 128) * -(-N // bn) * G
+        kb = -(-K // 32)
+        if 2 * ctas <= 148 and kb >= 8:
+            n_split = max(1, min(kb // 4, 148 // ctas))
     L = _lib.lib()
     scratch = None
     if n_split > 1:
