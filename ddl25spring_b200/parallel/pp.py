@@ -111,6 +111,32 @@ class Mesh:
                 grp = dist.new_group(ranks)
                 if s == self.stage_id:
                     self.dp_group = grp
+        # NCCL p2p operations between two ranks execute in issue order on one stream per communicator.  In 1F1B a stage
+        # issues "send activation k+1" before "receive gradient k" while its successor issues "send gradient k" before
+        # "receive activation k+1": on a single communicator the two sends wait for each other's receive forever.  Forward
+        # traffic (activations) and backward traffic (gradients) therefore get a communicator each; inside one direction
+        # both ends issue transfers in micro-batch order, so each communicator's streams always agree.  (gloo matches
+        # messages by tag and needs none of this.)
+        self.fwd_group = self.bwd_group = None
+        if dist.is_initialized() and dist.get_backend() == "nccl" and n_stages > 1:
+            world = dist.get_world_size()
+            self.fwd_group = dist.new_group(list(range(world)))
+            self.bwd_group = dist.new_group(list(range(world)))
+            # NCCL creates the communicator of a p2p pair lazily, in a blocking rendezvous of the two ranks, on their FIRST
+            # transfer.  Inside a schedule that first transfer can sit behind a dependency on the peer (a stage posts its first
+            # gradient receive before it sends the activation its peer is waiting for), so every pair is connected here, in
+            # stage order, before any schedule runs.
+            dev = torch.device("cuda", torch.cuda.current_device())
+            token = torch.zeros(1, device=dev)
+            for s in range(n_stages - 1):
+                lo, hi = self.rank_of(s), self.rank_of(s + 1)
+                if self.rank == lo:
+                    dist.send(token, dst=hi, group=self.fwd_group)
+                    dist.recv(token, src=hi, group=self.bwd_group)
+                elif self.rank == hi:
+                    dist.recv(token, src=lo, group=self.fwd_group)
+                    dist.send(token, dst=lo, group=self.bwd_group)
+            torch.cuda.synchronize()
 
     def rank_of(self, stage: int) -> int:
         return self.pipeline_id * self.n_stages + stage
@@ -160,10 +186,10 @@ class PipelineStage:
         def post_recv(op: Op):
             if op.kind == F and not self.is_first and op.mb not in recv_f:
                 t = self._buf()
-                recv_f[op.mb] = (t, dist.irecv(t, src=m.prev_rank))
+                recv_f[op.mb] = (t, dist.irecv(t, src=m.prev_rank, group=m.fwd_group))
             if op.kind == B and not self.is_last and op.mb not in recv_b:
                 t = self._buf()
-                recv_b[op.mb] = (t, dist.irecv(t, src=m.next_rank))
+                recv_b[op.mb] = (t, dist.irecv(t, src=m.next_rank, group=m.bwd_group))
 
         ops = self.schedule
         if ops:
@@ -187,7 +213,7 @@ class PipelineStage:
                 else:
                     saved_out[op.mb] = out
                     payload = out.detach().contiguous()
-                    pending_send.append((dist.isend(payload, dst=m.next_rank), payload))
+                    pending_send.append((dist.isend(payload, dst=m.next_rank, group=m.fwd_group), payload))
             else:
                 out = saved_out.pop(op.mb)
                 if self.is_last:
@@ -199,7 +225,7 @@ class PipelineStage:
                 x = saved_in.pop(op.mb)
                 if not self.is_first:
                     payload = x.grad.contiguous()
-                    pending_send.append((dist.isend(payload, dst=m.prev_rank), payload))
+                    pending_send.append((dist.isend(payload, dst=m.prev_rank, group=m.bwd_group), payload))
         for r, _keepalive in pending_send:
             r.wait()
         return self.losses
