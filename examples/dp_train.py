@@ -19,6 +19,8 @@ def main():
     ap.add_argument("--dmodel", type=int, default=288)
     ap.add_argument("--vocab", type=int, default=32_000)
     ap.add_argument("--fused", action="store_true", help="peer-memory gradient reducer instead of NCCL (GPU only)")
+    ap.add_argument("--kernels", action="store_true", help="run the model on the hand-written kernels (ops/nn.use_kernels)")
+    ap.add_argument("--graph", action="store_true", help="replay forward + backward from a CUDA graph (GPU only)")
     a = ap.parse_args()
     cuda = torch.cuda.is_available()
     if cuda:
@@ -27,22 +29,27 @@ def main():
     rank, dev = dist.get_rank(), ("cuda" if cuda else "cpu")
     torch.manual_seed(0)
     net = LLama(None, a.vocab, a.dmodel, 6, dev, 6, 256)
+    loss_fn = lambda m, t: causalLLMLoss(m(t), t, a.vocab)
+    if a.kernels and cuda:
+        from ddl25spring_b200.ops.nn import kernel_causal_lm_loss, use_kernels
+        use_kernels(net)
+        loss_fn = lambda m, t: kernel_causal_lm_loss(m(t), t)
     ds = iter(SyntheticTokens(a.vocab, 1, 256, skip=rank * 5000))
     if a.mode == "ga":
         reducer = None
         if a.fused and cuda:
             from ddl25spring_b200.parallel.symm_impl import SymmetricArena, SymmetricGradReducer
             reducer = SymmetricGradReducer(SymmetricArena(), sum(p.numel() for p in net.parameters()) + 4096)
-        dp = DataParallel(net, optimizer="adam", lr=8e-4, reducer=reducer)
+        dp = DataParallel(net, optimizer="adam", lr=8e-4, reducer=reducer, graph=a.graph)
         for itr in range(a.iters):
             x = next(ds).to(dev)
-            loss = dp.train_step(lambda m, t: causalLLMLoss(m(t), t, a.vocab), x)
+            loss = dp.train_step(loss_fn, x)
             print(itr, float(loss), flush=True)
     else:
         wa = WeightAveraging(net, torch.optim.Adam(net.parameters(), lr=8e-4))
         for itr in range(a.iters):
             x = next(ds).to(dev)
-            loss = causalLLMLoss(net(x), x, a.vocab)
+            loss = loss_fn(net, x)
             loss.backward()
             wa.step()
             print(itr, float(loss), flush=True)

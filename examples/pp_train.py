@@ -21,6 +21,7 @@ def main():
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--dmodel", type=int, default=288)
     ap.add_argument("--vocab", type=int, default=32_000)
+    ap.add_argument("--kernels", action="store_true", help="run the stage modules on the hand-written kernels (GPU only)")
     a = ap.parse_args()
     cuda = torch.cuda.is_available()
     if cuda:
@@ -32,6 +33,9 @@ def main():
     torch.manual_seed(0)
     full = LLama(None, a.vocab, a.dmodel, 6, dev, 6, 256)
     stage = full.split_stages(mesh.n_stages)[mesh.stage_id]
+    if a.kernels and cuda:
+        from ddl25spring_b200.ops.nn import use_kernels
+        use_kernels(stage)
     n_micro = 1 if a.schedule == "sequential" else a.micro
     st = PipelineStage(stage, mesh, (1, 256, a.dmodel), schedule=a.schedule, n_micro=n_micro,
                        loss_fn=lambda o, t: causalLLMLoss(o, t, a.vocab), device=dev)
