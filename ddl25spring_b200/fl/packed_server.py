@@ -78,9 +78,18 @@ class PackedFedAvgServer:
             X[i, :len(y)] = x.reshape(len(y), 784)
             Y[i, :len(y)] = y
         self.data_on_device = data_on_device
+        self.X_u8 = None
         if data_on_device:
             self.X_all, self.Y_all = X.to(self.device), Y.to(self.device)
         else:
+            # Host-resident shards cross PCIe as the raw uint8 pixels they were made from (1 byte per pixel instead of 4) when
+            # the float images are exactly the MNIST transform of 8-bit pixels; the transform then runs on the device
+            # (csrc/data.cu), bit-identical to the host one.  Anything else is shipped as fp32.
+            from ..core.data import MNIST_MEAN, MNIST_STD
+            u8 = torch.round((X * MNIST_STD + MNIST_MEAN) * 255.0).clamp_(0, 255).to(torch.uint8)
+            if self.device.type == "cuda" and torch.equal(u8.float().div_(255.0).sub_(MNIST_MEAN).div_(MNIST_STD), X):
+                self.X_u8 = u8.pin_memory()
+                self._norm = (MNIST_MEAN, MNIST_STD)
             self.X_all, self.Y_all = X.pin_memory(), Y.pin_memory()
         self.h2d_bytes_last_round = 0
 
@@ -133,7 +142,8 @@ class PackedFedAvgServer:
                 return (torch.zeros(G, self.n_max, 784, device=self.device),
                         torch.zeros(G, self.n_max, dtype=torch.int64, device=self.device),
                         ph.pin_memory() if cuda else ph,
-                        torch.zeros(G, n_perm, dtype=torch.int32, device=self.device))
+                        torch.zeros(G, n_perm, dtype=torch.int32, device=self.device),
+                        torch.zeros(G, self.n_max, 784, dtype=torch.uint8, device=self.device) if self.X_u8 is not None else None)
             # two staging sets: while round r trains out of one, round r+1's shards / permutations are staged into the other
             self._bufs[G] = (w_rows, [staging(), staging()])
         return self._engines[G]
@@ -142,23 +152,30 @@ class PackedFedAvgServer:
         """Host permutations + data movement for one round into staging set ``slot`` (on the copy stream on GPU)."""
         G = len(mine)
         self._engine(G)
-        Xg, Yg, perm_host, perm_dev = self._bufs[G][1][slot]
+        Xg, Yg, perm_host, perm_dev, Ug = self._bufs[G][1][slot]
         counts = [self.client_sample_counts[c] for c in mine]
         h2d = 0
-        for i, c in enumerate(mine):
-            seed = client_round_seed(self.seed, c, nr_round, self.nr_clients_per_round)
-            for e, pm in enumerate(epoch_permutations(counts[i], seed, self.nr_local_epochs)):
-                perm_host[i, e * self.n_max:e * self.n_max + counts[i]] = pm.to(torch.int32)
         cuda = self.device.type == "cuda"
         ctx = torch.cuda.stream(self._copy_stream) if cuda else _NullCtx()
         if cuda and self._slot_free[slot] is not None:
             self._copy_stream.wait_event(self._slot_free[slot])     # the round that last trained out of this set is done
         with ctx:
+            # shard copies first: they run on the copy engine while the host draws this round's permutations below
             for i, c in enumerate(mine):
-                Xg[i].copy_(self.X_all[c], non_blocking=True)        # pinned host -> device in the end-to-end mode
+                if Ug is not None:
+                    Ug[i].copy_(self.X_u8[c], non_blocking=True)     # pinned host -> device: raw pixels, 1 byte each
+                else:
+                    Xg[i].copy_(self.X_all[c], non_blocking=True)    # pinned host -> device in the end-to-end mode
                 Yg[i].copy_(self.Y_all[c], non_blocking=True)
                 if not self.data_on_device:
-                    h2d += self.X_all[c].numel() * 4 + self.Y_all[c].numel() * 8
+                    h2d += self.X_all[c].numel() * (1 if Ug is not None else 4) + self.Y_all[c].numel() * 8
+            if Ug is not None:
+                ops.u8_normalize(Ug, self._norm[0], self._norm[1], out=Xg)   # on the copy stream, behind the copies
+        for i, c in enumerate(mine):
+            seed = client_round_seed(self.seed, c, nr_round, self.nr_clients_per_round)
+            for e, pm in enumerate(epoch_permutations(counts[i], seed, self.nr_local_epochs)):
+                perm_host[i, e * self.n_max:e * self.n_max + counts[i]] = pm.to(torch.int32)
+        with ctx:
             perm_dev.copy_(perm_host, non_blocking=True)
             h2d += perm_host.numel() * 4
             ready = None
@@ -175,7 +192,7 @@ class PackedFedAvgServer:
             staged = self._stage(nr_round, mine, self._next_slot)
             self._next_slot ^= 1
         W = self._bufs[G][0]
-        Xg, Yg, _perm_host, perm_dev = self._bufs[G][1][staged["slot"]]
+        Xg, Yg, _perm_host, perm_dev, _Ug = self._bufs[G][1][staged["slot"]]
         gflat = self.arena.flat.detach()
         W.copy_(gflat.unsqueeze(0).expand(G, P))                 # server -> clients broadcast (hfl_complete.py:356)
         self.h2d_bytes_last_round = staged["h2d"]

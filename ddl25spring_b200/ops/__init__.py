@@ -205,3 +205,16 @@ def vae_loss(x_recon, x, mu, logvar, want_grad: bool = False):
                               _lib.p(mu.contiguous()), _lib.p(logvar.contiguous()), _lib.i64(mu.numel()), _lib.p(loss),
                               _lib.p(gs[0]), _lib.p(gs[1]), _lib.p(gs[2]), _lib.f32(1.0), _lib.stream()), "ddl_vae_loss")
     return (loss, gs) if want_grad else loss
+
+
+def u8_normalize(u8: torch.Tensor, mean: float, std: float, out: torch.Tensor | None = None) -> torch.Tensor:
+    """``(u8 / 255 - mean) / std`` as fp32, bit-identical on CPU and GPU (the input transform of hfl_complete.py:19-24)."""
+    if out is None:
+        out = torch.empty(u8.shape, dtype=torch.float32, device=u8.device)
+    if not u8.is_cuda:
+        out.copy_(u8.float().div_(255.0).sub_(mean).div_(std))
+        return out
+    assert u8.dtype == torch.uint8 and u8.is_contiguous() and out.is_contiguous() and u8.numel() % 4 == 0
+    _lib.check(_lib.lib().ddl_u8_normalize(_lib.p(u8), _lib.p(out), _lib.i64(u8.numel()), _lib.f32(mean), _lib.f32(std), _lib.stream()),
+               "ddl_u8_normalize")
+    return out

@@ -233,6 +233,10 @@ int ddl_gram_rowgather_tcgen05(const float* const* part_ptrs, int n_parts, int r
  * orders the GPUs with barriers before (inputs written) and after (results visible). */
 int ddl_nvls_allreduce(float* multicast_ptr, int64_t d0, int64_t d1, float scale, int max_ctas, void* stream);
 
+/* ---- input pipeline: out = (in / 255 - mean) / std, bit-identical to the host float transform (csrc/data.cu) ---------------
+ * (ref: ToTensor + Normalize in the DataLoader, lab/tutorial_1a/hfl_complete.py:19-24.)  n % 4 == 0. */
+int ddl_u8_normalize(const unsigned char* in, float* out, int64_t n, float mean, float std, void* stream);
+
 /* ---- K16 element-wise: fused QKV split + head transpose + rotary embedding, SwiGLU (csrc/llama_ops.cu) ---------------------
  * (ref: simplellm LLaMA block internals used by lab/tutorial_1b/primer/intro.py:17,28.)
  * qkv: [B, T, 3, H, hd]; q, k, v: [B, H, T, hd]; cos/sin: [>= T, hd/2].  backward == 0: qkv -> q, k, v (q, k rotated);

@@ -8,7 +8,7 @@ srv = PackedFedAvgServer(0.01, 100, split(ds.train, 100, True, 10), 0.08, 1, 10,
 srv.run(3)
 torch.cuda.synchronize()
 G = 8
-eng = srv._engine(G); W, stag = srv._bufs[G]; Xg, Yg, ph, pd = stag[0]
+eng = srv._engine(G); W, stag = srv._bufs[G]; Xg, Yg, ph, pd, _ = stag[0]
 for name, fn in [("local_train", lambda: eng.local_train(W, Xg, Yg, pd, [600] * G, 100, 1, 0.01, seed=1)),
                  ("test", lambda: srv._eval.eval_logits(srv.arena.flat, srv._test_xy[0], srv._test_xy[1], srv._correct, want_logits=False)),
                  ("train_local_clients", lambda: srv._train_local_clients(5, list(range(8))))]:

@@ -115,3 +115,25 @@ def test_local_train_learns(cuda_lib):
     ev.eval_logits(W.mean(0).contiguous(), xt, yt, c1, want_logits=False)
     assert int(c1) > int(c0) + 150, (int(c0), int(c1))
     assert torch.isfinite(W).all()
+
+
+def test_u8_transport_is_bit_identical_to_resident_floats():
+    """End-to-end mode ships raw uint8 pixels and normalises on the device: same bits as the host transform, same model."""
+    import torch
+    from ddl25spring_b200 import ops
+    from ddl25spring_b200.core.data import MNIST_MEAN, MNIST_STD, SyntheticMNIST, split
+    from ddl25spring_b200.fl.packed_server import PackedFedAvgServer
+    u8 = torch.randint(0, 256, (1000, 784), dtype=torch.uint8)
+    host = u8.float().div_(255.0).sub_(MNIST_MEAN).div_(MNIST_STD)
+    assert torch.equal(ops.u8_normalize(u8.cuda(), MNIST_MEAN, MNIST_STD).cpu(), host)
+    ds = SyntheticMNIST(n_train=1600, n_test=256, seed=0)
+    flats = []
+    for on_dev in (True, False):
+        srv = PackedFedAvgServer(0.05, 50, split(ds.train, 8, True, 1), 0.5, 1, 3, test_set=ds.test, device="cuda",
+                                 data_on_device=on_dev, prefetch_next=on_dev)
+        srv.run(2)
+        if not on_dev:
+            assert srv.X_u8 is not None
+            assert srv.h2d_bytes_last_round == 4 * 200 * 784 + 4 * 200 * 8 + 4 * 200 * 4      # u8 pixels + int64 labels + int32 perms
+        flats.append(srv.arena.flat.detach().clone())
+    assert torch.equal(flats[0], flats[1])
