@@ -59,6 +59,27 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   }
 }
 
+// Same update with the step counter read from device memory: inside a CUDA graph the counter cannot be a by-value argument.
+__global__ void __launch_bounds__(256) adam_devstep_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                                           float* __restrict__ v, AdamArgs a, const int* __restrict__ step_ptr,
+                                                           int64_t nvec) {
+  const float step = (float)max(1, *step_ptr);
+  a.bc1 = 1.f - powf(a.b1, step);
+  a.bc2_rsqrt = 1.f / sqrtf(1.f - powf(a.b2, step));
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    float4 w = reinterpret_cast<float4*>(p)[i];
+    const float4 d = ddl::ld_stream(reinterpret_cast<const float4*>(g) + i);
+    float4 mm = reinterpret_cast<float4*>(m)[i];
+    float4 vv = reinterpret_cast<float4*>(v)[i];
+    adam1(w.x, d.x, mm.x, vv.x, a); adam1(w.y, d.y, mm.y, vv.y, a);
+    adam1(w.z, d.z, mm.z, vv.z, a); adam1(w.w, d.w, mm.w, vv.w, a);
+    reinterpret_cast<float4*>(p)[i] = w;
+    reinterpret_cast<float4*>(m)[i] = mm;
+    reinterpret_cast<float4*>(v)[i] = vv;
+  }
+}
+
 int grid_for(int64_t nvec) {
   int64_t g = (nvec + 255) / 256;
   if (g > (int64_t)kNumSMs * 8) g = (int64_t)kNumSMs * 8;
@@ -91,6 +112,21 @@ int ddl_adam_step(float* params, const float* grads, float* exp_avg, float* exp_
   a.bc1 = 1.f - powf(beta1, (float)step);
   a.bc2_rsqrt = 1.f / sqrtf(1.f - powf(beta2, (float)step));
   adam_kernel<<<grid_for(n / 4), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, a, n / 4);
+  DDL_LAUNCH_CHECK();
+  return DDL_OK;
+}
+
+int ddl_adam_step_dev(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, const int* step_dev,
+                      float lr, float beta1, float beta2, float eps, float weight_decay, int decoupled, float grad_scale,
+                      void* stream) {
+  DDL_REQUIRE(n % 4 == 0, "n must be a multiple of 4 floats (arenas are padded)");
+  DDL_REQUIRE(step_dev != nullptr, "device step counter is NULL");
+  if (n == 0) return DDL_OK;
+  AdamArgs a;
+  a.lr = lr; a.b1 = beta1; a.b2 = beta2; a.eps = eps; a.wd = weight_decay; a.decoupled = decoupled;
+  a.gscale = grad_scale;
+  a.bc1 = 1.f; a.bc2_rsqrt = 1.f;
+  adam_devstep_kernel<<<grid_for(n / 4), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, a, step_dev, n / 4);
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

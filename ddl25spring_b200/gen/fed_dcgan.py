@@ -61,13 +61,86 @@ def dcgan_local_steps(pair: DCGANPair, images: torch.Tensor, steps: int, batch: 
     return float(d_loss.detach()), float(g_loss.detach())
 
 
+class GraphedDCGANStep:
+    """One full DCGAN iteration (D step on real + fake, fused Adam on D, G step through the updated D, fused Adam on G) captured
+    into ONE CUDA graph over the pair's static arenas.  The Adam moments and the bias-correction step live in static device
+    buffers (``ddl_adam_step_dev`` reads the step from memory), so the same graph serves every client: its moments are copied
+    in before and out after its local steps."""
+
+    def __init__(self, pair: DCGANPair, batch: int, lr: float, beta1: float = 0.5):
+        from ..utils.graphs import GraphedStep
+        dev = pair.device
+        pg, pd = pair.n_param_elems()
+        self.pg4, self.pd4 = _pad4(pg), _pad4(pd)
+        z = lambda n: torch.zeros(n, device=dev)
+        self.m_g, self.v_g, self.m_d, self.v_d = z(self.pg4), z(self.pg4), z(self.pd4), z(self.pd4)
+        self.step_t = torch.zeros((), dtype=torch.int32, device=dev)
+        G, D = pair.G, pair.D
+
+        def it(real, zz):
+            ones, zeros = torch.ones(batch, device=dev), torch.zeros(batch, device=dev)
+            self.step_t.add_(1)
+            pair.da.grad.zero_()
+            fake = G(zz)
+            d_loss = F.binary_cross_entropy_with_logits(D(real), ones) + F.binary_cross_entropy_with_logits(D(fake.detach()), zeros)
+            d_loss.backward()
+            ops.adam_step(pair.da.flat[:self.pd4], pair.da.grad[:self.pd4], self.m_d, self.v_d, self.step_t, lr, beta1, 0.999)
+            pair.ga.grad.zero_()
+            g_loss = F.binary_cross_entropy_with_logits(D(fake), ones)
+            g_loss.backward()
+            ops.adam_step(pair.ga.flat[:self.pg4], pair.ga.grad[:self.pg4], self.m_g, self.v_g, self.step_t, lr, beta1, 0.999)
+            return torch.stack([d_loss.detach(), g_loss.detach()])
+
+        saved = [t.detach().clone() for t in (pair.ga.flat, pair.da.flat)]
+        buffers = [(b, b.clone()) for m in (G, D) for b in m.buffers()]
+        ex_real = torch.zeros(batch, 3, 64, 64, device=dev)
+        ex_z = torch.zeros(batch, pair.nz, device=dev)
+        G.train(); D.train()
+        self.graph = GraphedStep(it, (ex_real, ex_z))
+        with torch.no_grad():                       # undo the warm-up / capture iterations
+            pair.ga.flat.copy_(saved[0]); pair.da.flat.copy_(saved[1])
+            for b, v in buffers:
+                b.copy_(v)
+            for t in (self.m_g, self.v_g, self.m_d, self.v_d):
+                t.zero_()
+            self.step_t.zero_()
+
+    def load(self, m_g, v_g, m_d, v_d, step0: int) -> None:
+        self.m_g.copy_(m_g); self.v_g.copy_(v_g); self.m_d.copy_(m_d); self.v_d.copy_(v_d)
+        self.step_t.fill_(step0)
+
+    def store(self, m_g, v_g, m_d, v_d) -> None:
+        m_g.copy_(self.m_g); v_g.copy_(self.v_g); m_d.copy_(self.m_d); v_d.copy_(self.v_d)
+
+    def __call__(self, real, z):
+        return self.graph(real, z)
+
+
+def dcgan_local_steps_graphed(pair: DCGANPair, gstep: GraphedDCGANStep, images: torch.Tensor, steps: int, batch: int,
+                              gen: torch.Generator, m_g, v_g, m_d, v_d, step0: int):
+    """Same iterations and the same random draws as :func:`dcgan_local_steps`, each replayed from the captured graph."""
+    dev = pair.device
+    pair.G.train(); pair.D.train()
+    gstep.load(m_g, v_g, m_d, v_d, step0)
+    losses = None
+    for _ in range(steps):
+        idx = torch.randint(0, len(images), (batch,), generator=gen)
+        real = images[idx].to(dev)
+        z = torch.randn(batch, pair.nz, generator=gen).to(dev)
+        losses = gstep(real, z)
+    gstep.store(m_g, v_g, m_d, v_d)
+    d_loss, g_loss = losses.tolist()
+    return d_loss, g_loss
+
+
 def _pad4(n: int) -> int:
     return (n + 3) // 4 * 4
 
 
 class FederatedDCGAN:
     def __init__(self, client_images: list[torch.Tensor], client_fraction: float = 1.0, local_steps: int = 2, batch_size: int = 16,
-                 lr: float = 2e-4, seed: int = 0, device=None, ngf: int = 64, ndf: int = 64, kernel_convs: bool | None = None):
+                 lr: float = 2e-4, seed: int = 0, device=None, ngf: int = 64, ndf: int = 64, kernel_convs: bool | None = None,
+                 graph: bool | None = None):
         self.device = torch.device(device) if device is not None else torch.device("cuda" if torch.cuda.is_available() else "cpu")
         self.clients = client_images
         self.counts = [len(c) for c in client_images]
@@ -78,6 +151,9 @@ class FederatedDCGAN:
         if kernel_convs is None:
             kernel_convs = self.device.type == "cuda"
         self.kernel_convs = kernel_convs
+        # one CUDA graph per iteration (GraphedDCGANStep): default on the kernel path, where launch overhead dominates
+        self.graph = (kernel_convs if graph is None else graph) and self.device.type == "cuda"
+        self._gstep = None
         self.glob = DCGANPair(self.device, ngf=ngf, ndf=ndf, kernel_convs=kernel_convs)
         self.work = DCGANPair(self.device, ngf=ngf, ndf=ndf, kernel_convs=kernel_convs)
         self.rank, self.world = (dist.get_rank(), dist.get_world_size()) if dist.is_initialized() else (0, 1)
@@ -108,8 +184,17 @@ class FederatedDCGAN:
                     self.work.da.flat.copy_(self.glob.da.flat)
                 mom = self._moments(c)
                 gen = torch.Generator().manual_seed(self.seed + c + 1 + r * self.k)
-                losses.append(dcgan_local_steps(self.work, self.clients[c], self.local_steps, self.batch, self.lr, gen,
-                                                mom[0], mom[1], mom[2], mom[3], mom[4]))
+                if self.graph and len(self.clients[c]) >= 1:
+                    if self._gstep is None:
+                        self._gstep = GraphedDCGANStep(self.work, self.batch, self.lr)
+                        with torch.no_grad():        # capture ran on the work pair: reload the global model
+                            self.work.ga.flat.copy_(self.glob.ga.flat)
+                            self.work.da.flat.copy_(self.glob.da.flat)
+                    losses.append(dcgan_local_steps_graphed(self.work, self._gstep, self.clients[c], self.local_steps, self.batch, gen,
+                                                            mom[0], mom[1], mom[2], mom[3], mom[4]))
+                else:
+                    losses.append(dcgan_local_steps(self.work, self.clients[c], self.local_steps, self.batch, self.lr, gen,
+                                                    mom[0], mom[1], mom[2], mom[3], mom[4]))
                 mom[4] += self.local_steps
                 UG[i].copy_(self.work.ga.flat.detach())
                 UD[i].copy_(self.work.da.flat.detach())

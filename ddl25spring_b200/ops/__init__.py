@@ -141,8 +141,15 @@ def adam_step(params, grads, exp_avg, exp_avg_sq, step: int, lr: float = 1e-3, b
               grad_scale: float = 1.0):
     if not params.is_cuda:
         g = grads * grad_scale if grad_scale != 1.0 else grads
-        return ref.adam_step(params, g, exp_avg, exp_avg_sq, step, lr, beta1, beta2, eps, weight_decay, decoupled)
+        return ref.adam_step(params, g, exp_avg, exp_avg_sq, int(step), lr, beta1, beta2, eps, weight_decay, decoupled)
     L = _lib.lib()
+    if torch.is_tensor(step):          # device-resident int32 counter: the step can live inside a CUDA graph
+        assert step.is_cuda and step.dtype == torch.int32
+        _lib.check(L.ddl_adam_step_dev(_lib.p(_lib.req_f32(params)), _lib.p(grads), _lib.p(exp_avg), _lib.p(exp_avg_sq),
+                                       _lib.i64(params.numel()), _lib.p(step), _lib.f32(lr), _lib.f32(beta1), _lib.f32(beta2),
+                                       _lib.f32(eps), _lib.f32(weight_decay), int(decoupled), _lib.f32(grad_scale),
+                                       _lib.stream()), "ddl_adam_step_dev")
+        return params
     _lib.check(L.ddl_adam_step(_lib.p(_lib.req_f32(params)), _lib.p(grads), _lib.p(exp_avg), _lib.p(exp_avg_sq),
                                _lib.i64(params.numel()), int(step), _lib.f32(lr), _lib.f32(beta1), _lib.f32(beta2),
                                _lib.f32(eps), _lib.f32(weight_decay), int(decoupled), _lib.f32(grad_scale),

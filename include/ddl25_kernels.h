@@ -77,6 +77,11 @@ int ddl_adam_step(float* params, const float* grads, float* exp_avg, float* exp_
                   float lr, float beta1, float beta2, float eps, float weight_decay, int decoupled,
                   float grad_scale, void* stream);
 
+/* same update, bias-correction step read from a DEVICE int (>= 1): for optimizer steps captured into a CUDA graph */
+int ddl_adam_step_dev(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, const int* step_dev,
+                      float lr, float beta1, float beta2, float eps, float weight_decay, int decoupled, float grad_scale,
+                      void* stream);
+
 /* ---- K13: softmax cross-entropy, value + gradient in one pass ---------------------------------
  * (ref: log_softmax+nll_loss hfl_complete.py:62,78; soft-target CE vfl.py:51,79; causalLLMLoss
  *  lab/tutorial_1b/primer/intro.py:29).  Exactly one of target_idx (int64, element stride

@@ -298,3 +298,22 @@ def test_fedavg_resnet_nhwc_graphed_clients_match_eager():
         flats.append(srv.arena.flat.detach().clone())
     assert torch.isfinite(flats[0]).all()
     assert torch.allclose(flats[0], flats[1], atol=1e-5), (flats[0] - flats[1]).abs().max()
+
+
+@pytest.mark.gpu
+def test_federated_dcgan_graphed_iterations_match_eager():
+    """GraphedDCGANStep (whole D+G iteration incl. fused Adam with a device-resident step counter) == eager iterations."""
+    from ddl25spring_b200.gen.fed_dcgan import FederatedDCGAN
+    torch.manual_seed(0)
+    clients = [torch.rand(24, 3, 64, 64) * 2 - 1 for _ in range(2)]
+    feds = []
+    for graph in (False, True):
+        fed = FederatedDCGAN(clients, client_fraction=1.0, local_steps=2, batch_size=8, device="cuda", ngf=32, ndf=32, graph=graph, seed=3)
+        assert fed.graph == graph
+        fed.run(2)
+        feds.append(fed)
+    a, b = feds
+    assert torch.allclose(a.glob.ga.flat, b.glob.ga.flat, atol=2e-5), (a.glob.ga.flat - b.glob.ga.flat).abs().max()
+    assert torch.allclose(a.glob.da.flat, b.glob.da.flat, atol=2e-5), (a.glob.da.flat - b.glob.da.flat).abs().max()
+    for x, y in zip(a.history, b.history):
+        assert abs(x[0] - y[0]) < 1e-4 and abs(x[1] - y[1]) < 1e-4
