@@ -48,15 +48,27 @@ class GeneratorNHWC(nn.Module):
         blocks.append(nn.Sequential(_Weight(ngf, 4, 4, 4, zero_tail=4 - nc)))
         self.blocks = nn.Sequential(*blocks)
 
+    def _block(self, i: int, y):
+        blk = self.blocks[i]
+        if i == 0:
+            z = y.reshape(y.shape[0], self.nz)
+            w0 = blk[0].weight
+            y = kernel_linear(z, w0.view(-1, self.nz), None, precise=False).view(z.shape[0], 4, 4, w0.shape[2])
+            return K.batch_norm_nhwc(y, blk[1], relu=True)
+        if i == len(self.blocks) - 1:
+            img = K.conv_transpose2d_nhwc(y, blk[0].weight, None, 2, 1, act="tanh")
+            return img[..., :self.nc].permute(0, 3, 1, 2)
+        return K.batch_norm_nhwc(K.conv_transpose2d_nhwc(y, blk[0].weight, None, 2, 1), blk[1], relu=True)
+
     def forward(self, z):
-        z = z.reshape(z.shape[0], self.nz)
-        w0 = self.blocks[0][0].weight
-        y = kernel_linear(z, w0.view(-1, self.nz), None, precise=False).view(z.shape[0], 4, 4, w0.shape[2])
-        y = K.batch_norm_nhwc(y, self.blocks[0][1], relu=True)
-        for blk in self.blocks[1:-1]:
-            y = K.batch_norm_nhwc(K.conv_transpose2d_nhwc(y, blk[0].weight, None, 2, 1), blk[1], relu=True)
-        img = K.conv_transpose2d_nhwc(y, self.blocks[-1][0].weight, None, 2, 1, act="tanh")
-        return img[..., :self.nc].permute(0, 3, 1, 2)
+        y = z
+        for i in range(len(self.blocks)):
+            y = self._block(i, y)
+        return y
+
+    def stages(self, cut: int = 3):
+        """Two pipeline stages (blocks [0, cut) | [cut, end)); NHWC activations travel between them."""
+        return _Stage(self, range(0, cut)), _Stage(self, range(cut, len(self.blocks)))
 
 
 class DiscriminatorNHWC(nn.Module):
@@ -70,13 +82,39 @@ class DiscriminatorNHWC(nn.Module):
         blocks.append(nn.Sequential(_Weight(1, 4, 4, chans[-1])))
         self.blocks = nn.Sequential(*blocks)
 
+    def _block(self, i: int, y):
+        blk = self.blocks[i]
+        if i == 0:
+            x = F.pad(y.permute(0, 2, 3, 1), (0, 4 - self.nc))                   # NCHW image -> NHWC, 4 channels (16-byte pixels)
+            return K.conv2d_nhwc(x, blk[0].weight, 2, 1, act="leaky_relu", slope=0.2)
+        if i == len(self.blocks) - 1:
+            w = blk[0].weight
+            return kernel_linear(y.reshape(y.shape[0], -1), w.view(1, -1), None, precise=False).squeeze(1)   # logits
+        return K.batch_norm_nhwc(K.conv2d_nhwc(y, blk[0].weight, 2, 1), blk[1], leaky=0.2)
+
     def forward(self, x):
-        x = F.pad(x.permute(0, 2, 3, 1), (0, 4 - self.nc))                       # NCHW image -> NHWC, 4 channels (16-byte pixels)
-        y = K.conv2d_nhwc(x, self.blocks[0][0].weight, 2, 1, act="leaky_relu", slope=0.2)
-        for blk in self.blocks[1:-1]:
-            y = K.batch_norm_nhwc(K.conv2d_nhwc(y, blk[0].weight, 2, 1), blk[1], leaky=0.2)
-        w = self.blocks[-1][0].weight
-        return kernel_linear(y.reshape(y.shape[0], -1), w.view(1, -1), None, precise=False).squeeze(1)   # logits
+        y = x
+        for i in range(len(self.blocks)):
+            y = self._block(i, y)
+        return y
+
+    def stages(self, cut: int = 2):
+        return _Stage(self, range(0, cut)), _Stage(self, range(cut, len(self.blocks)))
+
+
+class _Stage(nn.Module):
+    """A contiguous run of blocks of a GeneratorNHWC / DiscriminatorNHWC as its own module (pipeline stage)."""
+
+    def __init__(self, net: nn.Module, idx):
+        super().__init__()
+        self.idx = list(idx)
+        self.blocks = nn.ModuleList(net.blocks[i] for i in self.idx)      # registers exactly this stage's parameters
+        object.__setattr__(self, "_net", net)                             # not a submodule: no parameter duplication
+
+    def forward(self, y):
+        for i in self.idx:
+            y = self._net._block(i, y)
+        return y
 
 
 def from_torch_layout(sd: dict, kind: str) -> dict:

@@ -99,6 +99,31 @@ def resnet18_nhwc(num_classes: int = 10) -> ResNet18NHWC:
     return ResNet18NHWC(num_classes)
 
 
+def split_resnet18_nhwc_two_stage(model: ResNet18NHWC) -> tuple[nn.Module, nn.Module]:
+    """2-stage model-parallel split (BASELINE.json config 5): stem+layer1+layer2 | layer3+layer4+fc; the NHWC activation
+    [N, H/8, W/8, 128] travels between the stages (same cut as models.resnet.split_resnet18_two_stage)."""
+
+    class Front(nn.Module):
+        def __init__(s):
+            super().__init__()
+            s.conv1, s.bn1, s.layer1, s.layer2 = model.conv1, model.bn1, model.layer1, model.layer2
+
+        def forward(s, x):
+            y = K.max_pool3x3s2_nhwc(K.batch_norm_nhwc(s.conv1(x), s.bn1, relu=True))
+            return s.layer2(s.layer1(y))
+
+    class Back(nn.Module):
+        def __init__(s):
+            super().__init__()
+            s.layer3, s.layer4, s.fc = model.layer3, model.layer4, model.fc
+
+        def forward(s, y):
+            y = s.layer4(s.layer3(y))
+            return kernel_linear(K.global_avg_pool_nhwc(y), s.fc.weight, s.fc.bias, precise=False)
+
+    return Front(), Back()
+
+
 def from_torch_layout(sd: dict) -> dict:
     """State dict of ``models.resnet.ResNet18`` (OIHW conv weights) -> ``ResNet18NHWC`` (OHWI; stem padded to 4 channels)."""
     out = {}

@@ -317,3 +317,24 @@ def test_federated_dcgan_graphed_iterations_match_eager():
     assert torch.allclose(a.glob.da.flat, b.glob.da.flat, atol=2e-5), (a.glob.da.flat - b.glob.da.flat).abs().max()
     for x, y in zip(a.history, b.history):
         assert abs(x[0] - y[0]) < 1e-4 and abs(x[1] - y[1]) < 1e-4
+
+
+def test_nhwc_models_split_into_two_pipeline_stages():
+    from ddl25spring_b200.models import dcgan_nhwc
+    from ddl25spring_b200.models.resnet_nhwc import split_resnet18_nhwc_two_stage
+    torch.manual_seed(0)
+    net = ResNet18NHWC(10).eval()
+    front, back = split_resnet18_nhwc_two_stage(net)
+    x = torch.randn(2, 3, 32, 32)
+    mid = front(x)
+    assert mid.shape == (2, 4, 4, 128)
+    assert torch.allclose(back(mid), net(x), atol=1e-5)
+    assert sum(p.numel() for p in front.parameters()) + sum(p.numel() for p in back.parameters()) == sum(p.numel() for p in net.parameters())
+    G, D = dcgan_nhwc.GeneratorNHWC(100, 8).eval(), dcgan_nhwc.DiscriminatorNHWC(8).eval()
+    z = torch.randn(2, 100)
+    g0, g1 = G.stages()
+    assert torch.allclose(g1(g0(z)), G(z), atol=1e-6)
+    d0, d1 = D.stages()
+    img = G(z)
+    assert torch.allclose(d1(d0(img)), D(img), atol=1e-6)
+    assert sum(p.numel() for s in (g0, g1) for p in s.parameters()) == sum(p.numel() for p in G.parameters())
