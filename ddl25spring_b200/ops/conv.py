@@ -21,6 +21,7 @@ DCGAN layers of the north-star configs.
 from __future__ import annotations
 
 import ctypes as C
+import functools
 
 import torch
 import torch.nn.functional as F
@@ -77,16 +78,41 @@ def dgrad_taps(kh: int, kw: int, stride: int, pad: int):
     return phases
 
 
+@functools.lru_cache(maxsize=None)
+def _tap_arrays(taps: tuple):
+    """ctypes int arrays (map, dh, dw, weight tap) of a tap list - built once per distinct list (host time matters in eager mode)."""
+    return tuple(_ints([t[i] for t in taps]) for i in range(4))
+
+
+@functools.lru_cache(maxsize=None)
+def _fwd_taps_c(kh, kw, stride, pad):
+    return tuple(fwd_taps(kh, kw, stride, pad))
+
+
+@functools.lru_cache(maxsize=None)
+def _dgrad_taps_c(kh, kw, stride, pad):
+    """(all taps concatenated, ctypes phase_begin or None) of the input gradient."""
+    phases = dgrad_taps(kh, kw, stride, pad)
+    if stride == 1:
+        return tuple(phases[0]), None
+    taps, begin = [], [0]
+    for t in phases:
+        taps += t
+        begin.append(len(taps))
+    return tuple(taps), _ints(begin)
+
+
 def _tap_gemm(maps, N, Ha, Wa, Ca, w, w_mn, taps, out, Hh, Ww, o_off, o_sn, o_sh, o_sw, bias=None, alpha=1.0, beta=0.0, act=None,
               slope=0.2, phase_begin=None, phase_off=None):
     Cout, T, Cin = w.shape[0], w.shape[1] * w.shape[2], w.shape[3]
     ws = _workspace(out.device)
     ptrs = _lib.host_ptrs([m.data_ptr() for m in maps])
     n_phases = len(phase_off) if phase_off else 1
+    a0, a1, a2, a3 = _tap_arrays(taps)
     _lib.check(_lib.lib().ddl_conv_tap_gemm(
         ptrs, len(maps), int(N), int(Ha), int(Wa), int(Ca), _lib.p(w), int(Cout), int(T), int(Cin), int(w_mn),
-        _ints([t[0] for t in taps]), _ints([t[1] for t in taps]), _ints([t[2] for t in taps]), _ints([t[3] for t in taps]), len(taps),
-        n_phases, _ints(phase_begin) if phase_off else None, (C.c_int64 * n_phases)(*phase_off) if phase_off else None,
+        a0, a1, a2, a3, len(taps),
+        n_phases, phase_begin if phase_off else None, (C.c_int64 * n_phases)(*phase_off) if phase_off else None,
         _lib.p(out), int(Hh), int(Ww), _lib.i64(o_off), _lib.i64(o_sn), _lib.i64(o_sh), _lib.i64(o_sw), _lib.p(bias),
         _lib.f32(alpha), _lib.f32(beta), int(ACT[act]), _lib.f32(slope), _lib.p(ws["scratch"]), _lib.i64(ws["scratch"].numel()),
         _lib.stream()), "ddl_conv_tap_gemm")
@@ -115,7 +141,7 @@ def _fprop(x, ph, w, stride, pad, bias=None, act=None, slope=0.2):
         maps = [ph[i] for i in range(4)]
     Ho, Wo = _out_size(H, kh, stride, pad), _out_size(W, kw, stride, pad)
     y = torch.empty((N, Ho, Wo, Cout), device=w.device, dtype=torch.float32)
-    _tap_gemm(maps, N, Ha, Wa, Cin, w, 0, fwd_taps(kh, kw, stride, pad), y, Ho, Wo, 0, Ho * Wo * Cout, Wo * Cout, Cout, bias=bias,
+    _tap_gemm(maps, N, Ha, Wa, Cin, w, 0, _fwd_taps_c(kh, kw, stride, pad), y, Ho, Wo, 0, Ho * Wo * Cout, Wo * Cout, Cout, bias=bias,
               act=act, slope=slope)
     return y
 
@@ -124,17 +150,13 @@ def _dgrad(dy, w, stride, pad, H, W, bias=None, act=None, slope=0.2):
     """dy [N,Ho,Wo,Cout] -> dx [N,H,W,Cin] (also the forward of a transposed convolution, with bias / activation)."""
     Cout, kh, kw, Cin = w.shape
     N, Ho, Wo, _ = dy.shape
-    phases = dgrad_taps(kh, kw, stride, pad)
+    taps, begin = _dgrad_taps_c(kh, kw, stride, pad)
     dx = torch.empty((N, H, W, Cin), device=dy.device, dtype=torch.float32)
     if stride == 1:
-        _tap_gemm([dy], N, Ho, Wo, Cout, w, 1, phases[0], dx, H, W, 0, H * W * Cin, W * Cin, Cin, bias=bias, act=act, slope=slope)
+        _tap_gemm([dy], N, Ho, Wo, Cout, w, 1, taps, dx, H, W, 0, H * W * Cin, W * Cin, Cin, bias=bias, act=act, slope=slope)
         return dx
     assert H % 2 == 0 and W % 2 == 0
     # the four output phases (h%2, w%2) in ONE launch (grid.z = phase); a phase without taps is written as act(bias)
-    taps, begin = [], [0]
-    for t in phases:
-        taps += t
-        begin.append(len(taps))
     offs = [((idx >> 1) * W + (idx & 1)) * Cin for idx in range(4)]
     _tap_gemm([dy], N, Ho, Wo, Cout, w, 1, taps, dx, H // 2, W // 2, 0, H * W * Cin, 2 * W * Cin, 2 * Cin, bias=bias, act=act, slope=slope,
               phase_begin=begin, phase_off=offs)
@@ -148,12 +170,13 @@ def _wgrad(dy, x, ph, wshape, stride, pad, out=None, scratch="scratch"):
         maps, Hx, Wx = [x], x.shape[1], x.shape[2]
     else:
         maps, Hx, Wx = [ph[i] for i in range(4)], ph.shape[2], ph.shape[3]
-    taps = fwd_taps(kh, kw, stride, pad)
+    taps = _fwd_taps_c(kh, kw, stride, pad)
+    a0, a1, a2, a3 = _tap_arrays(taps)
     dw = out if out is not None else torch.empty(wshape, device=dy.device, dtype=torch.float32)
     ws = _workspace(dy.device)
     _lib.check(_lib.lib().ddl_conv_wgrad(
         _lib.p(dy), int(N), int(Ho), int(Wo), int(Cout), _lib.host_ptrs([m.data_ptr() for m in maps]), len(maps), int(Hx), int(Wx),
-        int(Cin), _ints([t[0] for t in taps]), _ints([t[1] for t in taps]), _ints([t[2] for t in taps]), _ints([t[3] for t in taps]),
+        int(Cin), a0, a1, a2, a3,
         len(taps), _lib.p(dw), int(kh * kw), _lib.f32(1.0), _lib.f32(0.0), _lib.p(ws[scratch]), _lib.i64(ws[scratch].numel()),
         _lib.stream()), "ddl_conv_wgrad")
     return dw
