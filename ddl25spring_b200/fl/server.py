@@ -79,6 +79,7 @@ class Server(ABC):
         self.loss_fn = loss_fn                       # nll for log-prob models (MnistCnn), cross-entropy for logit models
         self.include_buffers = include_buffers
         self.graph = graph                           # replay each local SGD step from a CUDA graph (ModelSlot.sgd_step_graphed)
+        self._eval_graphs: dict = {}
         torch.manual_seed(seed)                      # global-model init is seeded (hfl_complete.py:165)
         self.slot = ModelSlot(model_fn, self.device, include_buffers=include_buffers)
         self.model = self.slot.model
@@ -112,8 +113,18 @@ class Server(ABC):
         self.model.eval()
         correct = torch.zeros((), dtype=torch.int32, device=self.device)
         for lo in range(0, len(ys), self.test_batch_size):
-            out = self.model(xs[lo:lo + self.test_batch_size])
-            ops.eval_top1(out.float().contiguous(), ys[lo:lo + self.test_batch_size], correct)
+            xb = xs[lo:lo + self.test_batch_size]
+            if self.graph and xb.is_cuda:
+                # inference forward replayed from a CUDA graph per batch shape (weights / BN statistics live in the static arena)
+                key = tuple(xb.shape)
+                g = self._eval_graphs.get(key)
+                if g is None:
+                    from ..utils.graphs import GraphedStep
+                    g = self._eval_graphs[key] = GraphedStep(lambda t: self.model(t).float().contiguous(), (xb,))
+                out = g(xb)
+            else:
+                out = self.model(xb).float().contiguous()
+            ops.eval_top1(out, ys[lo:lo + self.test_batch_size], correct)
         if world > 1:
             c64 = correct.to(torch.int64)
             dist.all_reduce(c64)
