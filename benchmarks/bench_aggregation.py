@@ -29,7 +29,6 @@ def timeit(fn, flusher, iters=5, warm=3):
 
 def main():
     from ddl25spring_b200 import ops
-    from ddl25spring_b200.ops import reference as ref
     from ddl25spring_b200.ops.gemm import gram_tcgen05
     from ddl25spring_b200.utils.timing import L2Flusher, max_over_ranks
     world = int(os.environ.get("WORLD_SIZE", "1"))

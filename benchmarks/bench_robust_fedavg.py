@@ -8,9 +8,8 @@ of ResNet-18 runs on the channels-last tcgen05 convolution stack (models/resnet_
 from a CUDA graph (--model aten --no-graph: the autograd/ATen/cuDNN path); the attack, the robust
 aggregation (incl. BN running statistics, `include_buffers=True`), the optimizer step and the evaluation count are this
 framework's kernels; across GPUs the aggregation is the fused peer-memory kernel."""
-import argparse, json, os, sys, time
+import argparse, json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np
 import torch
 import torch.distributed as dist
 import torch.nn.functional as F

@@ -25,10 +25,8 @@ from __future__ import annotations
 
 import ctypes as C
 
-import numpy as np
 import torch
 
-from ..models.mnist_cnn import MNIST_LAYOUT
 from ..ops import _lib
 from ..ops.gemm import gemm
 

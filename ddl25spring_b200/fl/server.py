@@ -36,7 +36,7 @@ from torch import nn
 
 from .. import ops
 from ..core.results import RunResult, message_count
-from ..core.seeds import client_round_seed, clients_per_round, epoch_permutations
+from ..core.seeds import client_round_seed, clients_per_round
 from ..models.mnist_cnn import MnistCnn
 from .aggregators import Aggregator, WeightedMean
 from .attacks import Attack

@@ -6,7 +6,6 @@ Both are splittable into two pipeline stages for the model-parallel config.
 """
 from __future__ import annotations
 
-import torch
 from torch import nn
 
 

@@ -24,7 +24,7 @@ import torch.distributed as dist
 import torch.nn.functional as F
 from torch import nn, optim
 
-from ..core.data import HEART_CATEGORICAL, HEART_RAW_COLUMNS, HeartTable
+from ..core.data import HEART_RAW_COLUMNS, HeartTable
 from ..models.tabular import BottomModel, TopModel, VFLVAE, combined_loss
 
 
