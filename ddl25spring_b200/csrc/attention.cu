@@ -1,10 +1,9 @@
 // K16: causal self-attention forward + backward for the labs' LLaMA shape (T = 256, head dim 48, 6 heads, B <= 3).
 //
 // q, k, v, o: [B*H, T, D] fp32.  The problem is tiny (18 heads x 256 x 256 scores), far below one tensor-core tile
-// per SM, so this is a CUDA-core flash-style kernel: FOUR LANES per query row (forward, dQ) or per key row (dK + dV in
-// one pass), each holding a quarter of the head dimension; K/V (resp. Q/dO) tiles are staged in shared memory and the
-// lanes of a warp read the same row -> broadcast, no bank conflicts; online softmax keeps the running max / sum in
-// registers; nothing of size T x T is stored.
+// per SM, so this is a CUDA-core flash-style kernel: SIXTEEN LANES per query row (forward, dQ) or per key row (dK + dV in
+// one pass) = 4 key-splits x 4 lanes holding a quarter of the head dimension each; K/V (resp. Q/dO) tiles are staged in
+// shared memory; online softmax keeps the running max / sum in registers; nothing of size T x T is stored.
 // Backward recomputes the probabilities from the saved log-sum-exp.
 // Replaces (reference): the attention inside simplellm's LLaMA blocks (lab/tutorial_1b/primer/intro.py:17,28).
 #include "common.cuh"
@@ -12,17 +11,24 @@
 
 namespace {
 
-// Work split: a QUERY (forward, dQ) or KEY (dK/dV) row is owned by 4 adjacent lanes, each holding D/4 of the head dimension;
-// dot products are finished with two xor-shuffles.  A CTA of 128 threads covers 32 rows, so the lab shape (18 heads x 256
-// tokens) launches 144 CTAs - one per SM - and a thread's serial work per key is D/4 FMAs instead of D.  (The first version
-// used one thread per row and 36 CTAs: 90 us per kernel; see DESIGN.md.)
+// Work split: a QUERY (forward, dQ) or KEY (dK/dV) row is owned by 16 adjacent lanes = 4 key-splits x 4 dim-lanes.  A dim-lane
+// holds D/4 of the head dimension (dot products are finished with two xor-shuffles inside the quad); the four splits walk
+// interleaved quarters of the other operand's rows and are merged at the end (online-softmax merge in the forward, plain sums
+// in the backward).  A CTA of 128 threads covers 8 rows, so the lab shape (18 heads x 256 tokens) launches 576 CTAs = 16 warps
+// per SM.  History: one thread per row, 36 CTAs: 90 us per kernel; 4 lanes per row, 144 CTAs = 4 warps per SM:
+// 72 us, still latency-bound on one warp per scheduler; this layout hides the FMA / shuffle / exp latencies behind 16 warps.
 constexpr int kThreads = 128;
-constexpr int kRows = kThreads / 4;   // rows (queries or keys) per CTA
+constexpr int kRows = kThreads / 16;  // rows (queries or keys) per CTA
 constexpr int kTile = 32;             // rows of the other operand staged in shared memory per step
 
 __device__ __forceinline__ float quad_sum(float v) {
   v += __shfl_xor_sync(0xffffffffu, v, 1);
   v += __shfl_xor_sync(0xffffffffu, v, 2);
+  return v;
+}
+__device__ __forceinline__ float split_sum(float v) {       // over the 4 key-splits of a row
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  v += __shfl_xor_sync(0xffffffffu, v, 8);
   return v;
 }
 
@@ -37,15 +43,28 @@ __device__ __forceinline__ void load_tile(float (*dst)[D], const float* __restri
   }
 }
 
+struct Lane {
+  int row, warp_first, warp_last, split, g;
+};
+__device__ __forceinline__ Lane lane_of() {
+  Lane l;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  l.g = lane & 3;
+  l.split = (lane >> 2) & 3;
+  l.warp_first = blockIdx.x * kRows + w * 2;
+  l.warp_last = l.warp_first + 1;
+  l.row = l.warp_first + (lane >> 4);
+  return l;
+}
+
 template <int D>
 __global__ void __launch_bounds__(kThreads) attn_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k,
                                                             const float* __restrict__ v, float* __restrict__ o, float* __restrict__ lse,
                                                             int T, float scale) {
   constexpr int D4 = D / 4;
   __shared__ __align__(16) float Ks[kTile][D], Vs[kTile][D];
-  const int bh = blockIdx.y, g = threadIdx.x & 3;
-  const int i = blockIdx.x * kRows + (threadIdx.x >> 2);
-  const int i_warp_last = blockIdx.x * kRows + ((threadIdx.x >> 5) << 3) + 7;       // last query handled by this warp
+  const Lane L = lane_of();
+  const int bh = blockIdx.y, i = L.row, g = L.g;
   const int64_t base = (int64_t)bh * T * D;
   float qr[D4], acc[D4];
 #pragma unroll
@@ -57,22 +76,38 @@ __global__ void __launch_bounds__(kThreads) attn_fwd_kernel(const float* __restr
     load_tile<D>(Ks, k + base, j0, T, 1.f);
     load_tile<D>(Vs, v + base, j0, T, 1.f);
     __syncthreads();
-    const int jn = min(kTile, min(i_warp_last, T - 1) - j0 + 1);   // uniform per warp (shuffles inside the loop)
-    for (int r = 0; r < jn; ++r) {
+    const int jn = min(kTile, min(L.warp_last, T - 1) - j0 + 1);   // uniform per warp (shuffles inside the loop)
+    for (int rr = 0; rr < jn; rr += 4) {
+      const int r = rr + L.split;                                  // <= 31
       float s = 0.f;
 #pragma unroll
       for (int d = 0; d < D4; ++d) s = fmaf(qr[d], Ks[r][g * D4 + d], s);
       s = quad_sum(s);
-      if (j0 + r > i) continue;                                 // masked for this query (all 4 lanes of the query agree)
-      const float mn = fmaxf(m, s);
-      const float corr = __expf(m - mn), p = __expf(s - mn);
-      l = l * corr + p;
+      if (r < jn && j0 + r <= i) {                                 // the quad of a (row, split) agrees
+        const float mn = fmaxf(m, s);
+        const float corr = __expf(m - mn), p = __expf(s - mn);
+        l = l * corr + p;
 #pragma unroll
-      for (int d = 0; d < D4; ++d) acc[d] = fmaf(acc[d], corr, p * Vs[r][g * D4 + d]);
-      m = mn;
+        for (int d = 0; d < D4; ++d) acc[d] = fmaf(acc[d], corr, p * Vs[r][g * D4 + d]);
+        m = mn;
+      }
     }
   }
-  if (i < T) {
+  // merge the four key-splits of each row (online-softmax merge); all lanes take part
+#pragma unroll
+  for (int off = 4; off <= 8; off <<= 1) {
+    const float mo = __shfl_xor_sync(0xffffffffu, m, off), lo = __shfl_xor_sync(0xffffffffu, l, off);
+    const float mn = fmaxf(m, mo);
+    const float ca = m == -INFINITY ? 0.f : __expf(m - mn), cb = mo == -INFINITY ? 0.f : __expf(mo - mn);
+    l = l * ca + lo * cb;
+#pragma unroll
+    for (int d = 0; d < D4; ++d) {
+      const float ao = __shfl_xor_sync(0xffffffffu, acc[d], off);
+      acc[d] = acc[d] * ca + ao * cb;
+    }
+    m = mn;
+  }
+  if (i < T && L.split == 0) {
     const float inv = 1.f / l;
 #pragma unroll
     for (int d = 0; d < D4; ++d) o[base + (int64_t)i * D + g * D4 + d] = acc[d] * inv;
@@ -80,7 +115,7 @@ __global__ void __launch_bounds__(kThreads) attn_fwd_kernel(const float* __restr
   }
 }
 
-// dQ: 4 lanes per query row.  delta_i = sum_d dO_i,d * O_i,d is computed here and stored for the dK/dV kernel.
+// dQ.  delta_i = sum_d dO_i,d * O_i,d is computed here and stored for the dK/dV kernel.
 template <int D>
 __global__ void __launch_bounds__(kThreads) attn_bwd_dq_kernel(const float* __restrict__ q, const float* __restrict__ k,
                                                                const float* __restrict__ v, const float* __restrict__ o,
@@ -88,9 +123,8 @@ __global__ void __launch_bounds__(kThreads) attn_bwd_dq_kernel(const float* __re
                                                                float* __restrict__ dq, float* __restrict__ delta, int T, float scale) {
   constexpr int D4 = D / 4;
   __shared__ __align__(16) float Ks[kTile][D], Vs[kTile][D];
-  const int bh = blockIdx.y, g = threadIdx.x & 3;
-  const int i = blockIdx.x * kRows + (threadIdx.x >> 2);
-  const int i_warp_last = blockIdx.x * kRows + ((threadIdx.x >> 5) << 3) + 7;
+  const Lane L = lane_of();
+  const int bh = blockIdx.y, i = L.row, g = L.g;
   const int64_t base = (int64_t)bh * T * D;
   float qr[D4], go[D4], acc[D4];
   float dl = 0.f;
@@ -104,33 +138,37 @@ __global__ void __launch_bounds__(kThreads) attn_bwd_dq_kernel(const float* __re
   }
   dl = quad_sum(dl);
   const float li = i < T ? lse[(int64_t)bh * T + i] : 0.f;
-  if (i < T && g == 0) delta[(int64_t)bh * T + i] = dl;
+  if (i < T && g == 0 && L.split == 0) delta[(int64_t)bh * T + i] = dl;
   const int last = min(T, (blockIdx.x + 1) * kRows);
   for (int j0 = 0; j0 < last; j0 += kTile) {
     __syncthreads();
     load_tile<D>(Ks, k + base, j0, T, 1.f);
     load_tile<D>(Vs, v + base, j0, T, 1.f);
     __syncthreads();
-    const int jn = min(kTile, min(i_warp_last, T - 1) - j0 + 1);
-    for (int r = 0; r < jn; ++r) {
+    const int jn = min(kTile, min(L.warp_last, T - 1) - j0 + 1);
+    for (int rr = 0; rr < jn; rr += 4) {
+      const int r = rr + L.split;
       float s = 0.f, dp = 0.f;
 #pragma unroll
       for (int d = 0; d < D4; ++d) { s = fmaf(qr[d], Ks[r][g * D4 + d], s); dp = fmaf(go[d], Vs[r][g * D4 + d], dp); }
       s = quad_sum(s);
       dp = quad_sum(dp);
-      if (j0 + r > i) continue;
-      const float ds = __expf(s - li) * (dp - dl) * scale;
+      if (r < jn && j0 + r <= i) {
+        const float ds = __expf(s - li) * (dp - dl) * scale;
 #pragma unroll
-      for (int d = 0; d < D4; ++d) acc[d] = fmaf(ds, Ks[r][g * D4 + d], acc[d]);
+        for (int d = 0; d < D4; ++d) acc[d] = fmaf(ds, Ks[r][g * D4 + d], acc[d]);
+      }
     }
   }
-  if (i < T) {
+#pragma unroll
+  for (int d = 0; d < D4; ++d) acc[d] = split_sum(acc[d]);
+  if (i < T && L.split == 0) {
 #pragma unroll
     for (int d = 0; d < D4; ++d) dq[base + (int64_t)i * D + g * D4 + d] = acc[d];
   }
 }
 
-// dK and dV in one pass: 4 lanes per key row, looping over the queries at or after it.
+// dK and dV in one pass: the lanes of a key row loop over the queries at or after it.
 template <int D>
 __global__ void __launch_bounds__(kThreads) attn_bwd_dkv_kernel(const float* __restrict__ q, const float* __restrict__ k,
                                                                 const float* __restrict__ v, const float* __restrict__ dO,
@@ -139,9 +177,8 @@ __global__ void __launch_bounds__(kThreads) attn_bwd_dkv_kernel(const float* __r
   constexpr int D4 = D / 4;
   __shared__ __align__(16) float Qs[kTile][D], Gs[kTile][D];
   __shared__ float Ls[kTile], Ds[kTile];
-  const int bh = blockIdx.y, g = threadIdx.x & 3;
-  const int j = blockIdx.x * kRows + (threadIdx.x >> 2);
-  const int j_warp_first = blockIdx.x * kRows + ((threadIdx.x >> 5) << 3);            // first key handled by this warp
+  const Lane L = lane_of();
+  const int bh = blockIdx.y, j = L.row, g = L.g;
   const int64_t base = (int64_t)bh * T * D;
   float kr[D4], vr[D4], acck[D4], accv[D4];
 #pragma unroll
@@ -162,23 +199,27 @@ __global__ void __launch_bounds__(kThreads) attn_bwd_dkv_kernel(const float* __r
       Ds[threadIdx.x] = ok ? delta[(int64_t)bh * T + i0 + threadIdx.x] : 0.f;
     }
     __syncthreads();
-    for (int r = max(0, j_warp_first - i0); r < kTile; ++r) {  // uniform per warp; only queries i >= j contribute
+    for (int rr = max(0, L.warp_first - i0); rr < kTile; rr += 4) {   // uniform per warp; only queries i >= j contribute
+      const int r = min(rr + L.split, kTile - 1);
       float s = 0.f, dp = 0.f;
 #pragma unroll
       for (int d = 0; d < D4; ++d) { s = fmaf(Qs[r][g * D4 + d], kr[d], s); dp = fmaf(Gs[r][g * D4 + d], vr[d], dp); }
       s = quad_sum(s);
       dp = quad_sum(dp);
-      if (i0 + r < j) continue;
-      const float p = __expf(s - Ls[r]);
-      const float ds = p * (dp - Ds[r]);                        // Qs already carries `scale`
+      if (rr + L.split < kTile && i0 + r >= j) {
+        const float p = __expf(s - Ls[r]);
+        const float ds = p * (dp - Ds[r]);                      // Qs already carries `scale`
 #pragma unroll
-      for (int d = 0; d < D4; ++d) {
-        accv[d] = fmaf(p, Gs[r][g * D4 + d], accv[d]);
-        acck[d] = fmaf(ds, Qs[r][g * D4 + d], acck[d]);
+        for (int d = 0; d < D4; ++d) {
+          accv[d] = fmaf(p, Gs[r][g * D4 + d], accv[d]);
+          acck[d] = fmaf(ds, Qs[r][g * D4 + d], acck[d]);
+        }
       }
     }
   }
-  if (j < T) {
+#pragma unroll
+  for (int d = 0; d < D4; ++d) { acck[d] = split_sum(acck[d]); accv[d] = split_sum(accv[d]); }
+  if (j < T && L.split == 0) {
 #pragma unroll
     for (int d = 0; d < D4; ++d) {
       dk[base + (int64_t)j * D + g * D4 + d] = acck[d];
