@@ -69,7 +69,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         bn = 32 if N <= 32 else (64 if N <= 64 else 128)
         ctas = -(-M // 128) * -(-N // bn) * G
         kb = -(-K // 32)
-        if 2 * ctas <= 148 and kb >= 8:
+        if 2 * ctas <= 148 and kb >= 16:
             n_split = max(1, min(kb // 4, 148 // ctas))
     L = _lib.lib()
     scratch = None
