@@ -43,6 +43,27 @@ __device__ __forceinline__ void load_tile(float (*dst)[D], const float* __restri
   }
 }
 
+// dot / axpy of a lane's D/4 slice against a shared-memory row, four floats per LDS.128
+template <int D4>
+__device__ __forceinline__ float dot_slice(const float (&a)[D4], const float* __restrict__ row) {
+  float s = 0.f;
+#pragma unroll
+  for (int c = 0; c < D4; c += 4) {
+    const float4 v = *reinterpret_cast<const float4*>(row + c);
+    s = fmaf(a[c], v.x, s); s = fmaf(a[c + 1], v.y, s); s = fmaf(a[c + 2], v.z, s); s = fmaf(a[c + 3], v.w, s);
+  }
+  return s;
+}
+template <int D4>
+__device__ __forceinline__ void axpy_slice(float (&acc)[D4], float p, const float* __restrict__ row) {
+#pragma unroll
+  for (int c = 0; c < D4; c += 4) {
+    const float4 v = *reinterpret_cast<const float4*>(row + c);
+    acc[c] = fmaf(p, v.x, acc[c]); acc[c + 1] = fmaf(p, v.y, acc[c + 1]);
+    acc[c + 2] = fmaf(p, v.z, acc[c + 2]); acc[c + 3] = fmaf(p, v.w, acc[c + 3]);
+  }
+}
+
 struct Lane {
   int row, warp_first, warp_last, split, g;
 };
@@ -79,16 +100,14 @@ __global__ void __launch_bounds__(kThreads) attn_fwd_kernel(const float* __restr
     const int jn = min(kTile, min(L.warp_last, T - 1) - j0 + 1);   // uniform per warp (shuffles inside the loop)
     for (int rr = 0; rr < jn; rr += 4) {
       const int r = rr + L.split;                                  // <= 31
-      float s = 0.f;
-#pragma unroll
-      for (int d = 0; d < D4; ++d) s = fmaf(qr[d], Ks[r][g * D4 + d], s);
-      s = quad_sum(s);
+      const float s = quad_sum(dot_slice<D4>(qr, &Ks[r][g * D4]));
       if (r < jn && j0 + r <= i) {                                 // the quad of a (row, split) agrees
         const float mn = fmaxf(m, s);
         const float corr = __expf(m - mn), p = __expf(s - mn);
         l = l * corr + p;
 #pragma unroll
-        for (int d = 0; d < D4; ++d) acc[d] = fmaf(acc[d], corr, p * Vs[r][g * D4 + d]);
+        for (int d = 0; d < D4; ++d) acc[d] *= corr;
+        axpy_slice<D4>(acc, p, &Vs[r][g * D4]);
         m = mn;
       }
     }
@@ -148,15 +167,11 @@ __global__ void __launch_bounds__(kThreads) attn_bwd_dq_kernel(const float* __re
     const int jn = min(kTile, min(L.warp_last, T - 1) - j0 + 1);
     for (int rr = 0; rr < jn; rr += 4) {
       const int r = rr + L.split;
-      float s = 0.f, dp = 0.f;
-#pragma unroll
-      for (int d = 0; d < D4; ++d) { s = fmaf(qr[d], Ks[r][g * D4 + d], s); dp = fmaf(go[d], Vs[r][g * D4 + d], dp); }
-      s = quad_sum(s);
-      dp = quad_sum(dp);
+      const float s = quad_sum(dot_slice<D4>(qr, &Ks[r][g * D4]));
+      const float dp = quad_sum(dot_slice<D4>(go, &Vs[r][g * D4]));
       if (r < jn && j0 + r <= i) {
         const float ds = __expf(s - li) * (dp - dl) * scale;
-#pragma unroll
-        for (int d = 0; d < D4; ++d) acc[d] = fmaf(ds, Ks[r][g * D4 + d], acc[d]);
+        axpy_slice<D4>(acc, ds, &Ks[r][g * D4]);
       }
     }
   }
@@ -201,19 +216,13 @@ __global__ void __launch_bounds__(kThreads) attn_bwd_dkv_kernel(const float* __r
     __syncthreads();
     for (int rr = max(0, L.warp_first - i0); rr < kTile; rr += 4) {   // uniform per warp; only queries i >= j contribute
       const int r = min(rr + L.split, kTile - 1);
-      float s = 0.f, dp = 0.f;
-#pragma unroll
-      for (int d = 0; d < D4; ++d) { s = fmaf(Qs[r][g * D4 + d], kr[d], s); dp = fmaf(Gs[r][g * D4 + d], vr[d], dp); }
-      s = quad_sum(s);
-      dp = quad_sum(dp);
+      const float s = quad_sum(dot_slice<D4>(kr, &Qs[r][g * D4]));
+      const float dp = quad_sum(dot_slice<D4>(vr, &Gs[r][g * D4]));
       if (rr + L.split < kTile && i0 + r >= j) {
         const float p = __expf(s - Ls[r]);
         const float ds = p * (dp - Ds[r]);                      // Qs already carries `scale`
-#pragma unroll
-        for (int d = 0; d < D4; ++d) {
-          accv[d] = fmaf(p, Gs[r][g * D4 + d], accv[d]);
-          acck[d] = fmaf(ds, Qs[r][g * D4 + d], acck[d]);
-        }
+        axpy_slice<D4>(accv, p, &Gs[r][g * D4]);
+        axpy_slice<D4>(acck, ds, &Qs[r][g * D4]);
       }
     }
   }
