@@ -35,3 +35,11 @@ def test_dp_and_pp_launch_scripts():
                         "--dmodel", "48", "--vocab", "128"], cwd=ROOT, capture_output=True, text=True, timeout=200, env=env)
     assert r.returncode == 0, r.stderr[-2000:]
     assert "elapsed" in r.stdout
+
+
+def test_robust_resnet_fl_example_runs_on_cpu():
+    sys.path.insert(0, os.path.join(ROOT, "examples"))
+    import robust_resnet_fl
+    res = robust_resnet_fl.main(["--aggregator", "median", "--rounds", "1", "--clients", "3", "--samples", "16", "--batch", "8",
+                                 "--malicious_fraction", "0.34"])
+    assert len(res.test_accuracy) == 1 and res.test_accuracy[0] == res.test_accuracy[0]
