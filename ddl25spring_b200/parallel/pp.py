@@ -96,6 +96,80 @@ def check_schedule(name: str, n_stages: int, n_micro: int) -> int:
     return steps
 
 
+def p2p_program(name: str, n_stages: int, stage: int, n_micro: int) -> list[tuple]:
+    """The communication / compute actions :meth:`PipelineStage.run` issues, in host order, as data:
+    ``("recv", dir, mb)``, ``("compute", kind, mb)``, ``("send", dir, mb)`` with ``dir`` "fwd" (activations) or "bwd"
+    (gradients).  Receives are pre-posted one op ahead exactly like the executor does."""
+    ops = SCHEDULES[name](n_stages, stage, n_micro)
+    first, last = stage == 0, stage == n_stages - 1
+    prog, posted = [], set()
+
+    def post(op: Op):
+        if op.kind == F and not first and ("fwd", op.mb) not in posted:
+            posted.add(("fwd", op.mb)); prog.append(("recv", "fwd", op.mb))
+        if op.kind == B and not last and ("bwd", op.mb) not in posted:
+            posted.add(("bwd", op.mb)); prog.append(("recv", "bwd", op.mb))
+
+    if ops:
+        post(ops[0])
+    for i, op in enumerate(ops):
+        if i + 1 < len(ops):
+            post(ops[i + 1])
+        prog.append(("compute", op.kind, op.mb))
+        if op.kind == F and not last:
+            prog.append(("send", "fwd", op.mb))
+        if op.kind == B and not first:
+            prog.append(("send", "bwd", op.mb))
+    return prog
+
+
+def check_stream_ordered_p2p(name: str, n_stages: int, n_micro: int, per_direction: bool = True) -> int:
+    """Simulate the executor under NCCL semantics: the host never blocks, every p2p operation of a rank is queued in issue
+    order on ONE stream per communicator, and a transfer happens only when the send and the matching receive are both at
+    the head of their queues (rendezvous) and the send's payload has been computed.  ``per_direction=False`` puts
+    activations and gradients on the same communicator - the configuration that hung on the GPUs; ``True`` is what
+    :class:`Mesh` sets up.  Returns the number of simulation steps, raises ``RuntimeError`` on deadlock."""
+    from collections import deque
+    progs = [p2p_program(name, n_stages, s, n_micro) for s in range(n_stages)]
+    comm = (lambda d: d) if per_direction else (lambda d: "all")
+    queues = [dict() for _ in range(n_stages)]                 # stage -> communicator -> deque of (type, dir, mb)
+    computes = [deque() for _ in range(n_stages)]
+    for s, prog in enumerate(progs):
+        for act in prog:
+            if act[0] == "compute":
+                computes[s].append(act)
+            else:
+                queues[s].setdefault(comm(act[1]), deque()).append(act)
+    received = [set() for _ in range(n_stages)]                # (dir, mb) that arrived at stage s
+    computed = [set() for _ in range(n_stages)]                # (kind, mb) finished at stage s
+    steps = 0
+    while any(computes[s] or any(q for q in queues[s].values()) for s in range(n_stages)):
+        progressed = False
+        for s in range(n_stages):                              # compute stream: in order, gated by its input message
+            if computes[s]:
+                _, kind, mb = computes[s][0]
+                need = ("fwd", mb) if kind == F else ("bwd", mb)
+                has_input = (kind == F and s == 0) or (kind == B and s == n_stages - 1) or need in received[s]
+                if has_input and (kind == F or (F, mb) in computed[s]):
+                    computed[s].add((kind, mb)); computes[s].popleft(); progressed = True
+        for s in range(n_stages):                              # transfers: both heads must match
+            for c, q in queues[s].items():
+                if not q or q[0][0] != "send":
+                    continue
+                _, d, mb = q[0]
+                if ((F if d == "fwd" else B), mb) not in computed[s]:
+                    continue
+                peer = s + 1 if d == "fwd" else s - 1
+                pq = queues[peer].get(c)
+                if pq and pq[0] == ("recv", d, mb):
+                    q.popleft(); pq.popleft(); received[peer].add((d, mb)); progressed = True
+        steps += 1
+        if not progressed:
+            heads = [{c: (q[0] if q else None) for c, q in queues[s].items()} for s in range(n_stages)]
+            raise RuntimeError(f"stream-ordered p2p deadlock: {name!r}, {n_stages} stages, {n_micro} micro-batches, queue heads {heads}")
+    return steps
+
+
 # ------------------------------------------------------------------------------------------ mesh
 class Mesh:
     """``n_pipelines`` x ``n_stages`` process mesh with one DP group per stage."""

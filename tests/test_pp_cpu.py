@@ -128,3 +128,15 @@ def test_two_stage_model_parallel_split(which):
     outs = run_distributed(_two_stage_worker, 2, (which,), timeout=150)
     for err, n in outs:
         assert n > 0 and err < 1e-4, (err, n)
+
+
+@pytest.mark.parametrize("name", ["gpipe", "1f1b"])
+@pytest.mark.parametrize("stages", [2, 3, 4, 5])
+@pytest.mark.parametrize("micro", [1, 2, 3, 4, 8])
+def test_executor_p2p_order_is_deadlock_free_under_nccl_stream_semantics(name, stages, micro):
+    """NCCL runs a rank's p2p operations in issue order on one stream per communicator (rendezvous, no tags).  With activations
+    and gradients on one communicator the executor's pre-posted receives hang (observed on 2 B200s); with one communicator per
+    direction - what Mesh creates under NCCL - every schedule completes."""
+    assert pp.check_stream_ordered_p2p(name, stages, micro, per_direction=True) > 0
+    with pytest.raises(RuntimeError, match="deadlock"):
+        pp.check_stream_ordered_p2p(name, stages, micro, per_direction=False)
