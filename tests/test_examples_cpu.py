@@ -43,3 +43,41 @@ def test_robust_resnet_fl_example_runs_on_cpu():
     res = robust_resnet_fl.main(["--aggregator", "median", "--rounds", "1", "--clients", "3", "--samples", "16", "--batch", "8",
                                  "--malicious_fraction", "0.34"])
     assert len(res.test_accuracy) == 1 and res.test_accuracy[0] == res.test_accuracy[0]
+
+
+@pytest.mark.parametrize("name", ["horizontal_federated_learning", "vertical_federated_learning"])
+def test_tutorial_notebooks_execute(name):
+    """The tutorial notebooks (counterparts of the reference's lab notebooks) are stored clean and their code cells run."""
+    import json
+    path = os.path.join(ROOT, "notebooks", name + ".ipynb")
+    nb = json.load(open(path))
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import clear_notebook_metadata as cnm
+    assert cnm.main([os.path.join(ROOT, "notebooks"), "--check"]) == 0
+    env = {"__name__": "__notebook__"}
+    cwd = os.getcwd()
+    os.chdir(os.path.join(ROOT, "notebooks"))
+    try:
+        for cell in nb["cells"]:
+            if cell["cell_type"] == "code":
+                src = "".join(cell["source"])
+                src = src.replace("n_train=6000, n_test=1000", "n_train=600, n_test=100").replace("EPOCHS = 30", "EPOCHS = 2")
+                src = src.replace("epochs=100", "epochs=5")
+                exec(compile(src, path, "exec"), env)
+    finally:
+        os.chdir(cwd)
+
+
+def test_notebook_cleaner_strips_outputs(tmp_path):
+    import json
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import clear_notebook_metadata as cnm
+    nb = {"cells": [{"cell_type": "code", "metadata": {"collapsed": True}, "source": ["1+1"], "outputs": [{"output_type": "stream"}],
+                     "execution_count": 7}], "metadata": {"kernelspec": {"name": "python3"}, "widgets": {}}, "nbformat": 4, "nbformat_minor": 5}
+    p = tmp_path / "a.ipynb"
+    p.write_text(json.dumps(nb))
+    assert cnm.main([str(tmp_path), "--check"]) == 1
+    assert cnm.main([str(tmp_path)]) == 0
+    out = json.loads(p.read_text())
+    assert out["cells"][0]["outputs"] == [] and out["cells"][0]["execution_count"] is None and "widgets" not in out["metadata"]
+    assert cnm.main([str(tmp_path), "--check"]) == 0
