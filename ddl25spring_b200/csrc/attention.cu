@@ -82,6 +82,8 @@ template <int D>
 __global__ void __launch_bounds__(kThreads) attn_fwd_kernel(const float* __restrict__ q, const float* __restrict__ k,
                                                             const float* __restrict__ v, float* __restrict__ o, float* __restrict__ lse,
                                                             int T, float scale) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int D4 = D / 4;
   __shared__ __align__(16) float Ks[kTile][D], Vs[kTile][D];
   const Lane L = lane_of();
@@ -140,6 +142,8 @@ __global__ void __launch_bounds__(kThreads) attn_bwd_dq_kernel(const float* __re
                                                                const float* __restrict__ v, const float* __restrict__ o,
                                                                const float* __restrict__ dO, const float* __restrict__ lse,
                                                                float* __restrict__ dq, float* __restrict__ delta, int T, float scale) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int D4 = D / 4;
   __shared__ __align__(16) float Ks[kTile][D], Vs[kTile][D];
   const Lane L = lane_of();
@@ -189,6 +193,8 @@ __global__ void __launch_bounds__(kThreads) attn_bwd_dkv_kernel(const float* __r
                                                                 const float* __restrict__ v, const float* __restrict__ dO,
                                                                 const float* __restrict__ lse, const float* __restrict__ delta,
                                                                 float* __restrict__ dk, float* __restrict__ dv, int T, float scale) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int D4 = D / 4;
   __shared__ __align__(16) float Qs[kTile][D], Gs[kTile][D];
   __shared__ float Ls[kTile], Ds[kTile];
@@ -240,7 +246,7 @@ __global__ void __launch_bounds__(kThreads) attn_bwd_dkv_kernel(const float* __r
 template <int D>
 int launch_fwd(const float* q, const float* k, const float* v, float* o, float* lse, int BH, int T, float scale, cudaStream_t st) {
   dim3 grid((T + kRows - 1) / kRows, BH);
-  attn_fwd_kernel<D><<<grid, kThreads, 0, st>>>(q, k, v, o, lse, T, scale);
+  DDL_CUDA_CHECK(ddl_launch_pdl(attn_fwd_kernel<D>, dim3(grid), dim3(kThreads), 0, st, q, k, v, o, lse, T, scale));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -249,9 +255,9 @@ template <int D>
 int launch_bwd(const float* q, const float* k, const float* v, const float* o, const float* dO, const float* lse, float* dq, float* dk,
                float* dv, float* delta, int BH, int T, float scale, cudaStream_t st) {
   dim3 grid((T + kRows - 1) / kRows, BH);
-  attn_bwd_dq_kernel<D><<<grid, kThreads, 0, st>>>(q, k, v, o, dO, lse, dq, delta, T, scale);
+  DDL_CUDA_CHECK(ddl_launch_pdl(attn_bwd_dq_kernel<D>, dim3(grid), dim3(kThreads), 0, st, q, k, v, o, dO, lse, dq, delta, T, scale));
   DDL_LAUNCH_CHECK();
-  attn_bwd_dkv_kernel<D><<<grid, kThreads, 0, st>>>(q, k, v, dO, lse, delta, dk, dv, T, scale);
+  DDL_CUDA_CHECK(ddl_launch_pdl(attn_bwd_dkv_kernel<D>, dim3(grid), dim3(kThreads), 0, st, q, k, v, dO, lse, delta, dk, dv, T, scale));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

@@ -17,6 +17,8 @@ __global__ void __launch_bounds__(256) softmax_xent_kernel(const float* __restri
                                                            float* __restrict__ loss_sum, float* __restrict__ n_valid,
                                                            int64_t N, int C, float loss_scale, float grad_scale,
                                                            int64_t ignore_index) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -63,6 +65,8 @@ __global__ void __launch_bounds__(256) softmax_xent_kernel(const float* __restri
 __global__ void __launch_bounds__(256) eval_top1_kernel(const float* __restrict__ logits, int64_t ld,
                                                         const int64_t* __restrict__ target, int64_t N, int C,
                                                         int* __restrict__ correct) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -93,6 +97,8 @@ __global__ void __launch_bounds__(256) vae_loss_kernel(const float* __restrict__
                                                        float* __restrict__ loss, float* __restrict__ g_xr,
                                                        float* __restrict__ g_mu, float* __restrict__ g_lv,
                                                        float gscale) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float red[32];
   float acc = 0.f;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -128,9 +134,9 @@ int ddl_softmax_xent(const float* logits, int64_t ld, const int64_t* target_idx,
   DDL_REQUIRE((target_idx != nullptr) != (target_prob != nullptr), "pass exactly one of target_idx / target_prob");
   DDL_REQUIRE(loss_sum != nullptr, "loss_sum must be a device float (pre-zeroed by the caller)");
   if (N == 0) return DDL_OK;
-  softmax_xent_kernel<<<warp_grid(N), 256, 0, (cudaStream_t)stream>>>(logits, ld, target_idx, target_stride, target_prob,
+  DDL_CUDA_CHECK(ddl_launch_pdl(softmax_xent_kernel, dim3(warp_grid(N)), dim3(256), 0, (cudaStream_t)stream, logits, ld, target_idx, target_stride, target_prob,
                                                                        grad, loss_sum, n_valid, N, C, loss_scale,
-                                                                       grad_scale, ignore_index);
+                                                                       grad_scale, ignore_index));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -138,7 +144,7 @@ int ddl_softmax_xent(const float* logits, int64_t ld, const int64_t* target_idx,
 int ddl_eval_top1(const float* logits, int64_t ld, const int64_t* target, int64_t N, int C, int* correct,
                   void* stream) {
   if (N == 0) return DDL_OK;
-  eval_top1_kernel<<<warp_grid(N), 256, 0, (cudaStream_t)stream>>>(logits, ld, target, N, C, correct);
+  DDL_CUDA_CHECK(ddl_launch_pdl(eval_top1_kernel, dim3(warp_grid(N)), dim3(256), 0, (cudaStream_t)stream, logits, ld, target, N, C, correct));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -150,8 +156,8 @@ int ddl_vae_loss(const float* x_recon, const float* x, int64_t nx, const float* 
   int64_t g = (n + 255) / 256;
   if (g > kNumSMs * 4) g = kNumSMs * 4;
   if (g < 1) g = 1;
-  vae_loss_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(x_recon, x, nx, mu, logvar, nz, loss, grad_x_recon, grad_mu,
-                                                            grad_logvar, grad_scale);
+  DDL_CUDA_CHECK(ddl_launch_pdl(vae_loss_kernel, dim3((int)g), dim3(256), 0, (cudaStream_t)stream, x_recon, x, nx, mu, logvar, nz, loss, grad_x_recon, grad_mu,
+                                                            grad_logvar, grad_scale));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

@@ -10,6 +10,8 @@ namespace {
 __global__ void __launch_bounds__(256) rmsnorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                           float* __restrict__ y, float* __restrict__ rstd, int64_t rows, int d,
                                                           float eps) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (row >= rows) return;
@@ -26,6 +28,8 @@ __global__ void __launch_bounds__(256) rmsnorm_fwd_kernel(const float* __restric
 __global__ void __launch_bounds__(256) rmsnorm_bwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                           const float* __restrict__ dy, const float* __restrict__ rstd,
                                                           float* __restrict__ dx, float* __restrict__ dw, int64_t rows, int d) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (row >= rows) return;
@@ -50,7 +54,7 @@ extern "C" {
 int ddl_rmsnorm_fwd(const float* x, const float* w, float* y, float* rstd, int64_t rows, int d, float eps, void* stream) {
   if (rows == 0) return DDL_OK;
   const int64_t blocks = (rows + 7) / 8;
-  rmsnorm_fwd_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(x, w, y, rstd, rows, d, eps);
+  DDL_CUDA_CHECK(ddl_launch_pdl(rmsnorm_fwd_kernel, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream, x, w, y, rstd, rows, d, eps));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -59,7 +63,7 @@ int ddl_rmsnorm_bwd(const float* x, const float* w, const float* dy, const float
                     void* stream) {
   if (rows == 0) return DDL_OK;
   const int64_t blocks = (rows + 7) / 8;
-  rmsnorm_bwd_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(x, w, dy, rstd, dx, dw, rows, d);
+  DDL_CUDA_CHECK(ddl_launch_pdl(rmsnorm_bwd_kernel, dim3((unsigned)blocks), dim3(256), 0, (cudaStream_t)stream, x, w, dy, rstd, dx, dw, rows, d));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

@@ -10,6 +10,8 @@ namespace {
 __global__ void __launch_bounds__(256) sgd_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                   float* __restrict__ buf, float lr, float wd, float mom,
                                                   float gscale, int64_t nvec) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += stride) {
     float4 w = reinterpret_cast<float4*>(p)[v];
@@ -45,6 +47,8 @@ __device__ __forceinline__ void adam1(float& w, float g, float& m, float& v, con
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                    float* __restrict__ m, float* __restrict__ v, AdamArgs a,
                                                    int64_t nvec) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
     float4 w = reinterpret_cast<float4*>(p)[i];
@@ -63,6 +67,8 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
 __global__ void __launch_bounds__(256) adam_devstep_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                                            float* __restrict__ v, AdamArgs a, const int* __restrict__ step_ptr,
                                                            int64_t nvec) {
+  pdl_launch_dependents();
+  pdl_wait();
   const float step = (float)max(1, *step_ptr);
   a.bc1 = 1.f - powf(a.b1, step);
   a.bc2_rsqrt = 1.f / sqrtf(1.f - powf(a.b2, step));
@@ -94,8 +100,8 @@ int ddl_sgd_step(float* params, const float* grads, float* momentum_buf, int64_t
                  float momentum, float grad_scale, void* stream) {
   DDL_REQUIRE(n % 4 == 0, "n must be a multiple of 4 floats (arenas are padded)");
   if (n == 0) return DDL_OK;
-  sgd_kernel<<<grid_for(n / 4), 256, 0, (cudaStream_t)stream>>>(params, grads, momentum != 0.f ? momentum_buf : nullptr,
-                                                                 lr, weight_decay, momentum, grad_scale, n / 4);
+  DDL_CUDA_CHECK(ddl_launch_pdl(sgd_kernel, dim3(grid_for(n / 4)), dim3(256), 0, (cudaStream_t)stream, params, grads, momentum != 0.f ? momentum_buf : nullptr,
+                                                                 lr, weight_decay, momentum, grad_scale, n / 4));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -111,7 +117,7 @@ int ddl_adam_step(float* params, const float* grads, float* exp_avg, float* exp_
   a.gscale = grad_scale;
   a.bc1 = 1.f - powf(beta1, (float)step);
   a.bc2_rsqrt = 1.f / sqrtf(1.f - powf(beta2, (float)step));
-  adam_kernel<<<grid_for(n / 4), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, a, n / 4);
+  DDL_CUDA_CHECK(ddl_launch_pdl(adam_kernel, dim3(grid_for(n / 4)), dim3(256), 0, (cudaStream_t)stream, params, grads, exp_avg, exp_avg_sq, a, n / 4));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -126,7 +132,7 @@ int ddl_adam_step_dev(float* params, const float* grads, float* exp_avg, float* 
   a.lr = lr; a.b1 = beta1; a.b2 = beta2; a.eps = eps; a.wd = weight_decay; a.decoupled = decoupled;
   a.gscale = grad_scale;
   a.bc1 = 1.f; a.bc2_rsqrt = 1.f;
-  adam_devstep_kernel<<<grid_for(n / 4), 256, 0, (cudaStream_t)stream>>>(params, grads, exp_avg, exp_avg_sq, a, step_dev, n / 4);
+  DDL_CUDA_CHECK(ddl_launch_pdl(adam_devstep_kernel, dim3(grid_for(n / 4)), dim3(256), 0, (cudaStream_t)stream, params, grads, exp_avg, exp_avg_sq, a, step_dev, n / 4));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
