@@ -338,3 +338,27 @@ def test_nhwc_models_split_into_two_pipeline_stages():
     img = G(z)
     assert torch.allclose(d1(d0(img)), D(img), atol=1e-6)
     assert sum(p.numel() for s in (g0, g1) for p in s.parameters()) == sum(p.numel() for p in G.parameters())
+
+
+def test_tap_algebra_property_random_geometries():
+    """Hypothesis sweep: for random kernel sizes / strides / paddings / (even) image sizes the tap lists reproduce conv2d and
+    its input gradient exactly (fp64)."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=40, deadline=None)
+    @given(kh=st.integers(1, 4), kw=st.integers(1, 4), stride=st.sampled_from([1, 2]), pad=st.integers(0, 2),
+           H=st.sampled_from([4, 6, 8, 10]), W=st.sampled_from([4, 6, 8]), seed=st.integers(0, 10_000))
+    def check(kh, kw, stride, pad, H, W, seed):
+        if H + 2 * pad < kh or W + 2 * pad < kw:
+            return
+        g = torch.Generator().manual_seed(seed)
+        x = torch.randn(2, H, W, 3, dtype=torch.float64, generator=g).requires_grad_()
+        w = torch.randn(5, kh, kw, 3, dtype=torch.float64, generator=g)
+        y_ref = F.conv2d(x.permute(0, 3, 1, 2), w.permute(0, 3, 1, 2), None, stride, pad).permute(0, 2, 3, 1)
+        y = K.tap_conv_reference(x.detach(), w, stride, pad)
+        assert y.shape == y_ref.shape and torch.allclose(y, y_ref.detach(), atol=1e-10)
+        gy = torch.randn(y_ref.shape, dtype=torch.float64, generator=g)
+        (gx_ref,) = torch.autograd.grad(y_ref, x, gy)
+        assert torch.allclose(K.tap_dgrad_reference(gy, w, stride, pad, H, W), gx_ref, atol=1e-10)
+
+    check()
