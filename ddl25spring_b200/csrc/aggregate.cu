@@ -12,6 +12,7 @@
 // lab/tutorial_1a/hfl_complete.py:291-306 (FedSGD) and :370-383 (FedAvg).
 #include "common.cuh"
 #include "ddl25_kernels.h"
+#include "select.cuh"
 
 namespace {
 
@@ -45,24 +46,29 @@ __global__ void __launch_bounds__(256) weighted_sum_kernel(RowTable tab, int K, 
   for (int64_t v = v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < v1; v += stride) {
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     int k = 0;
+    // rows with weight 0 are neither loaded nor accumulated: Krum's selection weights are mostly zero (only the chosen
+    // rows cross HBM / NVLink), and a rejected row may hold NaN / Inf, which 0 * x would turn into NaN
     for (; k + UNROLL <= K; k += UNROLL) {
       float4 x[UNROLL];
+      float w[UNROLL];
 #pragma unroll
       for (int u = 0; u < UNROLL; ++u) {
+        w[u] = dev_w ? __ldg(dev_w + k + u) : tab.w[k + u];
         const float4* p = reinterpret_cast<const float4*>(tab.rows[k + u]) + v;
-        x[u] = peer_rows ? ddl::ld_coherent(p) : ddl::ld_stream(p);
+        x[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (w[u] != 0.f) x[u] = peer_rows ? ddl::ld_coherent(p) : ddl::ld_stream(p);
       }
 #pragma unroll
       for (int u = 0; u < UNROLL; ++u) {
-        const float w = dev_w ? __ldg(dev_w + k + u) : tab.w[k + u];
-        acc.x = fmaf(w, x[u].x, acc.x); acc.y = fmaf(w, x[u].y, acc.y);
-        acc.z = fmaf(w, x[u].z, acc.z); acc.w = fmaf(w, x[u].w, acc.w);
+        acc.x = fmaf(w[u], x[u].x, acc.x); acc.y = fmaf(w[u], x[u].y, acc.y);
+        acc.z = fmaf(w[u], x[u].z, acc.z); acc.w = fmaf(w[u], x[u].w, acc.w);
       }
     }
     for (; k < K; ++k) {
+      const float w = dev_w ? __ldg(dev_w + k) : tab.w[k];
+      if (w == 0.f) continue;
       const float4* p = reinterpret_cast<const float4*>(tab.rows[k]) + v;
       const float4 x = peer_rows ? ddl::ld_coherent(p) : ddl::ld_stream(p);
-      const float w = dev_w ? __ldg(dev_w + k) : tab.w[k];
       acc.x = fmaf(w, x.x, acc.x); acc.y = fmaf(w, x.y, acc.y);
       acc.z = fmaf(w, x.z, acc.z); acc.w = fmaf(w, x.w, acc.w);
     }
@@ -79,45 +85,23 @@ __global__ void __launch_bounds__(256) weighted_sum_kernel(RowTable tab, int K, 
 // ------------------------------------------------------------------------------------------
 // K4 / K5: coordinate-wise median and trimmed mean.
 // One thread per coordinate: the K values of that coordinate are loaded (one coalesced 128 B
-// line per warp per row), sorted with a fully unrolled bitonic network held in registers
-// (KP = K padded to a power of two with +inf), then reduced over ranks [lo, hi).
+// line per warp per row) into registers and run through a straight-line Batcher odd-even merge
+// network (select.cuh; KP = K padded to a power of two), then reduced over ranks [lo, hi).  A
+// window that is exactly the median takes the network pruned to the two centre ranks.
 //   median (odd K)  : lo = hi-1 = (K-1)/2
 //   median (even K) : lo = K/2-1, hi = K/2+1 (mean of the middle pair) or lower median
 //   trimmed mean    : lo = trim, hi = K - trim
 // ------------------------------------------------------------------------------------------
-template <int KP>
-__device__ __forceinline__ void bitonic_sort_regs(float (&a)[KP]) {
-#pragma unroll
-  for (int k = 2; k <= KP; k <<= 1) {
-#pragma unroll
-    for (int j = k >> 1; j > 0; j >>= 1) {
-#pragma unroll
-      for (int i = 0; i < KP; ++i) {
-        const int l = i ^ j;
-        if (l > i) {
-          const bool up = ((i & k) == 0);
-          const float lo = fminf(a[i], a[l]), hi = fmaxf(a[i], a[l]);
-          a[i] = up ? lo : hi;
-          a[l] = up ? hi : lo;
-        }
-      }
-    }
-  }
-}
-
-template <int KP>
+template <int KP, bool MEDIAN>
 __global__ void __launch_bounds__(128) rank_select_mean_kernel(RowTable tab, int K, int lo, int hi, OutTable ot,
                                                                int n_out, int64_t d0, int64_t d1) {
   const int64_t d = d0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (d >= d1) return;
   float a[KP];
 #pragma unroll
-  for (int k = 0; k < KP; ++k) a[k] = (k < K) ? __ldcg(tab.rows[k] + d) : __int_as_float(0x7f800000);
-  bitonic_sort_regs<KP>(a);
-  float s = 0.f;
-#pragma unroll
-  for (int k = 0; k < KP; ++k) s += (k >= lo && k < hi) ? a[k] : 0.f;
-  const float r = s / (float)(hi - lo);
+  for (int k = 0; k < KP; ++k)
+    a[k] = (k < K) ? __ldcg(tab.rows[k] + d) : (MEDIAN ? ddl::median_pad(k, K, KP) : __int_as_float(0x7f800000));
+  const float r = MEDIAN ? ddl::median_of<KP>(a, hi - lo == 2) : ddl::window_mean<KP>(a, lo, hi);
   for (int o = 0; o < n_out; ++o) ot.outs[o][d] = r;
 }
 
@@ -171,7 +155,10 @@ __global__ void __launch_bounds__(128) krum_select_kernel(const float* __restric
     int nb = 0;
     for (int j = 0; j < K; ++j) {
       if (j == i) continue;
-      float dj = fmaxf(s_diag[i] + s_diag[j] - 2.f * G[(int64_t)i * ldg + j], 0.f);
+      // a non-finite distance (NaN / Inf rows, or a Gram entry that overflowed fp32) must count as "infinitely far":
+      // fmaxf alone would turn NaN into 0 and make the poisoned row the best candidate
+      float dj = s_diag[i] + s_diag[j] - 2.f * G[(int64_t)i * ldg + j];
+      dj = (dj == dj && fabsf(dj) <= 3.0e38f) ? fmaxf(dj, 0.f) : __int_as_float(0x7f800000);
       int p = nb < m ? nb++ : m;   // position one past the kept range when full
       if (p == m) {
         if (dj >= best[m - 1]) continue;
@@ -182,6 +169,7 @@ __global__ void __launch_bounds__(128) krum_select_kernel(const float* __restric
     }
     sc = 0.f;
     for (int j = 0; j < nb; ++j) sc += best[j];
+    if (!(s_diag[i] == s_diag[i]) || fabsf(s_diag[i]) > 3.0e38f) sc = __int_as_float(0x7f800000);   // a non-finite row is never selected
     scores[i] = sc;
   }
   s_score[i] = sc;
@@ -209,7 +197,9 @@ int launch_rank_select(const RowTable& tab, int K, int lo, int hi, const OutTabl
   const int64_t n = d1 - d0;
   const int block = 128;
   const int64_t grid = (n + block - 1) / block;
-  rank_select_mean_kernel<KP><<<(unsigned)grid, block, 0, st>>>(tab, K, lo, hi, ot, n_out, d0, d1);
+  const bool med = (lo == (K - 1) / 2 && hi == lo + 1) || (K % 2 == 0 && lo == K / 2 - 1 && hi == K / 2 + 1);
+  if (med) rank_select_mean_kernel<KP, true><<<(unsigned)grid, block, 0, st>>>(tab, K, lo, hi, ot, n_out, d0, d1);
+  else rank_select_mean_kernel<KP, false><<<(unsigned)grid, block, 0, st>>>(tab, K, lo, hi, ot, n_out, d0, d1);
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

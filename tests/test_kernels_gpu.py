@@ -158,3 +158,24 @@ def test_krum_select_from_exact_gram(cuda_lib, K, f, multi):
     assert set(sel.cpu().tolist()) == set(exp_sel.tolist())
     assert not (set(sel.cpu().tolist()) & set(range(f)))
     assert abs(float(w.sum()) - 1.0) < 1e-6
+
+
+def test_krum_never_selects_non_finite_rows(cuda_lib):
+    """A Byzantine row with NaN / Inf entries (or one scaled up until its Gram entries overflow fp32) must get an
+    infinite score: the CPU oracle rejects it (NaN sorts last) and so must the GPU kernel."""
+    K, f = 12, 3
+    u = _updates(K, 4096, seed=5)
+    u[0, 7] = float("nan")
+    u[1, 9] = float("inf")
+    u[2] *= 1e25                                     # ||u||^2 overflows fp32 -> inf in the Gram matrix
+    from ddl25spring_b200.ops.gemm import gram_tcgen05
+    G = gram_tcgen05(u)
+    sel, w, scores = ops.krum_select(u, f, 2, gram_matrix=G)
+    assert not (set(sel.cpu().tolist()) & {0, 1, 2}), sel
+    assert torch.isinf(scores[:3]).all() and torch.isfinite(scores[3:]).all(), scores
+    agg = ops.weighted_sum(u, w)
+    assert torch.isfinite(agg).all()
+    # honest rows: same choice as the fp64 oracle restricted to finite rows
+    exp = ref.krum_scores(u.cpu(), f)
+    order = [i for i in torch.argsort(exp, stable=True).tolist() if i >= 3][:2]
+    assert set(sel.cpu().tolist()) == set(order)
