@@ -2,6 +2,7 @@
 // Everything here is written for Blackwell B200 only (compile: -gencode arch=compute_100a,code=sm_100a).
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdint>
 #include <cstdio>
 
@@ -43,6 +44,20 @@ void ddl_count_launch(int n = 1);
   } while (0)
 
 static constexpr int kNumSMs = 148;  // B200
+
+// One-time set-up that CUDA keeps PER DEVICE (cudaFuncSetAttribute for > 48 KB of dynamic shared memory): a plain
+// `static bool` would configure only the first device a multi-GPU host process touches and the launch on the second one
+// would fail.  Racing threads may both run the set-up; it is idempotent.
+struct DdlOncePerDevice {
+  std::atomic<unsigned long long> mask{0};
+  static unsigned long long bit() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+    return 1ull << (dev & 63);
+  }
+  bool need() const { return (mask.load(std::memory_order_acquire) & bit()) == 0; }
+  void done() { mask.fetch_or(bit(), std::memory_order_release); }
+};
 
 #ifdef __CUDACC__
 // Programmatic dependent launch: a step of the NHWC networks is ~200 dependent kernels of a few microseconds each, so the

@@ -575,8 +575,8 @@ int ddl_conv_tap_gemm(const float* const* acts, int n_maps, int N, int Ha, int W
 #define DDL_CONV_CASE3(BN_, MN_, DEEP_)                                                           \
   {                                                                                               \
     auto kern = conv_tap_gemm_kernel<BN_, MN_, DEEP_>;                                            \
-    static bool configured = false;                                                               \
-    if (!configured) { if (int e = set_smem(kern, ConvPlan<BN_, DEEP_>::TOTAL)) return e; configured = true; } \
+    static DdlOncePerDevice configured;                                                               \
+    if (configured.need()) { if (int e = set_smem(kern, ConvPlan<BN_, DEEP_>::TOTAL)) return e; configured.done(); } \
     DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kThreads), ConvPlan<BN_, DEEP_>::TOTAL, st, p)); \
   }
 #define DDL_CONV_CASE(BN_, MN_) { if (deep) DDL_CONV_CASE3(BN_, MN_, true) else DDL_CONV_CASE3(BN_, MN_, false) }
@@ -641,8 +641,8 @@ int ddl_conv_wgrad(const float* dY, int N, int Ho, int Wo, int Cout, const float
 #define DDL_WGRAD_CASE3(BN_, DEEP_)                                                               \
   {                                                                                               \
     auto kern = conv_wgrad_kernel<BN_, DEEP_>;                                                    \
-    static bool configured = false;                                                               \
-    if (!configured) { if (int e = set_smem(kern, ConvPlan<BN_, DEEP_>::TOTAL)) return e; configured = true; } \
+    static DdlOncePerDevice configured;                                                               \
+    if (configured.need()) { if (int e = set_smem(kern, ConvPlan<BN_, DEEP_>::TOTAL)) return e; configured.done(); } \
     DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kThreads), ConvPlan<BN_, DEEP_>::TOTAL, st, p)); \
   }
 #define DDL_WGRAD_CASE(BN_) { if (deep) DDL_WGRAD_CASE3(BN_, true) else DDL_WGRAD_CASE3(BN_, false) }

@@ -429,10 +429,10 @@ int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const Epilogue& ep
                 int n_split, int kb_per_split, cudaStream_t st) {
   using Plan = SmemPlan<BN, EB, SPLIT3>;
   auto kern = gemm_tcgen05_kernel<BN, EB, A_MN, B_MN, SPLIT3>;
-  static bool configured = false;
-  if (!configured) {
+  static DdlOncePerDevice configured;
+  if (configured.need()) {
     DDL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Plan::TOTAL));
-    configured = true;
+    configured.done();
   }
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, G * n_split);
   DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kThreads), Plan::TOTAL, st, ta, tb, epi, M, N, K, kb_per_split));
@@ -444,10 +444,10 @@ template <int BN, bool A_MN, bool B_MN, bool SPLIT3>
 int launch_gemm_short(const CUtensorMap& ta, const CUtensorMap& tb, const Epilogue& epi, int M, int N, int K, int G, cudaStream_t st) {
   using Plan = SmemPlan<BN, 4, SPLIT3, true>;
   auto kern = gemm_tcgen05_short_kernel<BN, A_MN, B_MN, SPLIT3>;
-  static bool configured = false;
-  if (!configured) {
+  static DdlOncePerDevice configured;
+  if (configured.need()) {
     DDL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Plan::TOTAL));
-    configured = true;
+    configured.done();
   }
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, G);
   DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kThreads), Plan::TOTAL, st, ta, tb, epi, M, N, K, (K + 31) / 32));
@@ -495,6 +495,10 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
   DDL_REQUIRE((lda * eb) % 16 == 0 && (ldb * eb) % 16 == 0, "operand leading dimensions must be multiples of 16 bytes");
   DDL_REQUIRE((reinterpret_cast<uintptr_t>(A) & 15) == 0 && (reinterpret_cast<uintptr_t>(B) & 15) == 0,
               "operands must be 16-byte aligned");
+  // a K-major operand's K is the innermost extent of its tensor map: TMA wants whole 16-byte units (a ragged inner extent hangs
+  // the copy on B200, see the gather path below) - pad the operand or use the MN-major form
+  DDL_REQUIRE((a_mn_major && b_mn_major) || ((int64_t)K * eb) % 16 == 0, "K-major operands need K*%d %% 16 == 0 (K=%d)", eb, K);
+  DDL_REQUIRE(K <= 0x7fffffff - 64, "K=%d too large", K);
   if (n_split < 1) n_split = 1;
   const int total_kb = (K + bk - 1) / bk;
   if (n_split > total_kb) n_split = total_kb;

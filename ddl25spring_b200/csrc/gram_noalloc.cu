@@ -24,7 +24,8 @@
 // Set-up.  Host code cannot use the array's name as a pointer (in host code the symbol is only a
 // stand-in; a kernel given it would fault or touch the wrong memory), so the first call on each
 // device resolves the real device address with cudaGetSymbolAddress while that device is current
-// and caches it.  That first call - which also triggers the usual one-time CUDA module load and
+// and caches it (per device ordinal, for the life of the process: the cached address does not survive a
+// cudaDeviceReset).  That first call - which also triggers the usual one-time CUDA module load and
 // function-attribute set-up - should be made before any stream capture is begun on that device.
 //
 // This entry point has no counterpart in the reference (the reference contains no native code and
@@ -63,7 +64,8 @@ extern "C" int ddl_gram_static_scratch(const float* updates, int64_t ld, int K, 
                                        int n_split, int precise, void* stream) {
   DDL_REQUIRE(updates != nullptr && gram != nullptr, "updates and gram must be device pointers supplied by the caller");
   DDL_REQUIRE(K >= 1 && K <= 128, "K=%d outside [1, 128] (one 128-row tile of clients)", K);
-  DDL_REQUIRE(D >= 1 && D <= 0x7fffffff, "D=%lld outside [1, 2^31)", (long long)D);
+  DDL_REQUIRE(D >= 4 && D <= 0x7fffffff - 64 && D % 4 == 0, "D=%lld must be a multiple of 4 in [4, 2^31 - 64)", (long long)D);
+  DDL_REQUIRE((ld * 4) % 16 == 0 && (reinterpret_cast<uintptr_t>(updates) & 15) == 0, "updates must be 16-byte aligned with a 16-byte row stride");
   DDL_REQUIRE(n_split >= 2, "n_split must be >= 2 (with one split no scratch is needed: call ddl_gemm_tcgen05)");
   const int64_t need = (int64_t)n_split * K * K;
   DDL_REQUIRE(need <= (int64_t)DDL_GRAM_STATIC_SCRATCH_FLOATS,

@@ -194,10 +194,10 @@ extern "C" int ddl_mnist_conv2_dgrad(const float* wt_dgrad, const float* dy2, co
   }
   DgradParams prm;
   prm.a1 = a1; prm.da1 = da1; prm.si = si; prm.ctas_per_client = kNumSMs / G;
-  static bool configured = false;
-  if (!configured) {
+  static DdlOncePerDevice configured;
+  if (configured.need()) {
     DDL_CUDA_CHECK(cudaFuncSetAttribute(conv2_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DG_SMEM));
-    configured = true;
+    configured.done();
   }
   DDL_CUDA_CHECK(ddl_launch_pdl(conv2_dgrad_kernel, dim3(prm.ctas_per_client * G), dim3(DG_THREADS), DG_SMEM, (cudaStream_t)stream, tm_d, tm_w, prm));
   DDL_LAUNCH_CHECK();

@@ -352,11 +352,11 @@ int ddl_mnist_conv2_pool_fwd(const float* W, const float* wt_fwd, const float* a
   Conv2Params prm;
   prm.W = W; prm.pooled = pooled; prm.pmask = pmask; prm.si = si;
   prm.ctas_per_client = kNumSMs / G;
-  static bool configured = false;
-  if (!configured) {
+  static DdlOncePerDevice configured;
+  if (configured.need()) {
     DDL_CUDA_CHECK(cudaFuncSetAttribute(conv2_pool_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CONV2_SMEM));
     DDL_CUDA_CHECK(cudaFuncSetAttribute(conv2_pool_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CONV2_SMEM));
-    configured = true;
+    configured.done();
   }
   const int grid = prm.ctas_per_client * G;
   if (train) DDL_CUDA_CHECK(ddl_launch_pdl(conv2_pool_fwd_kernel<true>, dim3(grid), dim3(kConv2Threads), CONV2_SMEM, (cudaStream_t)stream, tm_a, tm_w, prm));

@@ -198,10 +198,10 @@ int ddl_mnist_head_train(float* W, const float* h1, const int64_t* Y, int64_t y_
   DDL_REQUIRE(p_drop >= 0.f && p_drop < 1.f, "dropout probability must be in [0, 1)");
   StepInfo si = make_step(G, B, bsz, seed, 0.f, p_drop, lr);
   const int smem = (NCLS * FC1 + 16 + kHeadWarps * kPartial) * (int)sizeof(float);
-  static bool configured = false;
-  if (!configured) {
+  static DdlOncePerDevice configured;
+  if (configured.need()) {
     DDL_CUDA_CHECK(cudaFuncSetAttribute(head_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
+    configured.done();
   }
   dim3 grid(G, kHeadParts);
   DDL_CUDA_CHECK(ddl_launch_pdl(head_train_kernel, dim3(grid), dim3(kHeadWarps * 32), smem, (cudaStream_t)stream, W, h1, Y, y_client_stride, perm, perm_stride,

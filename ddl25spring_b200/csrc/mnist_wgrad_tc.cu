@@ -170,10 +170,10 @@ extern "C" int ddl_mnist_conv2_wgrad(const float* a1, const float* dy2, float* w
   }
   WgradParams prm;
   prm.part = wg_part; prm.si = si; prm.ctas_per_client = kNumSMs / G;
-  static bool configured = false;
-  if (!configured) {
+  static DdlOncePerDevice configured;
+  if (configured.need()) {
     DDL_CUDA_CHECK(cudaFuncSetAttribute(conv2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
-    configured = true;
+    configured.done();
   }
   DDL_CUDA_CHECK(ddl_launch_pdl(conv2_wgrad_kernel, dim3(prm.ctas_per_client * G), dim3(192), WG_SMEM, (cudaStream_t)stream, tm_a, tm_d, prm));
   DDL_LAUNCH_CHECK();

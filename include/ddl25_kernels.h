@@ -163,7 +163,10 @@ int ddl_mnist_small_update(float* W, const float* wg_part, int n_cta, const floa
  *    on one stream (or order them with events); leftover contents never need clearing because every
  *    partial tile is fully rewritten before it is read;
  *  - the first call on each device looks up the array's device address (cudaGetSymbolAddress) and
- *    does the one-time kernel set-up: make that first call before starting any stream capture.
+ *    does the one-time kernel set-up: make that first call before starting any stream capture;
+ *    the address is cached per device ordinal for the life of the process, so it does not survive a
+ *    cudaDeviceReset() - do not reset a device between calls;
+ *  - D must be a multiple of 4 (the tensor map's inner extent is a whole number of 16-byte units).
  * updates: [K, D] fp32, row stride ld (ld*4 and the pointer 16-byte aligned); gram: [K, K], row stride ldg. */
 #define DDL_GRAM_STATIC_SCRATCH_FLOATS (1 << 20)
 int ddl_gram_static_scratch(const float* updates, int64_t ld, int K, int64_t D, float* gram, int64_t ldg,

@@ -82,3 +82,16 @@ def test_static_scratch_rejects_oversized_problems(cuda_lib):
     torch.cuda.synchronize()
     exp = U.double() @ U.double().T
     assert float((G.double() - exp).abs().max() / exp.abs().max()) < 3e-3
+
+
+def test_static_scratch_rejects_ragged_inner_extent(cuda_lib):
+    """D is the innermost extent of the operand's tensor map: anything but whole 16-byte units must be refused with an
+    argument error before a launch (a ragged extent would stall the TMA copy)."""
+    from ddl25spring_b200.ops import _lib
+    L = cuda_lib
+    U = torch.randn(16, 70_004, device=DEV)
+    G = torch.empty(16, 16, device=DEV)
+    rc = L.ddl_gram_static_scratch(_lib.p(U), _lib.i64(U.stride(0)), 16, _lib.i64(70_001), _lib.p(G), _lib.i64(16), 8, 0,
+                                   _lib.stream())
+    assert rc == 1, rc                                     # DDL_ERR_ARG
+    assert "multiple of 4" in L.ddl_last_error().decode()
