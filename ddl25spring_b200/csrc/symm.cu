@@ -16,13 +16,29 @@
 //   4. exit barrier   : the last block to finish publishes "my stores are done" and waits for all peers, so
 //                       kernel completion on a GPU implies every peer's stores into it have landed.
 // Traffic per GPU ~ (W-1)/W of its rows out + the same in: the coordinate-sharded exchange of SURVEY 5.8.
-// All waits are bounded (5 s on %globaltimer): a missing peer sets an error flag instead of hanging the GPU.
+// All waits are bounded (5 s on %globaltimer): a missing peer sets an error flag instead of hanging the GPU, and once
+// the flag is set every later collective on the arena skips its stores (a timed-out exchange never publishes partial
+// results; the host raises at its next check()).
+//
+// Graph capture: the collective's sequence number ("epoch") and the finished-block counter live in DEVICE memory
+// (`state`: int[4] = go flag, finished blocks, epoch, spare) and are advanced by the kernel itself, so a launch carries no
+// per-call host value and can be recorded into a CUDA graph and replayed (DataParallel captures its bucket reductions as
+// parallel branches of the step graph).  One `state` + signal-pad set is a CHANNEL: collectives of one channel must be
+// stream-ordered on every rank and issued in the same order on all ranks.
+//
+// Optimizer epilogue (K2): with `opt.kind != 0` the weighted sum is treated as the summed gradient of this GPU's
+// coordinate shard; the kernel applies SGD(+momentum, weight decay) / Adam / AdamW to the local parameter shard (the
+// optimizer state exists only for the owned shard: ZeRO-1 style) and stores the NEW PARAMETERS to every replica, so
+// reduce-scatter + optimizer step + all-gather of a bucket are one launch.  With `mc_in` / `mc_out` (NVLS multicast
+// addresses) the W peer loads become one multimem.ld_reduce and the W peer stores one multimem.st: the switch adds.
 //
 // Replaces (reference): the CPU gloo all_reduce of flattened gradients / weights
 // (lab/tutorial_1b/DP/gradient_aggr/intro_DP_GA.py:53-67, weight_aggr/intro_DP_WA.py:54-67) and the Python
 // list reduction of client messages across "clients" (lab/tutorial_1a/hfl_complete.py:370-383).
 #include "common.cuh"
 #include "ddl25_kernels.h"
+#include "select.cuh"
+#include <cstring>
 
 namespace {
 
@@ -77,82 +93,131 @@ __device__ __forceinline__ float4 ld_peer(const float4* p) {
   return r;
 }
 
-template <int KP>
-__device__ __forceinline__ void sort_regs(float (&a)[KP]) {
-#pragma unroll
-  for (int k = 2; k <= KP; k <<= 1)
-#pragma unroll
-    for (int j = k >> 1; j > 0; j >>= 1)
-#pragma unroll
-      for (int i = 0; i < KP; ++i) {
-        const int l = i ^ j;
-        if (l > i) {
-          const bool up = ((i & k) == 0);
-          const float lo = fminf(a[i], a[l]), hi = fmaxf(a[i], a[l]);
-          a[i] = up ? lo : hi;
-          a[l] = up ? hi : lo;
-        }
-      }
-}
-
 struct ReduceArgs {
   int K, n_out;
   int64_t v0, v1;            // float4 range owned by this GPU
-  const float* base;         // optional local base vector (alpha * base + beta * sum)
+  const float* base;         // optional local base vector (alpha * base + beta * sum); the parameters when opt.kind != 0
+  const float* dev_w;        // optional DEVICE weights (override the by-value table: Krum's selection weights)
   float alpha, beta;
-  int rank_lo, rank_hi;      // sorted-rank window for MODE 1
-  int rank, world, epoch;
-  int* local_flags;          // [0] go flag, [1] finished-block counter (device-local)
-  unsigned int done_target;  // counter value that identifies the last block of THIS launch
+  int rank_lo, rank_hi;      // sorted-rank window for MODE 1 / 3
+  int rank, world;
+  int* state;                // device-local channel state: [0] go flag, [1] finished blocks, [2] epoch
   int* err;
+  const float* mc_in;        // NVLS: multicast address of the summed buffer (nullptr = peer loads through the row table)
+  float* mc_out;             // NVLS: multicast address of the destination (nullptr = peer stores through the out table)
+  ddl_opt_args opt;
 };
 
-// MODE 0: weighted sum (float4 per thread).  MODE 1: sorted-rank window mean (one coordinate per thread, KP rows).
+// One optimizer update of 4 coordinates: g = summed gradient (already scaled by beta = 1/W), p = parameters.
+__device__ __forceinline__ float4 opt_apply(const ddl_opt_args& o, float4 p, float4 g, int64_t v, float bc1, float bc2_rsqrt) {
+  float* pp = &p.x;
+  float* gg = &g.x;
+  if (o.kind == 1) {                                   // SGD (+ weight decay, + momentum)
+    float4 mb = make_float4(0.f, 0.f, 0.f, 0.f);
+    float* m4 = &mb.x;
+    if (o.m != nullptr) mb = reinterpret_cast<const float4*>(o.m)[v - o.state_off4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float d = fmaf(o.weight_decay, pp[i], gg[i]);
+      if (o.m != nullptr) { m4[i] = fmaf(o.momentum, m4[i], d); d = m4[i]; }
+      pp[i] = fmaf(-o.lr, d, pp[i]);
+    }
+    if (o.m != nullptr) reinterpret_cast<float4*>(o.m)[v - o.state_off4] = mb;
+  } else {                                             // 2 = Adam (L2 in the gradient), 3 = AdamW (decoupled decay)
+    float4 mb = reinterpret_cast<const float4*>(o.m)[v - o.state_off4];
+    float4 vb = reinterpret_cast<const float4*>(o.v)[v - o.state_off4];
+    float* m4 = &mb.x;
+    float* v4 = &vb.x;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float d = gg[i];
+      if (o.kind == 3) pp[i] *= (1.f - o.lr * o.weight_decay);
+      else d = fmaf(o.weight_decay, pp[i], d);
+      m4[i] = fmaf(o.beta1, m4[i], (1.f - o.beta1) * d);
+      v4[i] = fmaf(o.beta2, v4[i], (1.f - o.beta2) * d * d);
+      pp[i] -= (o.lr / bc1) * (m4[i] / (sqrtf(v4[i]) * bc2_rsqrt + o.eps));
+    }
+    reinterpret_cast<float4*>(o.m)[v - o.state_off4] = mb;
+    reinterpret_cast<float4*>(o.v)[v - o.state_off4] = vb;
+  }
+  return p;
+}
+
+// MODE 0: weighted sum (float4 per thread), optional optimizer epilogue / NVLS.  MODE 1: sorted-rank window mean
+// (one coordinate per thread, KP rows), MODE 3: the same for a window that is exactly the median (pruned network).
+// MODE 2: gather of this GPU's coordinate shard of every row.
 template <int MODE, int KP>
 __global__ void __launch_bounds__(256) symm_reduce_kernel(RowTable tab, OutTable ot, PeerPads pp, ReduceArgs a) {
+  // the channel's epoch is advanced by the LAST block of the previous collective, i.e. it is stable for the whole launch
+  const int epoch = ld_acquire_gpu(a.state + 2) + 1;
   // ---- 1. entry barrier
   if (blockIdx.x == 0) {
-    cross_gpu_barrier(pp, a.rank, a.world, 0, a.epoch, a.err);
+    cross_gpu_barrier(pp, a.rank, a.world, 0, epoch, a.err);
     __syncthreads();
-    if (threadIdx.x == 0) st_release_gpu(a.local_flags, a.epoch);
+    if (threadIdx.x == 0) st_release_gpu(a.state, epoch);
   } else {
     if (threadIdx.x == 0) {
       const unsigned long long t0 = gtime();
-      while (ld_acquire_gpu(a.local_flags) < a.epoch) {
+      while (ld_acquire_gpu(a.state) < epoch) {
         if (gtime() - t0 > kTimeoutNs) { atomicExch(a.err, 100); break; }
       }
     }
     __syncthreads();
   }
+  // a collective that timed out (now or earlier) must not publish anything: peers may be absent or out of step
+  const bool healthy = (*reinterpret_cast<volatile int*>(a.err) == 0);
   // ---- 2 + 3. reduce my coordinate shard over all rows, store to all replicas
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t v = a.v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; MODE == 0 && v < a.v1; v += stride) {
-    float4 r;
-    {
+  if constexpr (MODE == 0) {
+    float bc1 = 1.f, bc2_rsqrt = 1.f;
+    if (a.opt.kind >= 2) {
+      const float step = (float)(*a.opt.step_dev + 1);          // completed steps + 1; bumped by the step's last bucket
+      bc1 = 1.f - powf(a.opt.beta1, step);
+      bc2_rsqrt = 1.f / sqrtf(1.f - powf(a.opt.beta2, step));
+    }
+    for (int64_t v = a.v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; healthy && v < a.v1; v += stride) {
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      int k = 0;
-      for (; k + 8 <= a.K; k += 8) {
-        float4 x[8];
+      if (a.mc_in != nullptr) {
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(acc.x), "=f"(acc.y), "=f"(acc.z), "=f"(acc.w) : "l"(a.mc_in + 4 * v) : "memory");
+      } else {
+        // zero-weight rows are neither loaded nor accumulated (Krum: only the selected rows cross NVLink; a rejected
+        // row may hold NaN / Inf, which 0 * x would turn into NaN)
+        int k = 0;
+        for (; k + 8 <= a.K; k += 8) {
+          float4 x[8];
+          float w[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) x[u] = ld_peer(reinterpret_cast<const float4*>(tab.rows[k + u]) + v);
+          for (int u = 0; u < 8; ++u) {
+            w[u] = a.dev_w ? __ldg(a.dev_w + k + u) : tab.w[k + u];
+            x[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (w[u] != 0.f) x[u] = ld_peer(reinterpret_cast<const float4*>(tab.rows[k + u]) + v);
+          }
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          const float w = tab.w[k + u];
-          acc.x = fmaf(w, x[u].x, acc.x); acc.y = fmaf(w, x[u].y, acc.y); acc.z = fmaf(w, x[u].z, acc.z); acc.w = fmaf(w, x[u].w, acc.w);
+          for (int u = 0; u < 8; ++u) {
+            acc.x = fmaf(w[u], x[u].x, acc.x); acc.y = fmaf(w[u], x[u].y, acc.y); acc.z = fmaf(w[u], x[u].z, acc.z); acc.w = fmaf(w[u], x[u].w, acc.w);
+          }
+        }
+        for (; k < a.K; ++k) {
+          const float w = a.dev_w ? __ldg(a.dev_w + k) : tab.w[k];
+          if (w == 0.f) continue;
+          const float4 x = ld_peer(reinterpret_cast<const float4*>(tab.rows[k]) + v);
+          acc.x = fmaf(w, x.x, acc.x); acc.y = fmaf(w, x.y, acc.y); acc.z = fmaf(w, x.z, acc.z); acc.w = fmaf(w, x.w, acc.w);
         }
       }
-      for (; k < a.K; ++k) {
-        const float4 x = ld_peer(reinterpret_cast<const float4*>(tab.rows[k]) + v);
-        const float w = tab.w[k];
-        acc.x = fmaf(w, x.x, acc.x); acc.y = fmaf(w, x.y, acc.y); acc.z = fmaf(w, x.z, acc.z); acc.w = fmaf(w, x.w, acc.w);
-      }
-      r = make_float4(a.beta * acc.x, a.beta * acc.y, a.beta * acc.z, a.beta * acc.w);
-      if (a.base != nullptr) {
+      float4 r = make_float4(a.beta * acc.x, a.beta * acc.y, a.beta * acc.z, a.beta * acc.w);
+      if (a.opt.kind != 0) {
+        r = opt_apply(a.opt, reinterpret_cast<const float4*>(a.base)[v], r, v, bc1, bc2_rsqrt);
+      } else if (a.base != nullptr) {
         const float4 b = reinterpret_cast<const float4*>(a.base)[v];
         r.x = fmaf(a.alpha, b.x, r.x); r.y = fmaf(a.alpha, b.y, r.y); r.z = fmaf(a.alpha, b.z, r.z); r.w = fmaf(a.alpha, b.w, r.w);
       }
+      if (a.mc_out != nullptr) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(a.mc_out + 4 * v), "f"(r.x), "f"(r.y), "f"(r.z), "f"(r.w) : "memory");
+      } else {
+        for (int o = 0; o < a.n_out; ++o) reinterpret_cast<float4*>(ot.outs[o])[v] = r;
+      }
     }
-    for (int o = 0; o < a.n_out; ++o) reinterpret_cast<float4*>(ot.outs[o])[v] = r;
   }
   if constexpr (MODE == 2) {
     // all-to-all half of the coordinate-sharded exchange: local[k][j] = rows[k][4*v0 + j], j < 4*(v1 - v0).
@@ -160,7 +225,7 @@ __global__ void __launch_bounds__(256) symm_reduce_kernel(RowTable tab, OutTable
     // of every client's update over NVLink instead of whole updates.
     const int64_t ld4 = a.v1 - a.v0;            // float4 per local row (a.rank_lo carries extra row padding)
     float4* dst = reinterpret_cast<float4*>(ot.outs[0]);
-    for (int64_t v = a.v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < a.v1; v += stride) {
+    for (int64_t v = a.v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; healthy && v < a.v1; v += stride) {
       for (int k = 0; k < a.K; k += 4) {
         float4 x[4];
 #pragma unroll
@@ -179,45 +244,53 @@ __global__ void __launch_bounds__(256) symm_reduce_kernel(RowTable tab, OutTable
       }
     }
   }
-  if constexpr (MODE == 1) {
-    // one coordinate per thread (KP values in registers), 128 B coalesced peer loads per warp per row
-    for (int64_t d = 4 * a.v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; d < 4 * a.v1; d += stride) {
+  if constexpr (MODE == 1 || MODE == 3) {
+    // one coordinate per thread (KP values in registers), 128 B coalesced peer loads per warp per row.
+    // MODE 3 = median: symmetric -inf / +inf padding keeps the median at the centre ranks, pruned network (select.cuh).
+    for (int64_t d = 4 * a.v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; healthy && d < 4 * a.v1; d += stride) {
       float c[KP];
 #pragma unroll
       for (int k = 0; k < KP; ++k) {
-        c[k] = INFINITY;
+        c[k] = MODE == 3 ? ddl::median_pad(k, a.K, KP) : INFINITY;
         if (k < a.K) asm volatile("ld.global.relaxed.sys.f32 %0, [%1];" : "=f"(c[k]) : "l"(tab.rows[k] + d) : "memory");
       }
-      sort_regs<KP>(c);
-      float s = 0.f;
-#pragma unroll
-      for (int k = 0; k < KP; ++k)
-        if (k >= a.rank_lo && k < a.rank_hi) s += c[k];
-      s *= 1.f / (float)(a.rank_hi - a.rank_lo);
+      const float s = MODE == 3 ? ddl::median_of<KP>(c, a.rank_hi - a.rank_lo == 2) : ddl::window_mean<KP>(c, a.rank_lo, a.rank_hi);
       for (int o = 0; o < a.n_out; ++o) ot.outs[o][d] = s;
     }
   }
-  // ---- 4. exit barrier: the last block of this launch waits until every peer's stores have landed here
+  // ---- 4. exit barrier: the last block of this launch waits until every peer's stores have landed here, then
+  //         advances the channel (epoch, finished counter) for the next collective
   __threadfence_system();
   __syncthreads();
   __shared__ int s_last;
-  if (threadIdx.x == 0) s_last = (atomicAdd(reinterpret_cast<unsigned int*>(a.local_flags + 1), 1u) + 1u == a.done_target);
+  if (threadIdx.x == 0) s_last = (atomicAdd(reinterpret_cast<unsigned int*>(a.state + 1), 1u) + 1u == gridDim.x);
   __syncthreads();
-  if (s_last) cross_gpu_barrier(pp, a.rank, a.world, a.world, a.epoch, a.err);
+  if (s_last) {
+    cross_gpu_barrier(pp, a.rank, a.world, a.world, epoch, a.err);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      if (a.opt.kind != 0 && a.opt.bump_step && a.opt.step_dev != nullptr) atomicAdd(a.opt.step_dev, 1);
+      a.state[1] = 0;
+      st_release_gpu(a.state + 2, epoch);
+    }
+  }
 }
 
-__global__ void symm_barrier_kernel(PeerPads pp, int rank, int world, int epoch, int* err) {
+__global__ void symm_barrier_kernel(PeerPads pp, int rank, int world, int* state, int* err) {
+  const int epoch = ld_acquire_gpu(state + 2) + 1;
   cross_gpu_barrier(pp, rank, world, 0, epoch, err);
   __syncthreads();
   cross_gpu_barrier(pp, rank, world, world, epoch, err);
+  __syncthreads();
+  if (threadIdx.x == 0) st_release_gpu(state + 2, epoch);
 }
 
 int fill(RowTable& tab, OutTable& ot, PeerPads& pp, const float* const* rows, const float* w, int K, float* const* outs, int n_out,
          int* const* pads, int world) {
   DDL_REQUIRE(K >= 1 && K <= kMaxRows, "K=%d outside [1, %d]", K, kMaxRows);
   DDL_REQUIRE(world >= 1 && world <= kMaxWorld, "world=%d outside [1, %d]", world, kMaxWorld);
-  DDL_REQUIRE(n_out >= 1 && n_out <= kMaxWorld, "n_out=%d outside [1, %d]", n_out, kMaxWorld);
-  for (int k = 0; k < K; ++k) { tab.rows[k] = rows[k]; tab.w[k] = w ? w[k] : 1.f; }
+  DDL_REQUIRE(n_out >= 0 && n_out <= kMaxWorld, "n_out=%d outside [0, %d]", n_out, kMaxWorld);
+  for (int k = 0; k < K; ++k) { tab.rows[k] = rows ? rows[k] : nullptr; tab.w[k] = w ? w[k] : 1.f; }
   for (int o = 0; o < n_out; ++o) ot.outs[o] = outs[o];
   for (int p = 0; p < world; ++p) pp.pad[p] = pads[p];
   return DDL_OK;
@@ -254,43 +327,69 @@ int ddl_ipc_close(void* ptr) {
   return DDL_OK;
 }
 
-int ddl_symm_barrier(int* const* pads, int rank, int world, int epoch, int* err, void* stream) {
+int ddl_symm_barrier(int* const* pads, int rank, int world, int* state, int* err, void* stream) {
   PeerPads pp;
   DDL_REQUIRE(world >= 1 && world <= kMaxWorld, "world=%d outside [1, %d]", world, kMaxWorld);
+  DDL_REQUIRE(state != nullptr && err != nullptr, "channel state / error flag missing");
   for (int p = 0; p < world; ++p) pp.pad[p] = pads[p];
-  symm_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pp, rank, world, epoch, err);
+  symm_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pp, rank, world, state, err);
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
 
-// mode 0: out = alpha*base + beta*sum_k w_k rows_k ; mode 1: mean of sorted ranks [rank_lo, rank_hi) (K <= 64);
-// mode 2: outs[0][k][j] = rows[k][d0 + j] - (base ? base[d0 + j] : 0), local row pitch (d1 - d0) + 4*rank_lo floats
-int ddl_symm_reduce(int mode, const float* const* rows, const float* weights, int K, const float* base, float alpha, float beta,
-                    int rank_lo, int rank_hi, float* const* outs, int n_out, int64_t d0, int64_t d1, int* const* pads, int rank,
-                    int world, int epoch, int* local_flags, int64_t* done_counter_host, int* err, int max_ctas, void* stream) {
+// mode 0: out = alpha*base + beta*sum_k w_k rows_k (or the optimizer epilogue); mode 1: mean of sorted ranks
+// [rank_lo, rank_hi) (K <= 64); mode 2: outs[0][k][j] = rows[k][d0 + j] - (base ? base[d0 + j] : 0), local row pitch
+// (d1 - d0) + 4*rank_lo floats
+int ddl_symm_reduce(int mode, const float* const* rows, const float* weights, const float* dev_weights, int K, const float* base,
+                    float alpha, float beta, int rank_lo, int rank_hi, float* const* outs, int n_out, int64_t d0, int64_t d1,
+                    int* const* pads, int rank, int world, int* state, int* err, int max_ctas, const ddl_opt_args* opt,
+                    const float* mc_in, float* mc_out, void* stream) {
   DDL_REQUIRE(d0 % 4 == 0 && d1 % 4 == 0 && d1 >= d0, "coordinate range must be float4 aligned");
   DDL_REQUIRE(mode != 1 || (K <= 64 && rank_lo >= 0 && rank_lo < rank_hi && rank_hi <= K), "bad rank window / K for rank-select mode");
   DDL_REQUIRE(mode >= 0 && mode <= 2, "mode must be 0 (weighted sum), 1 (rank-select mean) or 2 (gather shard)");
+  DDL_REQUIRE(state != nullptr && err != nullptr, "channel state / error flag missing");
+  DDL_REQUIRE((mc_in == nullptr && mc_out == nullptr) || mode == 0, "multicast operands are for mode 0 only");
+  DDL_REQUIRE(mc_in != nullptr || rows != nullptr, "no input rows");
+  DDL_REQUIRE(mc_out != nullptr || n_out >= 1, "no outputs");
   RowTable tab;
   OutTable ot;
   PeerPads pp;
   if (int e = fill(tab, ot, pp, rows, weights, K, outs, n_out, pads, world)) return e;
   ReduceArgs a;
-  a.K = K; a.n_out = n_out; a.v0 = d0 / 4; a.v1 = d1 / 4; a.base = base; a.alpha = alpha; a.beta = beta;
-  a.rank_lo = rank_lo; a.rank_hi = rank_hi; a.rank = rank; a.world = world; a.epoch = epoch; a.local_flags = local_flags; a.err = err;
+  a.K = K; a.n_out = n_out; a.v0 = d0 / 4; a.v1 = d1 / 4; a.base = base; a.dev_w = dev_weights; a.alpha = alpha; a.beta = beta;
+  a.rank_lo = rank_lo; a.rank_hi = rank_hi; a.rank = rank; a.world = world; a.state = state; a.err = err;
+  a.mc_in = mc_in; a.mc_out = mc_out;
+  memset(&a.opt, 0, sizeof(a.opt));
+  if (opt != nullptr && opt->kind != 0) {
+    DDL_REQUIRE(mode == 0 && base != nullptr, "the optimizer epilogue needs mode 0 and base = the local parameters");
+    DDL_REQUIRE(opt->kind >= 1 && opt->kind <= 3, "opt.kind must be 1 (sgd), 2 (adam) or 3 (adamw)");
+    DDL_REQUIRE(opt->kind == 1 || (opt->m != nullptr && opt->v != nullptr && opt->step_dev != nullptr), "Adam needs m, v and a device step counter");
+    DDL_REQUIRE(opt->state_off4 >= 0 && opt->state_off4 <= a.v0, "optimizer state offset beyond the shard start");
+    a.opt = *opt;
+    if (a.opt.kind == 1 && a.opt.momentum == 0.f) a.opt.m = nullptr;
+  }
   int64_t g = ((a.v1 - a.v0) + 255) / 256;
   const int cap = max_ctas > 0 ? max_ctas : kNumSMs * 2;     // all blocks must be co-resident (they wait on block 0)
   if (g > cap) g = cap;
   if (g < 1) g = 1;
-  *done_counter_host += g;
-  a.done_target = (unsigned int)(*done_counter_host);
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == 0) symm_reduce_kernel<0, 1><<<(int)g, 256, 0, st>>>(tab, ot, pp, a);
   else if (mode == 2) symm_reduce_kernel<2, 1><<<(int)g, 256, 0, st>>>(tab, ot, pp, a);
-  else if (K <= 8) symm_reduce_kernel<1, 8><<<(int)g, 256, 0, st>>>(tab, ot, pp, a);
-  else if (K <= 16) symm_reduce_kernel<1, 16><<<(int)g, 256, 0, st>>>(tab, ot, pp, a);
-  else if (K <= 32) symm_reduce_kernel<1, 32><<<(int)g, 256, 0, st>>>(tab, ot, pp, a);
-  else symm_reduce_kernel<1, 64><<<(int)g, 256, 0, st>>>(tab, ot, pp, a);
+  else {
+    // a window that is exactly the median of K values (single centre rank, or the centre pair of an even K) takes the
+    // pruned network; any other window the full sort
+    const bool med = (rank_lo == (K - 1) / 2 && rank_hi == rank_lo + 1) || (K % 2 == 0 && rank_lo == K / 2 - 1 && rank_hi == K / 2 + 1);
+#define DDL_SYMM_SEL(KP)                                                                    \
+    do {                                                                                    \
+      if (med) symm_reduce_kernel<3, KP><<<(int)g, 256, 0, st>>>(tab, ot, pp, a);           \
+      else symm_reduce_kernel<1, KP><<<(int)g, 256, 0, st>>>(tab, ot, pp, a);               \
+    } while (0)
+    if (K <= 8) DDL_SYMM_SEL(8);
+    else if (K <= 16) DDL_SYMM_SEL(16);
+    else if (K <= 32) DDL_SYMM_SEL(32);
+    else DDL_SYMM_SEL(64);
+#undef DDL_SYMM_SEL
+  }
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

@@ -33,6 +33,24 @@ class _DevBuf:
         self.tensor = torch.as_tensor(self, device=torch.device("cuda", device_index))
 
 
+class OptArgs(C.Structure):
+    """``ddl_opt_args`` of include/ddl25_kernels.h: the optimizer epilogue of the fused bucket reduce (K2)."""
+    _fields_ = [("kind", C.c_int), ("lr", C.c_float), ("weight_decay", C.c_float), ("momentum", C.c_float),
+                ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("m", C.c_void_p), ("v", C.c_void_p),
+                ("state_off4", C.c_int64), ("step_dev", C.c_void_p), ("bump_step", C.c_int)]
+
+
+class Channel:
+    """One ordered sequence of collectives: signal pads on every rank + a device-resident sequence number.
+
+    The kernels advance the sequence number themselves, so a launch carries no per-call host value and can be captured
+    into a CUDA graph.  Collectives of one channel must be stream-ordered on every rank and issued in the same order
+    by all ranks; independent streams (the DP bucket reducer next to the main stream) use separate channels."""
+
+    def __init__(self, pad_ptrs: list[int], state: torch.Tensor):
+        self.pad_ptrs, self.state = pad_ptrs, state
+
+
 class SymmetricArena:
     def __init__(self, group=None):
         assert dist.is_initialized() and torch.cuda.is_available()
@@ -42,18 +60,17 @@ class SymmetricArena:
         self.L = _lib.lib()
         self._bufs: dict[str, _DevBuf] = {}
         self._peers: dict[str, list[int]] = {}
-        self.epoch = 0
-        self.done_counter = C.c_int64(0)
-        pads = self.alloc("__pads__", 4 * 2 * 16 + 64, torch.int32)       # int[2*world] (+ slack)
-        self.pad_ptrs = self.peer_ptrs("__pads__")
-        self.local_flags = torch.zeros(2, dtype=torch.int32, device="cuda")
+        self._sizes: dict[str, int] = {}
+        self._n_channels = 0
         self.err = torch.zeros(1, dtype=torch.int32, device="cuda")
-        del pads
+        self.main = self.new_channel()
         self.barrier()
 
     # ------------------------------------------------------------------ allocation + exchange
     def alloc(self, name: str, nbytes: int, dtype=torch.float32) -> torch.Tensor:
         """Collective: every rank must call with the same ``name`` / size, in the same order."""
+        if name in self._bufs:
+            raise KeyError(f"symmetric buffer {name!r} already exists")
         want = int(nbytes)
         nbytes = (want + 255) // 256 * 256
         ptr = C.c_void_p()
@@ -72,7 +89,6 @@ class SymmetricArena:
             _lib.check(self.L.ddl_ipc_import((C.c_ubyte * 64).from_buffer_copy(h), C.byref(out)), "ddl_ipc_import")
             peers.append(out.value)
         self._bufs[name], self._peers[name] = buf, peers
-        self._sizes = getattr(self, "_sizes", {})
         self._sizes[name] = want
         return buf.tensor[:want].view(dtype)
 
@@ -82,29 +98,41 @@ class SymmetricArena:
     def peer_ptrs(self, name: str) -> list[int]:
         return self._peers[name]
 
-    # ------------------------------------------------------------------ barriers / errors
-    def next_epoch(self) -> int:
-        self.epoch += 1
-        return self.epoch
+    def new_channel(self) -> Channel:
+        """Collective: a fresh set of signal pads + sequence state (see :class:`Channel`)."""
+        name = f"__pads{self._n_channels}__"
+        self._n_channels += 1
+        self.alloc(name, 4 * 2 * 16 + 64, torch.int32)                # int[2*world] (+ slack), zeroed by the allocator
+        return Channel(self.peer_ptrs(name), torch.zeros(4, dtype=torch.int32, device="cuda"))
 
-    def barrier(self) -> None:
+    # ------------------------------------------------------------------ barriers / errors
+    def barrier(self, channel: Channel | None = None) -> None:
         """Cross-GPU barrier executed BY the GPUs (in stream order), not by the hosts."""
-        _lib.check(self.L.ddl_symm_barrier(_lib.host_ptrs(self.pad_ptrs), self.rank, self.world, self.next_epoch(),
-                                           _lib.p(self.err), _lib.stream()), "ddl_symm_barrier")
+        ch = channel or self.main
+        _lib.check(self.L.ddl_symm_barrier(_lib.host_ptrs(ch.pad_ptrs), self.rank, self.world, _lib.p(ch.state), _lib.p(self.err),
+                                           _lib.stream()), "ddl_symm_barrier")
 
     def check(self) -> None:
+        """Raise if any collective on this arena timed out (a rank did not launch its kernel within 5 s).  Reads one
+        device int: call it where the host synchronises anyway (after an accuracy read-back, every N optimizer steps)."""
         e = int(self.err.item())
         if e:
-            raise RuntimeError(f"peer-memory collective timed out on rank {self.rank} (code {e}): a rank did not launch its kernel")
+            raise RuntimeError(f"peer-memory collective timed out on rank {self.rank} (code {e}): a rank did not launch its "
+                               "kernel; every later collective on this arena skipped its stores")
 
     def reduce(self, mode: int, row_ptrs, weights, out_ptrs, d0: int, d1: int, *, base=None, alpha=0.0, beta=1.0,
-               rank_lo=0, rank_hi=1, max_ctas: int = 0) -> None:
-        K = len(row_ptrs)
-        _lib.check(self.L.ddl_symm_reduce(int(mode), _lib.host_ptrs(row_ptrs), _lib.host_floats(weights), K, _lib.p(base),
-                                          _lib.f32(alpha), _lib.f32(beta), int(rank_lo), int(rank_hi), _lib.host_ptrs(out_ptrs),
-                                          len(out_ptrs), _lib.i64(d0), _lib.i64(d1), _lib.host_ptrs(self.pad_ptrs), self.rank,
-                                          self.world, self.next_epoch(), _lib.p(self.local_flags), C.byref(self.done_counter),
-                                          _lib.p(self.err), int(max_ctas), _lib.stream()), "ddl_symm_reduce")
+               rank_lo=0, rank_hi=1, max_ctas: int = 0, dev_weights: torch.Tensor | None = None, channel: Channel | None = None,
+               opt: OptArgs | None = None, mc_in: int = 0, mc_out: int = 0) -> None:
+        ch = channel or self.main
+        K = len(row_ptrs) if row_ptrs else (len(weights) if weights is not None else self.world)
+        w = None if (weights is None or dev_weights is not None) else _lib.host_floats(weights)
+        _lib.check(self.L.ddl_symm_reduce(int(mode), _lib.host_ptrs(row_ptrs) if row_ptrs else None, w, _lib.p(dev_weights), K,
+                                          _lib.p(base), _lib.f32(alpha), _lib.f32(beta), int(rank_lo), int(rank_hi),
+                                          _lib.host_ptrs(out_ptrs) if out_ptrs else None, len(out_ptrs) if out_ptrs else 0,
+                                          _lib.i64(d0), _lib.i64(d1), _lib.host_ptrs(ch.pad_ptrs), self.rank, self.world,
+                                          _lib.p(ch.state), _lib.p(self.err), int(max_ctas),
+                                          C.byref(opt) if opt is not None else None, C.c_void_p(mc_in or None),
+                                          C.c_void_p(mc_out or None), _lib.stream()), "ddl_symm_reduce")
 
 
 def shard_bounds(n: int, world: int, rank: int, align: int = 4) -> tuple[int, int]:

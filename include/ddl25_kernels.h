@@ -172,25 +172,44 @@ int ddl_mnist_small_update(float* W, const float* wg_part, int n_cta, const floa
 int ddl_gram_static_scratch(const float* updates, int64_t ld, int K, int64_t D, float* gram, int64_t ldg,
                             int n_split, int precise, void* stream);
 
-/* ---- Symmetric peer memory + fused cross-GPU reduce (K1 / K2 / K4 / K5 over NVLink) ------------
+/* ---- Symmetric peer memory + fused cross-GPU reduce (K1 / K2 / K2b / K4 / K5 over NVLink) ------
  * (ref: gloo all_reduce of flattened grads/weights, lab/tutorial_1b/DP/gradient_aggr/intro_DP_GA.py:53-67,
  *  weight_aggr/intro_DP_WA.py:54-67; client-message reduction lab/tutorial_1a/hfl_complete.py:370-383).
  * ddl_symm_alloc/ipc_*: cudaMalloc'd buffers shared between the ranks of one node with CUDA IPC.
  * ddl_symm_reduce: ONE kernel per GPU = entry barrier + reduce of coordinates [d0, d1) over all rows
  * (local or peer pointers; HOST arrays of device pointers) + store to every outs[] replica + exit barrier.
- *  mode 0: out = alpha*base + beta*sum_k weights[k]*rows[k]; mode 1: mean of sorted ranks [rank_lo, rank_hi).
- * pads[p]: int[2*world] signal pad on GPU p; epoch must increase by 1 per collective on every rank;
- * local_flags: int[2] device-local (zeroed once); *done_counter_host: host counter owned by the caller;
- * *err (device int, zeroed once) becomes non-zero if a peer did not arrive within 5 s. */
+ *  mode 0: out = alpha*base + beta*sum_k weights[k]*rows[k]  (dev_weights: optional DEVICE weights that override
+ *          `weights`, e.g. Krum's selection weights; zero-weight rows are not read);  with opt->kind != 0 the sum
+ *          is a gradient: out = the new parameters after an SGD / Adam / AdamW step on base (the local parameter
+ *          shard) - reduce-scatter, optimizer step and all-gather of a DP bucket in one launch;  with mc_in /
+ *          mc_out (NVLS multicast addresses of the summed / destination buffers) the peer loads / stores go
+ *          through the switch (multimem.ld_reduce / multimem.st) and rows / outs may be NULL / 0.
+ *  mode 1: mean of sorted ranks [rank_lo, rank_hi) (K <= 64; a window that is the median uses a pruned network);
+ *  mode 2: gather of this GPU's coordinate shard of every row (minus base) into outs[0].
+ * A CHANNEL is pads[p] (int[2*world] signal pad on GPU p) + state (int[4] on this GPU, zeroed once): the sequence
+ * number of the collective lives in `state` and is advanced by the kernel, so launches can be captured into CUDA
+ * graphs; collectives of one channel must be stream-ordered and issued in the same order on every rank.
+ * *err (device int, zeroed once) becomes non-zero if a peer did not arrive within 5 s; from then on every
+ * collective given that flag skips its stores. */
+typedef struct ddl_opt_args {
+  int kind;            /* 0 none, 1 SGD, 2 Adam (L2 decay), 3 AdamW (decoupled decay) */
+  float lr, weight_decay, momentum, beta1, beta2, eps;
+  float* m;            /* SGD momentum buffer / Adam exp_avg of the owned shard (index: coordinate - 4*state_off4) */
+  float* v;            /* Adam exp_avg_sq of the owned shard */
+  int64_t state_off4;  /* first owned coordinate / 4 */
+  int* step_dev;       /* DEVICE int: completed optimizer steps (bias correction uses *step_dev + 1) */
+  int bump_step;       /* != 0 on the LAST bucket of a step: the kernel increments *step_dev when it finishes */
+} ddl_opt_args;
 int ddl_symm_alloc(void** ptr, int64_t bytes);
 int ddl_symm_free(void* ptr);
 int ddl_ipc_export(void* ptr, unsigned char* handle64);
 int ddl_ipc_import(const unsigned char* handle64, void** ptr);
 int ddl_ipc_close(void* ptr);
-int ddl_symm_barrier(int* const* pads, int rank, int world, int epoch, int* err, void* stream);
-int ddl_symm_reduce(int mode, const float* const* rows, const float* weights, int K, const float* base, float alpha, float beta,
-                    int rank_lo, int rank_hi, float* const* outs, int n_out, int64_t d0, int64_t d1, int* const* pads, int rank,
-                    int world, int epoch, int* local_flags, int64_t* done_counter_host, int* err, int max_ctas, void* stream);
+int ddl_symm_barrier(int* const* pads, int rank, int world, int* state, int* err, void* stream);
+int ddl_symm_reduce(int mode, const float* const* rows, const float* weights, const float* dev_weights, int K, const float* base,
+                    float alpha, float beta, int rank_lo, int rank_hi, float* const* outs, int n_out, int64_t d0, int64_t d1,
+                    int* const* pads, int rank, int world, int* state, int* err, int max_ctas, const ddl_opt_args* opt,
+                    const float* mc_in, float* mc_out, void* stream);
 
 /* ---- K7: vertical-FL embedding gather fused into the top model's first GEMM --------------------
  * (ref: torch.cat(party_outs, 1) + fc1, lab/tutorial_2b/vfl.py:36-37; exercise_3.py:128,85).
