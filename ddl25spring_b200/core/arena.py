@@ -103,6 +103,20 @@ class FlatArena:
                 src.data = v  # parameter / buffer now aliases the arena
         self.module = module
 
+    def rebase(self, storage: torch.Tensor) -> None:
+        """Move the arena onto caller-provided storage (e.g. a symmetric / peer-mapped buffer) and re-bind the module's
+        parameters and buffers as views into it.  ``storage``: 1-D, same dtype / device, at least ``size`` elements."""
+        assert storage.dim() == 1 and storage.numel() >= self.size and storage.dtype == self.flat.dtype
+        new = storage[:self.size]
+        with torch.no_grad():
+            new.copy_(self.flat)
+        self.flat = new
+        if self.module is not None:
+            params = dict(self.module.named_parameters())
+            bufs = dict(self.module.named_buffers())
+            for s, v in zip(self.specs, self.views()):
+                (bufs[s.name] if s.is_buffer else params[s.name]).data = v
+
     def bind_grads(self) -> torch.Tensor:
         """Allocate the gradient arena and alias every ``param.grad`` into it."""
         if self.grad is None:

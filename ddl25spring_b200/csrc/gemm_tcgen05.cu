@@ -45,6 +45,10 @@ struct Epilogue {
   float beta;           // direct (n_split == 1) path only: C = act(alpha*acc + beta*C_old + bias)
   int n_split;          // > 1: write raw partial tiles to C = scratch[split][g][M][N] (ldc = N)
   int same_ab;          // A and B are the same matrix (Gram / SYRK): stage each tile once, use it as both operands
+  const float* center;  // SPLIT3 only, may be null: K-vector subtracted from every row of the staged tiles before the hi/lo
+                        // split (Krum scores update DELTAS u_k - global; re-centring in shared memory means the K x D delta
+                        // matrix is never materialised in HBM)
+  int64_t center_len;   // valid entries of `center` (guards the ragged last k-block)
 };
 
 __device__ __forceinline__ float apply_act(float v, int act, float slope) {
@@ -242,13 +246,29 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
       uint32_t phase = 0;
       int s = 0;
       constexpr int NV = (Plan::A_BYTES + Plan::B_BYTES) / 16;   // float4 count of A|B (contiguous)
+      const int nv = epi.same_ab ? Plan::A_BYTES / 16 : NV;      // SYRK: only the A tile was staged
+      // Re-centring: float4 i of a K-major 128B-swizzled tile is row i/8, physical 16-byte chunk i%8, i.e. logical
+      // columns 4*((i%8) ^ (row%8)) .. +3.  With 128 splitter threads striding by 128, a thread's chunk and row%8 never
+      // change, so it needs ONE float4 of the centre vector per k-block, fetched before the wait on the TMA bytes.
+      const int cchunk = ((et & 7) ^ ((et >> 3) & 7)) * 4;
       for (int kb = 0; kb < num_kb; ++kb) {
+        float4 cv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (epi.center != nullptr) {
+          const int64_t c0 = (int64_t)(kb_begin + kb) * BK + cchunk;
+          if (c0 + 3 < epi.center_len) cv = __ldg(reinterpret_cast<const float4*>(epi.center + c0));
+          else if (c0 < epi.center_len) {
+            cv.x = epi.center[c0];
+            if (c0 + 1 < epi.center_len) cv.y = epi.center[c0 + 1];
+            if (c0 + 2 < epi.center_len) cv.z = epi.center[c0 + 2];
+          }
+        }
         mbar_wait(&full_bar[s], phase);
         float4* hi = reinterpret_cast<float4*>(stage_base + s * Plan::STAGE_BYTES);
         float4* lo = hi + NV;
 #pragma unroll 4
-        for (int i = et; i < NV; i += 32 * kEpiWarps) {
+        for (int i = et; i < nv; i += 32 * kEpiWarps) {
           float4 x = hi[i], h, l;
+          x.x -= cv.x; x.y -= cv.y; x.z -= cv.z; x.w -= cv.w;
           h.x = __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u); l.x = x.x - h.x;
           h.y = __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u); l.y = x.y - h.y;
           h.z = __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u); l.z = x.z - h.z;
@@ -483,11 +503,11 @@ int64_t ddl_gemm_scratch_floats(int M, int N, int G, int n_split) {
   return n_split > 1 ? (int64_t)n_split * G * M * N : 0;
 }
 
-int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_mn_major, const void* B, int64_t ldb,
+static int gemm_impl(const void* A, int64_t lda, int64_t a_group_stride, int a_mn_major, const void* B, int64_t ldb,
                      int64_t b_group_stride, int b_mn_major, float* C, int64_t ldc, int64_t c_group_stride,
                      const float* bias, int64_t bias_group_stride, int act, float slope, float alpha, float beta,
                      int M, int N, int K, int G, int dtype_bytes, int precise, int n_split, float* scratch,
-                     void* stream) {
+                     const float* center, void* stream) {
   DDL_REQUIRE(M > 0 && N > 0 && K > 0 && G > 0, "empty GEMM");
   DDL_REQUIRE(dtype_bytes == 4 || dtype_bytes == 2, "operands must be fp32 (tf32 math) or bf16");
   DDL_REQUIRE(!(precise && dtype_bytes != 4), "precise (3xTF32) mode needs fp32 operands");
@@ -528,11 +548,15 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
   epi.act = act; epi.slope = slope; epi.alpha = alpha; epi.beta = beta; epi.n_split = n_split;
   // Gram / SYRK: identical operands that fit one tile in both dimensions are staged once
   epi.same_ab = (A == B && lda == ldb && a_group_stride == b_group_stride && a_mn_major == 0 && b_mn_major == 0 && M == N &&
-                 M <= BM && N <= BN && !precise) ? 1 : 0;
+                 M <= BM && N <= BN) ? 1 : 0;
+  DDL_REQUIRE(center == nullptr || (precise && eb == 4 && !a_mn_major && !b_mn_major && (reinterpret_cast<uintptr_t>(center) & 15) == 0),
+              "re-centring needs the 3xTF32 mode, K-major fp32 operands and a 16-byte aligned centre vector");
+  epi.center = center; epi.center_len = K;
   cudaStream_t st = (cudaStream_t)stream;
   int rc;
   const bool amn = a_mn_major != 0, bmn = b_mn_major != 0;
   if (use_short) {
+    DDL_REQUIRE(center == nullptr, "re-centring is not available on the short-K path");
     epi.same_ab = 0;
     return precise ? dispatch_short<true>(amn, bmn, ta, tb, epi, M, N, K, G, st) : dispatch_short<false>(amn, bmn, ta, tb, epi, M, N, K, G, st);
   }
@@ -554,6 +578,25 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
     DDL_LAUNCH_CHECK();
   }
   return DDL_OK;
+}
+
+int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_mn_major, const void* B, int64_t ldb,
+                     int64_t b_group_stride, int b_mn_major, float* C, int64_t ldc, int64_t c_group_stride,
+                     const float* bias, int64_t bias_group_stride, int act, float slope, float alpha, float beta,
+                     int M, int N, int K, int G, int dtype_bytes, int precise, int n_split, float* scratch,
+                     void* stream) {
+  return gemm_impl(A, lda, a_group_stride, a_mn_major, B, ldb, b_group_stride, b_mn_major, C, ldc, c_group_stride, bias,
+                   bias_group_stride, act, slope, alpha, beta, M, N, K, G, dtype_bytes, precise, n_split, scratch, nullptr, stream);
+}
+
+// K3: Gram matrix of update DELTAS, G = (U - 1 c^T)(U - 1 c^T)^T, without materialising the deltas: the 3xTF32 splitter
+// subtracts the centre (the global model) from every staged tile in shared memory.  center == NULL: plain U U^T.
+int ddl_gram_tcgen05(const float* updates, int64_t ld, int K, int64_t D, const float* center, float* gram, int64_t ldg,
+                     int precise, int n_split, float* scratch, void* stream) {
+  DDL_REQUIRE(K >= 1 && K <= BM, "K=%d outside [1, %d] (one tile of clients)", K, BM);
+  DDL_REQUIRE(D >= 4 && D <= 0x7fffffff - 64, "D=%lld out of range", (long long)D);
+  return gemm_impl(updates, ld, 0, 0, updates, ld, 0, 0, gram, ldg, 0, nullptr, 0, 0, 0.f, 1.f, 0.f, K, K, (int)D, 1, 4,
+                   center != nullptr ? 1 : precise, n_split, scratch, center, stream);
 }
 
 // K7 host side: A = cat_p(parts[p]) along K, parts may be peer-mapped device pointers.
@@ -597,6 +640,7 @@ int ddl_gather_gemm_tcgen05(const float* const* parts, const int* part_dims, con
   epi.C = n_split > 1 ? scratch : C;
   epi.ldc = ldc; epi.c_group_stride = 0; epi.bias = bias; epi.bias_group_stride = 0;
   epi.act = act; epi.slope = slope; epi.alpha = 1.f; epi.beta = 0.f; epi.n_split = n_split; epi.same_ab = 0;
+  epi.center = nullptr; epi.center_len = 0;
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, n_split);
 #define DDL_GATHER_CASE(BN_, P_)                                                                              \
@@ -624,7 +668,7 @@ int ddl_gather_gemm_tcgen05(const float* const* parts, const int* part_dims, con
 // K3 fused: G = U U^T where the rows of U live on different GPUs (rows_per_part consecutive rows each, row stride ld) and only
 // the coordinate slice [d0, d1) is reduced here (every GPU owns one slice; the K x K partials are summed afterwards).
 int ddl_gram_rowgather_tcgen05(const float* const* part_ptrs, int n_parts, int rows_per_part, int64_t ld, int64_t d0, int64_t d1,
-                               float* gram, int64_t ldg, int precise, int n_split, float* scratch, void* stream) {
+                               const float* center, float* gram, int64_t ldg, int precise, int n_split, float* scratch, void* stream) {
   DDL_REQUIRE(n_parts >= 1 && n_parts <= kMaxParts, "n_parts=%d outside [1, %d]", n_parts, kMaxParts);
   DDL_REQUIRE(rows_per_part >= 8 && rows_per_part % 8 == 0, "rows_per_part=%d must be a multiple of 8 (1024-byte swizzle atoms)", rows_per_part);
   const int Kc = n_parts * rows_per_part;                      // clients = rows of U
@@ -651,6 +695,8 @@ int ddl_gram_rowgather_tcgen05(const float* const* part_ptrs, int n_parts, int r
   epi.C = n_split > 1 ? scratch : gram;
   epi.ldc = ldg; epi.c_group_stride = 0; epi.bias = nullptr; epi.bias_group_stride = 0;
   epi.act = 0; epi.slope = 0.f; epi.alpha = 1.f; epi.beta = 0.f; epi.n_split = n_split; epi.same_ab = 1;
+  DDL_REQUIRE(center == nullptr || (precise && (reinterpret_cast<uintptr_t>(center + d0) & 15) == 0), "re-centring needs precise != 0 and an aligned centre vector");
+  epi.center = center ? center + d0 : nullptr; epi.center_len = Kdim;
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(1, 1, n_split);
 #define DDL_ROWG_CASE2(BN_, P_)                                                                                \

@@ -86,20 +86,23 @@ class Krum(Aggregator):
         self.last_scores: torch.Tensor | None = None
 
     def __call__(self, updates, weights, *, out=None, global_flat=None):
-        K = updates.shape[0]
-        U = updates
-        if global_flat is not None:
-            U = updates - global_flat[None, :]
-        if self.score_dims is not None:
-            U = U[:, :self.score_dims]
+        U = updates if self.score_dims is None else updates[:, :self.score_dims]
         if U.is_cuda:
+            # the global model is subtracted from the staged tiles inside the Gram kernel (3xTF32): no K x D delta matrix
             from ..ops.gemm import gram_tcgen05
-            G = gram_tcgen05(U.contiguous() if U.stride(1) != 1 else U, precise=self.precise)
+            center = None
+            if global_flat is not None:
+                center = global_flat if self.score_dims is None else global_flat[:self.score_dims]
+            if center is not None and (U.shape[1] % 4 or U.stride(1) != 1 or center.data_ptr() % 16):
+                U, center = (U - center[None, :]).contiguous(), None           # ragged score_dims: rare, not the hot path
+            G = gram_tcgen05(U, precise=self.precise, center=center)
             sel, selw, scores = ops.krum_select(U, self.f, self.multi, gram_matrix=G)
         else:
+            if global_flat is not None:
+                U = U - (global_flat if self.score_dims is None else global_flat[:self.score_dims])[None, :]
             sel, selw, scores = ops.krum_select(U, self.f, self.multi)
         self.last_selected, self.last_scores = sel, scores
-        return ops.weighted_sum(updates, selw, out)
+        return ops.weighted_sum(updates, selw, out)           # device weights; rows with weight 0 are not read
 
     def __repr__(self):
         return f"Krum(f={self.f}, multi={self.multi})"

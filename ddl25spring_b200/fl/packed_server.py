@@ -67,6 +67,10 @@ class PackedFedAvgServer:
         self.model = MnistCnn(p_drop1, p_drop2).to(self.device)
         self.arena = FlatArena.from_module(self.model)
         assert self.arena.size == P
+        if collective is not None and self.world > 1 and hasattr(collective, "global_storage"):
+            # keep the global model in the symmetric buffer the fused kernels write the aggregate into (on every rank):
+            # the new global model needs no further copy
+            self.arena.rebase(collective.global_storage())
 
         # client shards: [N, n_max, 784] + [N, n_max] (+ counts), on device or in pinned host memory
         xs, ys = zip(*[materialize_client_data(s) for s in client_subsets])
@@ -276,6 +280,9 @@ class PackedFedAvgServer:
                 self._aggregate(W_local, mine_pos, weights)
             acc = self.test()
             res.device_time_ms.append(timer.stop_ms())
+            if self.collective is not None and self.world > 1:
+                self.collective.arena.check()          # the host is synchronised here anyway: a peer time-out raises instead of
+                                                       # silently leaving a stale global model
             elapsed += perf_counter() - t0
             res.wall_time.append(round(elapsed, 1))
             res.message_count.append(message_count(nr_round, self.nr_clients_per_round))

@@ -254,9 +254,14 @@ class DecentralizedServer(Server):
             with torch.no_grad():
                 if self.collective is not None and self.world > 1:
                     mine_pos = [p for p in range(len(chosen)) if p % self.world == self.rank]
-                    base = torch.zeros_like(gflat) if self.message_is_gradient else gflat.clone()
-                    self.collective.aggregate(self.aggregator, U[:len(mine_pos)], mine_pos, weights, base)
-                    agg = agg_out.copy_(base)
+                    # gradient messages are aggregated around 0, weight messages around the current global model (Krum scores
+                    # deltas); the fused kernels leave the aggregate in agg_out on every rank
+                    if self.message_is_gradient:
+                        agg_out.zero_()
+                    else:
+                        agg_out.copy_(gflat)
+                    self.collective.aggregate(self.aggregator, U[:len(mine_pos)], mine_pos, weights, agg_out)
+                    agg = agg_out
                 else:
                     agg = self.aggregator(U, weights, out=agg_out,
                                           global_flat=None if self.message_is_gradient else gflat)
@@ -267,6 +272,8 @@ class DecentralizedServer(Server):
             res.message_count.append(message_count(nr_round, self.nr_clients_per_round))
             res.samples.append(self.samples_per_round(chosen))
             res.test_accuracy.append(self.test())
+            if self.collective is not None and self.world > 1:
+                self.collective.arena.check()      # test() synchronised the host: raise on a peer time-out instead of going on
         return res
 
 

@@ -108,15 +108,29 @@ def default_gram_splits(K: int, D: int) -> int:
 
 
 def gram_tcgen05(updates: torch.Tensor, out: torch.Tensor | None = None, n_split: int | None = None,
-                 precise: bool = False) -> torch.Tensor:
+                 precise: bool = False, center: torch.Tensor | None = None) -> torch.Tensor:
     """``G = U U^T`` for ``U`` = ``[K <= 128, D]`` client updates: split-K over D across all SMs with
     TMEM accumulators, deterministic partial reduction.  TF32 inputs (pass update *deltas*, whose
-    norms are small, to keep cancellation in ``G_ii + G_jj - 2 G_ij`` benign) or ``precise``."""
+    norms are small, to keep cancellation in ``G_ii + G_jj - 2 G_ij`` benign) or ``precise``.
+
+    ``center`` ([D], e.g. the global model): the Gram matrix of ``U - center`` is computed WITHOUT forming the
+    K x D delta matrix - the centre is subtracted from each staged tile in shared memory (3xTF32 path)."""
     K, D = updates.shape
     assert K <= 128, "one M tile: at most 128 clients per Gram launch"
     if n_split is None:
         n_split = default_gram_splits(K, D)
-    return gemm(updates, updates, n_split=n_split, precise=precise, out=out)
+    if center is None:
+        return gemm(updates, updates, n_split=n_split, precise=precise, out=out)
+    assert updates.is_cuda and updates.dtype == torch.float32 and updates.stride(1) == 1 and center.is_contiguous()
+    assert center.numel() >= D and center.dtype == torch.float32
+    if out is None:
+        out = torch.empty(K, K, device=updates.device, dtype=torch.float32)
+    n_split = max(1, min(n_split, (D + 31) // 32))
+    scratch = torch.empty(n_split * K * K, device=updates.device, dtype=torch.float32) if n_split > 1 else None
+    rc = _lib.lib().ddl_gram_tcgen05(_lib.p(updates), _lib.i64(updates.stride(0)), int(K), _lib.i64(D), _lib.p(center), _lib.p(out),
+                                     _lib.i64(out.stride(0)), 1, int(n_split), _lib.p(scratch), _lib.stream())
+    _lib.check(rc, "ddl_gram_tcgen05")
+    return out
 
 
 def gather_linear_ptrs(part_ptrs, part_dims, part_lds, M: int, w: torch.Tensor, bias: torch.Tensor | None = None,
@@ -149,17 +163,17 @@ def gather_linear_ptrs(part_ptrs, part_dims, part_lds, M: int, w: torch.Tensor, 
 
 
 def gram_rowgather_ptrs(part_ptrs, rows_per_part: int, ld: int, d0: int, d1: int, out: torch.Tensor, n_split: int = 148,
-                        precise: bool = True):
+                        precise: bool = True, center: torch.Tensor | None = None):
     """K3 fused all-gather + Gram: ``out = U[:, d0:d1] @ U[:, d0:d1].T`` with the rows of ``U`` on different GPUs
     (``part_ptrs[p]`` = device pointer, possibly peer-mapped, of GPU p's ``rows_per_part`` rows).  Row order p-major."""
     Kc = len(part_ptrs) * rows_per_part
     kb = (d1 - d0 + 31) // 32
-    if precise:
+    if precise and center is None:                 # raw weights: keep accumulation chains short; re-centred deltas do not need it
         n_split = max(n_split, -(-(d1 - d0) // PRECISE_CHAIN))
     n_split = max(1, min(n_split, kb))
     scratch = torch.empty(n_split * Kc * Kc, device=out.device, dtype=torch.float32) if n_split > 1 else None
     rc = _lib.lib().ddl_gram_rowgather_tcgen05(_lib.host_ptrs(part_ptrs), len(part_ptrs), int(rows_per_part), _lib.i64(ld), _lib.i64(d0),
-                                               _lib.i64(d1), _lib.p(out), _lib.i64(out.stride(0)), int(precise), int(n_split),
+                                               _lib.i64(d1), _lib.p(center), _lib.p(out), _lib.i64(out.stride(0)), int(precise), int(n_split),
                                                _lib.p(scratch), _lib.stream())
     _lib.check(rc, "ddl_gram_rowgather_tcgen05")
     return out

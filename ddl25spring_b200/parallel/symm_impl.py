@@ -156,11 +156,17 @@ class SymmetricAggregator:
             self.nvls = NvlsAllReduce.create(row_elems, self.arena)
         self.G, self.P = max_rows_per_rank, row_elems
         self.rows = self.arena.alloc("client_rows", self.G * self.P * 4).view(self.G, self.P)
-        self.result = self.arena.alloc("agg_result", self.P * 4)
+        self.result = self.arena.alloc("agg_result", self.P * 4)       # every rank's replica of the aggregate; a server may use it
+                                                                          # directly as its global parameter arena (global_storage())
         self.partial = self.arena.alloc("agg_partial", self.P * 4)
         self.partial_ptrs = self.arena.peer_ptrs("agg_partial")
         self.row_ptrs = self.arena.peer_ptrs("client_rows")
         self.res_ptrs = self.arena.peer_ptrs("agg_result")
+
+    def global_storage(self) -> torch.Tensor:
+        """Symmetric buffer the fused kernels write the aggregate into on EVERY rank: a server that keeps its global model
+        here (``FlatArena.rebase``) gets the new model without a further copy."""
+        return self.result
 
     def row_buffer(self, G: int) -> torch.Tensor:
         """Symmetric storage for this rank's ``G`` client weight rows (the engine trains in place in it)."""
@@ -223,7 +229,8 @@ class SymmetricAggregator:
                 from ..ops.gemm import gram_rowgather_ptrs
                 g0, g1 = shard_bounds(self.P, world, a.rank, align=32)
                 a.barrier()
-                gram_rowgather_ptrs(self.row_ptrs, rows_per_rank, self.P, g0, g1, self._gpart, precise=True)
+                gram_rowgather_ptrs(self.row_ptrs, rows_per_rank, self.P, g0, g1, self._gpart, precise=True,
+                                    center=gflat.detach())      # re-centred in shared memory: Gram of the deltas
                 order = torch.tensor([(k % world) * rows_per_rank + k // world for k in range(K)], device="cuda")
             else:
                 order = None
@@ -239,9 +246,11 @@ class SymmetricAggregator:
                 G = G[order][:, order].contiguous()                # back to client order
             sel, selw, scores = ops.krum_select(U, aggregator.f, aggregator.multi, gram_matrix=G)
             aggregator.last_selected, aggregator.last_scores = sel, scores
-            # selection weights live on the device; every rank reduces its shard of the selected rows
-            a.reduce(0, ptrs, selw.tolist(), self.res_ptrs, d0, d1)
-        gflat.copy_(self.result)
+            # selection weights stay on the device (no host round trip); every rank reduces its shard of the SELECTED rows
+            # only - zero-weight rows are not read
+            a.reduce(0, ptrs, None, self.res_ptrs, d0, d1, dev_weights=selw)
+        if gflat.data_ptr() != self.result.data_ptr():          # servers that adopt `result` as their global arena skip this copy
+            gflat.copy_(self.result)
 
 
 class _DevView:

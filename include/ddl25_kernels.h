@@ -119,6 +119,13 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
                      int M, int N, int K, int G, int dtype_bytes, int precise, int n_split, float* scratch,
                      void* stream);
 
+/* K3: G = (U - 1 c^T)(U - 1 c^T)^T for U = [K <= 128, D] (row stride ld): the Gram matrix of the update DELTAS u_k - c
+ * [north star: Krum].  The centre c (the global model, [D], 16-byte aligned; NULL = plain U U^T) is subtracted from the
+ * staged tiles in shared memory (3xTF32 mode is implied), so no K x D delta matrix is written to HBM.  Split-K scratch:
+ * n_split * K * K floats when n_split > 1. */
+int ddl_gram_tcgen05(const float* updates, int64_t ld, int K, int64_t D, const float* center, float* gram, int64_t ldg,
+                     int precise, int n_split, float* scratch, void* stream);
+
 /* ---- Packed MnistCnn engine: G clients trained in lock-step, grouped kernels -------------------
  * (ref: MnistCnn forward/backward + train_epoch, lab/tutorial_1a/hfl_complete.py:39-80, executed
  *  for all clients packed on the GPU at once instead of one client at a time, :365-375).
@@ -250,9 +257,10 @@ int ddl_causal_attention_bwd(const float* q, const float* k, const float* v, con
  * (HOST array of device pointers, may be peer-mapped) is the base of GPU p's rows_per_part rows (row stride ld floats).
  * Every k-block is TMA-loaded straight from the owning GPUs into one shared-memory tile that serves as both MMA operands.
  * Row order of the result: p * rows_per_part + i.  rows_per_part % 8 == 0, K <= 128; split-K scratch: n_split*K*K floats.
- * precise != 0 (3xTF32) is recommended: raw weights cannot be shifted to small-norm deltas in flight. */
+ * center (may be NULL; [>= d1] floats, precise != 0 required): subtracted from every row while the tiles sit in shared
+ * memory, so the Gram matrix is that of the deltas u_k - center although raw weights cross NVLink. */
 int ddl_gram_rowgather_tcgen05(const float* const* part_ptrs, int n_parts, int rows_per_part, int64_t ld, int64_t d0, int64_t d1,
-                               float* gram, int64_t ldg, int precise, int n_split, float* scratch, void* stream);
+                               const float* center, float* gram, int64_t ldg, int precise, int n_split, float* scratch, void* stream);
 
 /* ---- NVLS all-reduce: in-switch reduction through a multicast address (multimem.ld_reduce / multimem.st) -----------------
  * (ref: gloo all_reduce, lab/tutorial_1b/DP/gradient_aggr/intro_DP_GA.py:63).  multicast_ptr addresses the same symmetric
