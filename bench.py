@@ -1,18 +1,28 @@
 #!/usr/bin/env python
-"""Headline benchmark: federated rounds/s and samples/s of FedAvg on MnistCnn (BASELINE.json metric
-"FL rounds/sec + samples/sec at 1/2/4/8 B200").
-
-Workload (identical for both arms): FedAvg as in lab/tutorial_1a/hfl_complete.py:336-390 — 100
-simulated clients holding an IID split of a 60 000-sample MNIST-shaped synthetic set, 8 sampled
-clients per GPU per round (client_fraction = 0.08 * n_gpus: weak scaling), E = 1 local epoch of
-minibatch SGD (B = 100, lr = 0.01), sample-count-weighted aggregation, and the top-1 evaluation of
-the new global model on the 10 000-sample test set that ``run()`` performs every round.
-One "step" = one federated round.
+"""Headline benchmark (BASELINE.json metric "FL rounds/sec + samples/sec at 1/2/4/8 B200; robust-aggregation
+latency/round").
 
   python bench.py [--gpus N --steps K --warmup W]           product arm (this framework)
   python bench.py --impl reference [...]                    unmodified reference from baseline/_ref
 
-Prints ONE JSON line on rank 0.
+Headline workload (identical for both arms; `value`, `ms_per_step`, `e2e`): FedAvg as in
+lab/tutorial_1a/hfl_complete.py:336-390 - 100 simulated clients holding an IID split of a 60 000-sample MNIST-shaped
+synthetic set, 8 sampled clients per GPU per round (client_fraction = 0.08 * n_gpus: weak scaling), E = 1 local epoch of
+minibatch SGD (B = 100, lr = 0.01), sample-count-weighted aggregation, and the top-1 evaluation of the new global model on
+the 10 000-sample test set that ``run()`` performs every round.  One "step" = one federated round.
+
+The product arm then measures, at the same N, the other north-star configurations of BASELINE.json and adds them to the
+SAME JSON line (they never change `value`):
+
+  "dp"      config 2 - data-parallel ResNet-18 on 32x32 CIFAR-shaped batches (256 per GPU): the fused peer-memory bucket
+            reduce (reduce-scatter + SGD + all-gather in one kernel per bucket, captured inside the step graph) next to the
+            NCCL all-reduce arm of the same model and stock torch DDP;
+  "robust"  config 4 - Byzantine-robust FedAvg of ResNet-18, 8 clients per GPU (64 at N = 8), 20 % sign-flip attackers:
+            rounds/s, samples/s and the aggregation latency per round of mean / Krum / coordinate median / trimmed mean,
+            each next to the NCCL all_gather + torch implementation of the same rule measured in the same process.
+
+Every extra section is guarded: an exception is reported inside its section, and a watchdog prints the line with what has
+been measured if the extras exceed their time budget.  Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
 
@@ -20,13 +30,17 @@ import argparse
 import json
 import os
 import sys
+import threading
+import time
 
 REPO = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, REPO)
 
 NR_CLIENTS, CLIENTS_PER_GPU, BATCH, EPOCHS, LR, SEED = 100, 8, 100, 1, 0.01, 10
 SAMPLES_PER_CLIENT = 600
+MODEL_BYTES = 1_199_882 * 4
 METRIC = "fl_samples_per_sec"
+RESNET_PARAMS = 11_181_642
 
 
 def parse():
@@ -36,6 +50,8 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--aggregator", default="mean")
+    ap.add_argument("--sections", default="dp,robust", help="extra north-star sections of the product arm ('' = none)")
+    ap.add_argument("--extras-budget-s", type=float, default=420.0, help="wall-clock budget of the extra sections")
     return ap.parse_args()
 
 
@@ -56,17 +72,17 @@ def init_dist(n_gpus: int):
     return rank, world, local
 
 
-def config_dict(n_gpus: int, extra: dict | None = None) -> dict:
-    cfg = {"model": "MnistCnn (LeNet-style, 1 199 882 params)", "algorithm": "FedAvg",
-           "nr_clients": NR_CLIENTS, "clients_per_round": CLIENTS_PER_GPU * n_gpus,
-           "client_fraction": round(CLIENTS_PER_GPU * n_gpus / NR_CLIENTS, 4), "local_epochs": EPOCHS,
-           "batch_size": BATCH, "lr": LR, "global_batch": CLIENTS_PER_GPU * n_gpus * BATCH, "seq_len": None,
-           "samples_per_round": CLIENTS_PER_GPU * n_gpus * SAMPLES_PER_CLIENT * EPOCHS, "test_samples_per_round": 10_000,
-           "parallelism": f"clients packed {CLIENTS_PER_GPU}/GPU x {n_gpus} GPU(s), one rank per GPU",
-           "step": "one federated round: broadcast, local training of all sampled clients, aggregation, test()"}
-    if extra:
-        cfg.update(extra)
-    return cfg
+def config_dict(n_gpus: int) -> dict:
+    """The workload definition - byte-identical in both arms (arm-specific remarks go to the top-level `notes`)."""
+    return {"model": "MnistCnn (LeNet-style, 1 199 882 params)", "algorithm": "FedAvg",
+            "nr_clients": NR_CLIENTS, "clients_per_round": CLIENTS_PER_GPU * n_gpus,
+            "client_fraction": round(CLIENTS_PER_GPU * n_gpus / NR_CLIENTS, 4), "local_epochs": EPOCHS,
+            "batch_size": BATCH, "lr": LR, "global_batch": CLIENTS_PER_GPU * n_gpus * BATCH, "seq_len": None,
+            "samples_per_round": CLIENTS_PER_GPU * n_gpus * SAMPLES_PER_CLIENT * EPOCHS, "test_samples_per_round": 10_000,
+            "aggregator": "mean",
+            "parallelism": f"clients packed {CLIENTS_PER_GPU}/GPU x {n_gpus} GPU(s), one rank per GPU",
+            "step": "one federated round: broadcast, local training of all sampled clients, aggregation, test()",
+            "l2": "product arm: L2 flushed (252 MB write) between timed rounds; reference arm: stock run(), rounds back to back"}
 
 
 # ----------------------------------------------------------------------------------------- reference arm
@@ -79,7 +95,6 @@ def run_reference_arm(args):
         print(json.dumps({"impl": "reference", "unavailable": why}))
         return
     rank, world, local = init_dist(args.gpus)
-    import torch
     import torch.distributed as dist
 
     out = None
@@ -88,13 +103,25 @@ def run_reference_arm(args):
         r = rr.run_reference(NR_CLIENTS, CLIENTS_PER_GPU * args.gpus / NR_CLIENTS, BATCH, EPOCHS, LR, SEED, args.warmup,
                              args.steps)
         ms = r["seconds"] * 1e3 / args.steps
-        out = {"impl": "reference", "metric": METRIC, "value": r["samples"] / r["seconds"], "unit": "samples/s",
+        k = CLIENTS_PER_GPU * args.gpus
+        # The stock run() IS end to end: every round it moves each sampled client's minibatches host -> device (float32 images +
+        # int64 labels from the CPU DataLoader), copies the global weights to the device once per client and every client's
+        # weights back (hfl_complete.py:323-325,332), moves the 10 000 test images and reads the accuracy.
+        h2d = k * SAMPLES_PER_CLIENT * EPOCHS * (784 * 4 + 8) + k * MODEL_BYTES + MODEL_BYTES + 10_000 * (784 * 4 + 8)
+        d2h = k * MODEL_BYTES + MODEL_BYTES + 8
+        val = r["samples"] / r["seconds"]
+        out = {"impl": "reference", "metric": METRIC, "value": val, "unit": "samples/s",
                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32 (cuDNN TF32 convs, torch default)",
                "data": "synthetic", "rounds_per_sec": 1e3 / ms, "final_test_accuracy": r["acc"],
-               "config": config_dict(args.gpus, {"reference_device": r["device"],
-                                                 "note": "stock FedAvgServer.run(); single process, uses one GPU whatever N is; "
-                                                         "wall-clock timed (the reference has no device timing)"})}
+               "e2e": {"value": val, "unit": "samples/s", "ms_per_step": ms, "h2d_bytes_per_step": int(h2d),
+                       "d2h_bytes_per_step": int(d2h),
+                       "api": "lab.tutorial_1a.hfl_complete.FedAvgServer(...).run(K): wall clock around the stock call, which "
+                              "includes its own per-batch host->device copies and per-client weight read-backs"},
+               "config": config_dict(args.gpus),
+               "notes": {"reference_device": r["device"],
+                         "scope": "stock FedAvgServer.run(); single process, uses one GPU whatever N is; wall-clock timed "
+                                  "(the reference has no device timing), so `value` and `e2e.value` are the same measurement"}}
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -103,11 +130,10 @@ def run_reference_arm(args):
 
 
 # ----------------------------------------------------------------------------------------- product arm
-def build_server(n_gpus: int, data_on_device: bool, aggregator: str, dataset, prefetch: bool = True):
+def build_server(n_gpus: int, data_on_device: bool, aggregator: str, dataset, collective, prefetch: bool = True):
     from ddl25spring_b200.core.data import split
     from ddl25spring_b200.fl.aggregators import make_aggregator
     from ddl25spring_b200.fl.packed_server import PackedFedAvgServer
-    from ddl25spring_b200.parallel.symm import make_collective
 
     subsets = split(dataset.train, NR_CLIENTS, True, SEED)
     kw = {}
@@ -115,12 +141,12 @@ def build_server(n_gpus: int, data_on_device: bool, aggregator: str, dataset, pr
         kw = dict(n_byzantine=max(1, int(0.2 * CLIENTS_PER_GPU * n_gpus)))
     return PackedFedAvgServer(LR, BATCH, subsets, CLIENTS_PER_GPU * n_gpus / NR_CLIENTS, EPOCHS, SEED,
                               test_set=dataset.test, device="cuda", aggregator=make_aggregator(aggregator, **kw),
-                              data_on_device=data_on_device, collective=make_collective(), prefetch_next=prefetch)
+                              data_on_device=data_on_device, collective=collective, prefetch_next=prefetch)
 
 
 def timed_rounds(server, steps: int, warmup: int, device, flusher, sampler=None):
     """W untimed rounds, then K rounds each bracketed by CUDA events (L2 flushed in between, outside the
-    events); returns (sum of device ms over the K rounds — max over ranks, accuracies)."""
+    events); returns (sum of device ms over the K rounds - max over ranks, accuracies)."""
     import torch
     from ddl25spring_b200.utils.timing import barrier_sync, max_over_ranks
 
@@ -143,6 +169,244 @@ def timed_rounds(server, steps: int, warmup: int, device, flusher, sampler=None)
     return max_over_ranks(total, device), accs
 
 
+def _peaks() -> dict:
+    try:
+        return json.load(open(os.path.join(REPO, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
+def _time_ms(fn, iters: int, warm: int, flusher) -> float:
+    """Median device time of fn over `iters` runs (L2 flushed before each), max over ranks."""
+    import torch
+    from ddl25spring_b200.utils.timing import max_over_ranks
+
+    for _ in range(warm):
+        fn()
+    ts = []
+    for _ in range(iters):
+        flusher.flush()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return max_over_ranks(sorted(ts)[len(ts) // 2], "cuda")
+
+
+# ---- config 2: data-parallel ResNet-18
+def section_dp(rank: int, world: int, steps: int, warmup: int, arena) -> dict:
+    import torch
+    import torch.distributed as dist
+    import torch.nn.functional as F
+
+    from ddl25spring_b200.models.resnet_nhwc import resnet18_nhwc
+    from ddl25spring_b200.parallel.dp import DataParallel
+    from ddl25spring_b200.utils.timing import max_over_ranks
+
+    batch = 256
+    g = torch.Generator().manual_seed(rank)
+    x = torch.randn(batch, 3, 32, 32, generator=g).cuda()
+    y = torch.randint(0, 10, (batch,), generator=g).cuda()
+
+    def loss_fn(m, xb, yb):
+        return F.cross_entropy(m(xb), yb)
+
+    out = {"model": "ResNet-18 (11 181 642 params), NHWC tcgen05 convolution stack", "per_gpu_batch": batch,
+           "global_batch": batch * world, "optimizer": "SGD lr 0.05", "steps": steps, "warmup": warmup,
+           "timing": "CUDA events around `steps` back-to-back train_step() calls, max over ranks; inputs resident in HBM",
+           "samples_per_s": {}, "ms_per_step": {}}
+
+    def run(step):
+        for _ in range(warmup):
+            step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        return max_over_ranks(e0.elapsed_time(e1) / steps, "cuda")
+
+    arms = ["graphed_step"] if world == 1 else ["fused_in_graph", "fused_nvls_in_graph", "nccl_graphed", "torch_ddp"]
+    n_red = RESNET_PARAMS + 8192
+    for arm in arms:
+        model = dp = ddp = opt = None
+        try:
+            torch.manual_seed(0)
+            model = resnet18_nhwc().cuda()
+            if arm == "torch_ddp":
+                ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[torch.cuda.current_device()])
+                opt = torch.optim.SGD(ddp.parameters(), lr=0.05)
+
+                def step():
+                    opt.zero_grad(set_to_none=True)
+                    loss_fn(ddp, x, y).backward()
+                    opt.step()
+            else:
+                reducer = None
+                if arm.startswith("fused"):
+                    from ddl25spring_b200.parallel.symm_impl import SymmetricGradReducer
+                    reducer = SymmetricGradReducer(arena, n_red, use_nvls="nvls" in arm, tag=arm)
+                dp = DataParallel(model, bucket_mb=8.0, optimizer="sgd", lr=0.05, reducer=reducer, graph=True)
+
+                def step():
+                    dp.train_step(loss_fn, x, y)
+            ms = run(step)
+            out["ms_per_step"][arm] = round(ms, 4)
+            out["samples_per_s"][arm] = round(batch * world / ms * 1e3, 1)
+            if arm.startswith("fused"):
+                arena.check()
+        except Exception as e:                      # one arm failing (e.g. no NVLS multicast) must not cost the others
+            out["ms_per_step"][arm] = None
+            out.setdefault("errors", {})[arm] = f"{type(e).__name__}: {e}"[:300]
+        finally:
+            model = dp = ddp = opt = None
+            torch.cuda.empty_cache()
+    if world > 1:
+        fused = [out["samples_per_s"].get(a) for a in ("fused_in_graph", "fused_nvls_in_graph") if out["samples_per_s"].get(a)]
+        if fused and out["samples_per_s"].get("nccl_graphed"):
+            out["fused_over_nccl"] = round(max(fused) / out["samples_per_s"]["nccl_graphed"], 3)
+    return out
+
+
+# ---- config 4: Byzantine-robust FedAvg of ResNet-18
+def section_robust(rank: int, world: int, flusher, coll_arena) -> dict:
+    import torch
+    import torch.distributed as dist
+    import torch.nn.functional as F
+
+    from ddl25spring_b200.core.data import SyntheticCIFAR, split
+    from ddl25spring_b200.fl.aggregators import make_aggregator
+    from ddl25spring_b200.fl.attacks import SignFlip, choose_malicious
+    from ddl25spring_b200.fl.server import FedAvgServer
+    from ddl25spring_b200.models.resnet_nhwc import resnet18_nhwc
+    from ddl25spring_b200.utils.timing import max_over_ranks
+
+    samples, batch, rounds = 256, 64, 3
+    K = CLIENTS_PER_GPU * world
+    ds = SyntheticCIFAR(n_train=K * samples, n_test=2000, seed=0)
+    subsets = split(ds.train, K, True, 1)
+    mal = choose_malicious(K, 0.2, 0)
+    f = int(mal.sum())
+    peaks = _peaks()
+    hbm = peaks.get("hbm_gbs", 6551.0) * 1e9
+    srv = FedAvgServer(0.05, batch, subsets, 1.0, 1, 10, model_fn=resnet18_nhwc, test_set=ds.test, device="cuda",
+                       loss_fn=F.cross_entropy, include_buffers=True, graph=True, attack=SignFlip(4.0), malicious=mal,
+                       test_batch_size=1000)
+    D = srv.arena.size
+    coll = None
+    if world > 1:
+        from ddl25spring_b200.parallel.symm_impl import SymmetricAggregator
+        coll = SymmetricAggregator(arena=coll_arena, max_rows_per_rank=CLIENTS_PER_GPU, row_elems=D, tag="robust")
+        srv.collective = coll
+    local_bytes = CLIENTS_PER_GPU * D * 4
+    link_bytes = (world - 1) / world * local_bytes
+    roof_ms = max(local_bytes / hbm, link_bytes / 900e9) * 1e3
+    out = {"model": "ResNet-18 (NHWC tcgen05 stack, BN statistics aggregated with the weights)", "clients_per_round": K,
+           "clients_per_gpu": CLIENTS_PER_GPU, "attackers": f, "attack": "sign-flip x4", "samples_per_client": samples,
+           "local_batch": batch, "rounds_timed": rounds, "row_floats": D,
+           "aggregation_roofline_ms": round(roof_ms, 4),
+           "roofline": "max(this GPU's 8 rows read once from HBM at the measured copy bandwidth, (W-1)/W of them over NVLink "
+                       "at 900 GB/s)",
+           "baseline": "same rule as NCCL all_gather of the rows + torch ops (mv / cdist+topk / median / sort), same process",
+           "results": {}}
+    mine_pos = [p for p in range(K) if p % world == rank]
+    w = torch.full((K,), 1.0 / K)
+    for name in ("mean", "krum", "median", "trimmed_mean"):
+        res_row = {}
+        try:
+            kw = dict(n_byzantine=f, multi=max(1, K - 2 * f)) if name == "krum" else {}
+            srv.aggregator = make_aggregator(name, **kw)
+            srv.run(1)                                               # warm-up round (graph capture on the first one)
+            res = srv.run(rounds)
+            ms = max_over_ranks(sum(res.device_time_ms) / rounds, "cuda")
+            res_row.update({"ms_per_round": round(ms, 3), "rounds_per_s": round(1e3 / ms, 3),
+                            "samples_per_s": round(K * samples / ms * 1e3, 1),
+                            "test_acc_last": round(res.test_accuracy[-1], 2)})
+            # aggregation latency alone, on the update rows of the last round
+            g = srv.arena.flat.detach().clone()
+            if world > 1:
+                U = coll.row_buffer(CLIENTS_PER_GPU)
+                agg_ms = _time_ms(lambda: coll.aggregate(srv.aggregator, U, mine_pos, w, g), 5, 2, flusher)
+                coll.arena.check()
+            else:
+                U = srv._updates
+                agg_ms = _time_ms(lambda: srv.aggregator(U, w, global_flat=g), 5, 2, flusher)
+            res_row["aggregation_ms"] = round(agg_ms, 4)
+            res_row["frac_of_roofline"] = round(roof_ms / agg_ms, 3)
+            # baseline: gather every row everywhere, then the torch statement of the rule
+            if world > 1:
+                allrows = torch.empty(world, CLIENTS_PER_GPU, D, device="cuda")
+                Uc = U.contiguous()
+
+                def gather():
+                    dist.all_gather_into_tensor(allrows.view(-1), Uc.view(-1))
+                    return allrows.view(K, D)
+            else:
+                def gather():
+                    return U
+            t = int(-(-0.2 * K // 1))
+
+            def base_fn():
+                A = gather()
+                if name == "mean":
+                    return A.mean(0)
+                if name == "median":
+                    return torch.median(A, dim=0).values
+                if name == "trimmed_mean":
+                    return torch.sort(A, dim=0).values[t:K - t].mean(0)
+                Ad = A - g[None, :]
+                dd = torch.cdist(Ad, Ad).pow(2)
+                dd.fill_diagonal_(float("inf"))
+                sc = torch.sort(dd, dim=1).values[:, :K - f - 2].sum(1)
+                return A[torch.argsort(sc)[:max(1, K - 2 * f)]].mean(0)
+            res_row["aggregation_ms_nccl_torch"] = round(_time_ms(base_fn, 2, 1, flusher), 4)
+            res_row["speedup_vs_nccl_torch"] = round(res_row["aggregation_ms_nccl_torch"] / agg_ms, 2)
+            allrows = None
+        except Exception as e:
+            res_row["error"] = f"{type(e).__name__}: {e}"[:300]
+        out["results"][name] = res_row
+        torch.cuda.empty_cache()
+    return out
+
+
+class Watchdog:
+    """If the extra sections overrun their wall-clock budget (a hung collective after one rank failed), rank 0 prints the
+    line with what has been measured and every rank leaves: the headline is never lost to an extra."""
+
+    def __init__(self, budget_s: float, rank: int, out: dict):
+        self.rank, self.out = rank, out
+        self.t = threading.Timer(budget_s, self.fire)
+        self.t.daemon = True
+        self.lock = threading.Lock()
+        self.printed = False
+
+    def fire(self):
+        with self.lock:
+            if self.printed:
+                return
+            self.printed = True
+            if self.rank == 0:
+                self.out.setdefault("extras_note", "extra sections stopped by the time budget; unfinished ones are absent")
+                print(json.dumps(self.out), flush=True)
+        time.sleep(1.0 if self.rank == 0 else 3.0)
+        os._exit(0)
+
+    def finish(self):
+        with self.lock:
+            self.t.cancel()
+            if self.printed:
+                return False
+            self.printed = True
+            return True
+
+
 def run_ours(args):
     rank, world, local = init_dist(args.gpus)
     import torch
@@ -153,6 +417,7 @@ def run_ours(args):
         return
     from ddl25spring_b200 import ops
     from ddl25spring_b200.core.data import SyntheticMNIST
+    from ddl25spring_b200.parallel.symm import make_collective
     from ddl25spring_b200.utils.clocks import ClockSampler
     from ddl25spring_b200.utils.timing import L2Flusher
 
@@ -160,9 +425,10 @@ def run_ours(args):
     n_gpus = world
     dataset = SyntheticMNIST(seed=0)
     flusher = L2Flusher(device)
+    collective = make_collective()                   # fused peer-memory aggregation (None on one GPU); raises if it cannot be set up
 
     # ---- kernel-side number: data resident in HBM
-    server = build_server(n_gpus, True, args.aggregator, dataset)
+    server = build_server(n_gpus, True, args.aggregator, dataset, collective)
     sampler = ClockSampler(local)
     for _ in range(args.warmup):
         server.run(1)
@@ -175,32 +441,58 @@ def run_ours(args):
     # ---- end-to-end number through the public API: shards in pinned host memory, copied H2D every round,
     #      accuracy read back D2H every round
     # (no cross-round prefetch here: every round's own H2D copy and D2H read are inside that round's timed region)
-    server = build_server(n_gpus, False, args.aggregator, dataset, prefetch=False)
+    server = build_server(n_gpus, False, args.aggregator, dataset, collective, prefetch=False)
     e2e_ms, _ = timed_rounds(server, args.steps, args.warmup, device, flusher)
     h2d = server.h2d_bytes_last_round
     del server
+    torch.cuda.empty_cache()
 
     samples_round = CLIENTS_PER_GPU * n_gpus * SAMPLES_PER_CLIENT * EPOCHS
     ms = ms_total / args.steps
     e2e = e2e_ms / args.steps
-    if rank == 0:
-        out = {"metric": METRIC, "value": samples_round / (ms / 1e3), "unit": "samples/s", "n_gpus": n_gpus,
-               "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-               "scaling": "weak", "vs_baseline": None, "dtype": "fp32 (TF32 tensor-core convs like the reference's cuDNN default; "
-                                                               "3xTF32 fp32-grade linears)",
-               "data": "synthetic", "rounds_per_sec": 1e3 / ms, "final_test_accuracy": accs[-1],
-               "clocks": sampler.summary(),
-               "e2e": {"value": samples_round / (e2e / 1e3), "unit": "samples/s", "ms_per_step": e2e,
-                       "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
-                       "api": "PackedFedAvgServer(...).run(1) with data_on_device=False"},
-               "gpu_launches": int(launches),
-               "config": config_dict(n_gpus, {"l2": "L2 flushed (252 MB write) between timed rounds",
-                                              "aggregator": args.aggregator,
-                                              "timing": "CUDA events per round on the launching stream, summed, max over ranks"})}
-        print(json.dumps(out))
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    cfg = config_dict(n_gpus)
+    cfg["aggregator"] = args.aggregator
+    out = {"metric": METRIC, "value": samples_round / (ms / 1e3), "unit": "samples/s", "n_gpus": n_gpus,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "fp32 (TF32 tensor-core convs like the reference's cuDNN default; "
+                                                           "3xTF32 fp32-grade linears)",
+           "data": "synthetic", "rounds_per_sec": 1e3 / ms, "final_test_accuracy": accs[-1],
+           "clocks": sampler.summary(),
+           "e2e": {"value": samples_round / (e2e / 1e3), "unit": "samples/s", "ms_per_step": e2e,
+                   "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
+                   "api": "PackedFedAvgServer(...).run(1) with data_on_device=False"},
+           "gpu_launches": int(launches),
+           "config": cfg,
+           "notes": {"timing": "CUDA events per round on the launching stream, summed, max over ranks",
+                     "collective": "fused peer-memory kernels (parallel/symm_impl.py)" if collective is not None else "single GPU"}}
+
+    sections = [s for s in args.sections.split(",") if s]
+    wd = Watchdog(args.extras_budget_s, rank, out)
+    if sections:
+        wd.t.start()
+    arena = collective.arena if collective is not None else None
+    for name in sections:
+        t0 = time.perf_counter()
+        try:
+            if name == "dp":
+                sec = section_dp(rank, world, max(10, args.steps), max(3, args.warmup), arena)
+            elif name == "robust":
+                sec = section_robust(rank, world, flusher, arena)
+            else:
+                sec = {"error": f"unknown section {name!r}"}
+        except Exception as e:
+            sec = {"error": f"{type(e).__name__}: {e}"[:400]}
+        sec["wall_s"] = round(time.perf_counter() - t0, 1)
+        out[name] = sec
+        torch.cuda.empty_cache()
+    if wd.finish():
+        if rank == 0:
+            print(json.dumps(out), flush=True)
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+    else:                                              # the watchdog already printed: just leave
+        time.sleep(5)
 
 
 if __name__ == "__main__":

@@ -148,20 +148,21 @@ class SymmetricAggregator:
     gathers the rows it needs with peer copies and scores locally)."""
 
     def __init__(self, arena: SymmetricArena | None = None, max_rows_per_rank: int = 16, row_elems: int = 1_200_000,
-                 use_nvls: bool = False):
+                 use_nvls: bool = False, tag: str = ""):
         self.arena = arena or SymmetricArena()
+        self.tag = tag                     # several aggregators may share one arena: buffer names carry the tag
         self.nvls = None
         if use_nvls:                       # in-switch reduction of the per-GPU partial sums (falls back when unsupported)
             from .nvls import NvlsAllReduce
             self.nvls = NvlsAllReduce.create(row_elems, self.arena)
         self.G, self.P = max_rows_per_rank, row_elems
-        self.rows = self.arena.alloc("client_rows", self.G * self.P * 4).view(self.G, self.P)
-        self.result = self.arena.alloc("agg_result", self.P * 4)       # every rank's replica of the aggregate; a server may use it
+        self.rows = self.arena.alloc("client_rows" + tag, self.G * self.P * 4).view(self.G, self.P)
+        self.result = self.arena.alloc("agg_result" + tag, self.P * 4)       # every rank's replica of the aggregate; a server may use it
                                                                           # directly as its global parameter arena (global_storage())
-        self.partial = self.arena.alloc("agg_partial", self.P * 4)
-        self.partial_ptrs = self.arena.peer_ptrs("agg_partial")
-        self.row_ptrs = self.arena.peer_ptrs("client_rows")
-        self.res_ptrs = self.arena.peer_ptrs("agg_result")
+        self.partial = self.arena.alloc("agg_partial" + tag, self.P * 4)
+        self.partial_ptrs = self.arena.peer_ptrs("agg_partial" + tag)
+        self.row_ptrs = self.arena.peer_ptrs("client_rows" + tag)
+        self.res_ptrs = self.arena.peer_ptrs("agg_result" + tag)
 
     def global_storage(self) -> torch.Tensor:
         """Symmetric buffer the fused kernels write the aggregate into on EVERY rank: a server that keeps its global model
@@ -219,13 +220,17 @@ class SymmetricAggregator:
             U = getattr(self, "_U", None)
             if U is None or U.shape != (K, shard + pad):
                 U = self._U = torch.zeros(K, shard + pad, device="cuda")
-                self._gpart = a.alloc(f"gram_part_{K}", K * K * 4).view(K, K)
-                self._gsum = a.alloc(f"gram_sum_{K}", K * K * 4).view(K, K)
-                self._gpart_ptrs, self._gsum_ptrs = a.peer_ptrs(f"gram_part_{K}"), a.peer_ptrs(f"gram_sum_{K}")
+            kb = getattr(self, "_gram_bufs", None)
+            if kb is None:
+                kb = self._gram_bufs = {}
+            if K not in kb:                                       # K x K partial / summed Gram buffers, one pair per round size
+                n1, n2 = f"gram_part_{K}{self.tag}", f"gram_sum_{K}{self.tag}"
+                kb[K] = (a.alloc(n1, K * K * 4).view(K, K), a.alloc(n2, K * K * 4).view(K, K), a.peer_ptrs(n1), a.peer_ptrs(n2))
+            self._gpart, self._gsum, self._gpart_ptrs, self._gsum_ptrs = kb[K]
             rows_per_rank = K // world
             if getattr(aggregator, "fused_gather", False) and K == rows_per_rank * world and rows_per_rank % 8 == 0:
                 # ONE kernel: every k-block of U is TMA-loaded from the owning GPUs and used as both MMA operands (3xTF32,
-                # because raw weights cannot be shifted to small-norm deltas in flight); result rows are rank-major.
+                # with the global model subtracted in shared memory: the Gram of the deltas); result rows are rank-major.
                 from ..ops.gemm import gram_rowgather_ptrs
                 g0, g1 = shard_bounds(self.P, world, a.rank, align=32)
                 a.barrier()
@@ -259,36 +264,149 @@ class _DevView:
         self.tensor = torch.as_tensor(self, device="cuda")
 
 
-class SymmetricGradReducer:
-    """``reducer`` for :class:`parallel.dp.DataParallel`: in-place sum of a gradient bucket over all ranks by
-    the fused peer-memory kernel, launched on a side stream so it overlaps the rest of backward."""
+class _Work:
+    def __init__(self, ev):
+        self.ev = ev
 
-    def __init__(self, arena: SymmetricArena, n_elems: int, max_ctas: int = 32):
+    def wait(self):
+        torch.cuda.current_stream().wait_event(self.ev)
+
+
+class SymmetricGradReducer:
+    """``reducer`` for :class:`parallel.dp.DataParallel` (K2): the bucketed gradient all-reduce as ONE fused peer-memory
+    kernel per bucket, on a side stream and its own channel so it runs under the rest of backward.
+
+    ``fuse_optimizer=True`` (default) makes that kernel the whole tail of the training step for its bucket: every rank sums
+    ITS coordinate shard of the bucket over all ranks (reduce-scatter), applies 1/W and the optimizer update to that shard
+    of the parameters - momentum / Adam moments exist only for the owned shard (ZeRO-1) - and stores the NEW PARAMETERS into
+    every rank's replica (all-gather).  Gradients and parameters therefore both live in symmetric memory.  The launches
+    carry no per-step host state, so DataParallel(graph=True) records them as side branches of the step graph.
+
+    ``use_nvls=True`` puts both arenas behind NVLS multicast addresses (torch symmetric memory does the binding): the W
+    peer loads become one ``multimem.ld_reduce`` (the switch adds) and the W peer stores one ``multimem.st``.
+
+    Replaces lab/tutorial_1b/DP/gradient_aggr/intro_DP_GA.py:53-67 (barrier, flatten, CPU copy, gloo all-reduce, copy back,
+    divide, Adam step - strictly one after the other)."""
+
+    capturable = True
+
+    def __init__(self, arena: SymmetricArena, n_elems: int, max_ctas: int = 32, fuse_optimizer: bool = True,
+                 use_nvls: bool = False, tag: str = ""):
         self.arena = arena
-        self.grad = arena.alloc("dp_grad", n_elems * 4)
-        self.ptrs = arena.peer_ptrs("dp_grad")
+        n = (n_elems + 127) // 128 * 128
+        self.n = n
+        self.mc_grad = self.mc_param = 0
+        self.param = None
+        if use_nvls:
+            import torch.distributed._symmetric_memory as symm_mem
+            grp = arena.group or dist.group.WORLD
+            dev = torch.device("cuda", torch.cuda.current_device())
+            bufs = []
+            for _ in range(2 if fuse_optimizer else 1):
+                b = symm_mem.empty(n, dtype=torch.float32, device=dev)
+                h = symm_mem.rendezvous(b, grp.group_name)
+                if not int(getattr(h, "multicast_ptr", 0)):
+                    raise RuntimeError("NVLS multicast is not available for this group")
+                b.zero_()
+                bufs.append((b, h))
+            self._nvls_keep = bufs
+            self.grad, self.mc_grad = bufs[0][0], int(bufs[0][1].multicast_ptr)
+            self.ptrs = None
+            if fuse_optimizer:
+                self.param, self.mc_param = bufs[1][0], int(bufs[1][1].multicast_ptr)
+            self.param_ptrs = None
+        else:
+            self.grad = arena.alloc("dp_grad" + tag, n * 4)
+            self.ptrs = arena.peer_ptrs("dp_grad" + tag)
+            if fuse_optimizer:
+                self.param = arena.alloc("dp_param" + tag, n * 4)
+                self.param_ptrs = arena.peer_ptrs("dp_param" + tag)
+        self.fuses_optimizer = fuse_optimizer
+        self.channel = arena.new_channel()
         self.stream = torch.cuda.Stream()
         self.max_ctas = max_ctas
+        self.step_dev = torch.zeros(1, dtype=torch.int32, device="cuda")       # completed optimizer steps (Adam bias correction)
+        self._opt = None
+        self._state: dict[tuple[int, int], tuple] = {}
+        arena.barrier()
 
-    class _Work:
-        def __init__(self, ev):
-            self.ev = ev
+    # ---- optimizer epilogue
+    def configure(self, optimizer: str, lr: float, weight_decay: float = 0.0, betas=(0.9, 0.999), eps: float = 1e-8,
+                  momentum: float = 0.0) -> None:
+        kind = {"sgd": 1, "adam": 2, "adamw": 3}[optimizer]
+        self._opt = dict(kind=kind, lr=lr, weight_decay=weight_decay, momentum=momentum, beta1=betas[0], beta2=betas[1], eps=eps)
 
-        def wait(self):
-            torch.cuda.current_stream().wait_event(self.ev)
+    def prepare(self, lo: int, hi: int) -> None:
+        """Allocate the optimizer moments of the OWNED shard of bucket [lo, hi) (call before any graph capture)."""
+        o = self._opt
+        if (lo, hi) in self._state:
+            return
+        s0, s1 = shard_bounds(hi - lo, self.arena.world, self.arena.rank)
+        need_m = o["kind"] >= 2 or o["momentum"] != 0.0
+        m = torch.zeros(max(s1 - s0, 4), device="cuda") if need_m else None
+        v = torch.zeros(max(s1 - s0, 4), device="cuda") if o["kind"] >= 2 else None
+        self._state[(lo, hi)] = (m, v)
 
+    def _opt_args(self, lo: int, hi: int, s0: int, s1: int) -> OptArgs:
+        o = self._opt
+        self.prepare(lo, hi)
+        m, v = self._state[(lo, hi)]
+        return OptArgs(kind=o["kind"], lr=o["lr"], weight_decay=o["weight_decay"], momentum=o["momentum"], beta1=o["beta1"],
+                       beta2=o["beta2"], eps=o["eps"], m=None if m is None else m.data_ptr(), v=None if v is None else v.data_ptr(),
+                       state_off4=(lo + s0) // 4, step_dev=self.step_dev.data_ptr(), bump_step=0)
+
+    def reset_state(self) -> None:
+        for m, v in self._state.values():
+            if m is not None:
+                m.zero_()
+            if v is not None:
+                v.zero_()
+        self.step_dev.zero_()
+
+    def end_of_step(self) -> None:
+        """Called once per optimizer step after the last bucket (on the reducer's stream): advance the step counter."""
+        if self.fuses_optimizer and self._opt is not None and self._opt["kind"] >= 2:
+            with torch.cuda.stream(self.stream):
+                self.step_dev.add_(1)
+
+    # ---- reducer protocol
     def __call__(self, view: torch.Tensor, lo: int, hi: int):
         a = self.arena
         ready = torch.cuda.Event()
         ready.record()
-        n = hi - lo
-        s0, s1 = shard_bounds(n, a.world, a.rank)
+        s0, s1 = shard_bounds(hi - lo, a.world, a.rank)
+        fused = self.fuses_optimizer and self._opt is not None
         with torch.cuda.stream(self.stream):
             self.stream.wait_event(ready)
-            a.reduce(0, self.ptrs, [1.0] * a.world, self.ptrs, lo + s0, lo + s1, max_ctas=self.max_ctas)
+            if fused:
+                a.reduce(0, self.ptrs, [1.0] * a.world, self.param_ptrs, lo + s0, lo + s1, base=self.param, beta=1.0 / a.world,
+                         max_ctas=self.max_ctas, channel=self.channel, opt=self._opt_args(lo, hi, s0, s1),
+                         mc_in=self.mc_grad, mc_out=self.mc_param)
+                view.zero_()          # every peer has read this bucket (exit barrier): ready for the next backward
+            else:
+                a.reduce(0, self.ptrs, [1.0] * a.world, self.ptrs, lo + s0, lo + s1, max_ctas=self.max_ctas, channel=self.channel,
+                         mc_in=self.mc_grad, mc_out=self.mc_grad)
             done = torch.cuda.Event()
             done.record()
-        return self._Work(done)
+        return _Work(done)
+
+
+class SymmetricWeightAverager:
+    """K2b: in-place average of the replicas' parameters by the fused peer-memory kernel (each rank averages its coordinate
+    shard over all replicas and stores it back into all of them).  The intended semantics of
+    lab/tutorial_1b/DP/weight_aggr/intro_DP_WA.py:54-67, whose own write-back is a no-op (:67)."""
+
+    def __init__(self, arena: SymmetricArena, n_elems: int, max_ctas: int = 0, tag: str = ""):
+        self.arena = arena
+        self.n = (n_elems + 127) // 128 * 128
+        self.param = arena.alloc("wa_param" + tag, self.n * 4)
+        self.ptrs = arena.peer_ptrs("wa_param" + tag)
+        self.max_ctas = max_ctas
+
+    def average_(self) -> None:
+        a = self.arena
+        s0, s1 = shard_bounds(self.n, a.world, a.rank)
+        a.reduce(0, self.ptrs, [1.0 / a.world] * a.world, self.ptrs, s0, s1, max_ctas=self.max_ctas)
 
 
 class FusedVFLGather:

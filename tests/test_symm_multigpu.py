@@ -67,34 +67,119 @@ def test_symm_reduce_matches_oracle():
     print("fused vs nccl ms:", outs[0]["fused_ms"], outs[0]["nccl_ms"])
 
 
-def _dp_worker(rank, world):
+def _dp_worker(rank, world, optimizer, graph, nvls):
+    """DataParallel with the fused peer-memory reducer (reduce-scatter + optimizer on the owned shard + all-gather of the new
+    parameters in one kernel per bucket; with graph=True captured as branches of the step graph) against the NCCL all-reduce +
+    whole-arena optimizer kernel."""
+    import copy
     import torch.nn.functional as F
     from ddl25spring_b200.parallel.dp import DataParallel
     from ddl25spring_b200.parallel.symm_impl import SymmetricArena, SymmetricGradReducer
     torch.manual_seed(0)
     m = torch.nn.Sequential(torch.nn.Linear(64, 512), torch.nn.ReLU(), torch.nn.Linear(512, 512), torch.nn.ReLU(),
                             torch.nn.Linear(512, 10)).cuda()
-    import copy
     m2 = copy.deepcopy(m)
     arena = SymmetricArena()
     n = sum(p.numel() for p in m.parameters()) + 1024
-    dp = DataParallel(m, bucket_mb=0.25, optimizer="sgd", lr=0.05, reducer=SymmetricGradReducer(arena, n))
-    ref = DataParallel(m2, bucket_mb=0.25, optimizer="sgd", lr=0.05)          # NCCL all_reduce path
+    try:
+        red = SymmetricGradReducer(arena, n, use_nvls=nvls)
+    except Exception as e:
+        if nvls:
+            return ("unsupported", repr(e))
+        raise
+    kw = dict(bucket_mb=0.25, optimizer=optimizer, lr=0.05 if optimizer == "sgd" else 1e-3, weight_decay=0.01,
+              momentum=0.9 if optimizer == "sgd" else 0.0)
+    dp = DataParallel(m, reducer=red, graph=graph, **kw)
+    ref = DataParallel(m2, **kw)                                              # NCCL all_reduce path
+    assert dp.fused_step and not ref.fused_step
     g = torch.Generator().manual_seed(rank)
     x, y = torch.randn(32, 64, generator=g).cuda(), torch.randint(0, 10, (32,), generator=g).cuda()
-    for _ in range(3):
-        dp.train_step(lambda mod, a, b: F.cross_entropy(mod(a), b), x, y)
-        ref.train_step(lambda mod, a, b: F.cross_entropy(mod(a), b), x, y)
+    lf = lambda mod, a, b: F.cross_entropy(mod(a), b)
+    l1 = [float(dp.train_step(lf, x, y)) for _ in range(5)]
+    l2 = [float(ref.train_step(lf, x, y)) for _ in range(5)]
     torch.cuda.synchronize(); arena.check()
-    return float((dp.arena.flat - ref.arena.flat).abs().max()), len(dp.buckets)
+    werr = float((dp.arena.flat - ref.arena.flat).abs().max())
+    gleft = float(dp.arena.grad.abs().max())                                 # the fused kernels re-zero the gradient arena
+    return ("ok", werr, len(dp.buckets), max(abs(a - b) for a, b in zip(l1, l2)), gleft)
+
+
+@pytest.mark.timeout(400)
+@pytest.mark.parametrize("optimizer,graph,nvls", [("sgd", False, False), ("adam", False, False), ("adamw", True, False),
+                                                  ("sgd", True, False), ("sgd", True, True)])
+def test_dp_with_fused_reducer_matches_nccl(optimizer, graph, nvls):
+    world = min(torch.cuda.device_count(), 8)
+    outs = run_distributed(_dp_worker, world, (optimizer, graph, nvls), timeout=300, backend="nccl")
+    if outs[0][0] == "unsupported":
+        pytest.skip("NVLS multicast not available: " + outs[0][1])
+    for _, err, nb, lerr, gleft in outs:
+        assert err < 2e-5 and nb > 1 and lerr < 1e-4 and gleft == 0.0, (err, nb, lerr, gleft)
+    assert len({o[1] for o in outs}) >= 1
+
+
+def _wa_worker(rank, world):
+    import copy
+    import torch.nn.functional as F
+    from ddl25spring_b200.parallel.dp import WeightAveraging
+    from ddl25spring_b200.parallel.symm_impl import SymmetricArena, SymmetricWeightAverager
+    torch.manual_seed(0)
+    m = torch.nn.Sequential(torch.nn.Linear(32, 256), torch.nn.ReLU(), torch.nn.Linear(256, 10)).cuda()
+    m2 = copy.deepcopy(m)
+    arena = SymmetricArena()
+    n = sum(p.numel() for p in m.parameters()) + 512
+    wa = WeightAveraging(m, lr=0.05, averager=SymmetricWeightAverager(arena, n))
+    ref = WeightAveraging(m2, lr=0.05)
+    g = torch.Generator().manual_seed(rank)
+    x, y = torch.randn(16, 32, generator=g).cuda(), torch.randint(0, 10, (16,), generator=g).cuda()
+    for _ in range(3):
+        for w in (wa, ref):
+            F.cross_entropy(w.module(x), y).backward()
+            w.step()
+    torch.cuda.synchronize(); arena.check()
+    return float((wa.arena.flat - ref.arena.flat).abs().max()), wa.arena.flat.clone().cpu()
 
 
 @pytest.mark.timeout(300)
-def test_dp_with_fused_reducer_matches_nccl():
+def test_weight_averaging_fused_matches_nccl():
     world = min(torch.cuda.device_count(), 8)
-    outs = run_distributed(_dp_worker, world, timeout=240, backend="nccl")
-    for err, nb in outs:
-        assert err < 1e-5 and nb > 1, (err, nb)
+    outs = run_distributed(_wa_worker, world, timeout=240, backend="nccl")
+    for err, _ in outs:
+        assert err < 1e-6, err
+    torch.testing.assert_close(outs[0][1], outs[-1][1], rtol=0, atol=0)       # replicas identical after averaging
+
+
+def _timeout_worker(rank, world):
+    """A rank that never launches its kernel: the others must time out, raise, and publish nothing."""
+    from ddl25spring_b200.parallel.symm_impl import SymmetricArena, shard_bounds
+    a = SymmetricArena()
+    n = 4096
+    rows = a.alloc("rows", n * 4)
+    res = a.alloc("res", n * 4)
+    rows.fill_(1.0 + rank)
+    res.fill_(-7.0)
+    torch.cuda.synchronize()
+    import torch.distributed as dist
+    dist.barrier()
+    raised = False
+    if rank != 0:                                   # rank 0 "crashed": it never joins the collective
+        d0, d1 = shard_bounds(n, world, rank)
+        a.reduce(0, a.peer_ptrs("rows"), [1.0] * world, a.peer_ptrs("res"), d0, d1)
+        torch.cuda.synchronize()
+        try:
+            a.check()
+        except RuntimeError:
+            raised = True
+    dist.barrier()
+    torch.cuda.synchronize()
+    return raised, float(res.min()), float(res.max())
+
+
+@pytest.mark.timeout(300)
+def test_missing_peer_times_out_loudly_and_publishes_nothing():
+    world = min(torch.cuda.device_count(), 8)
+    outs = run_distributed(_timeout_worker, world, timeout=240, backend="nccl")
+    assert all(o[0] for o in outs[1:]) and not outs[0][0]
+    for _, lo, hi in outs:
+        assert lo == -7.0 and hi == -7.0          # nobody's result buffer was touched
 
 
 def _fedavg_worker(rank, world, agg_name):
