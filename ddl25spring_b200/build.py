@@ -52,6 +52,12 @@ def build(verbose: bool = False, force: bool = False) -> Path:
     if force:
         for o in OBJDIR.glob("*.o"):
             o.unlink()
+    stems = {s.stem for s in srcs}
+    stale = [o for o in OBJDIR.glob("*.o") if o.stem not in stems]      # objects of sources that were removed / moved out
+    for o in stale:
+        o.unlink()
+    if stale and LIB.exists():
+        LIB.unlink()
     hdr_mtime = _deps_mtime()
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
         objs = list(ex.map(lambda s: _compile(s, hdr_mtime, verbose), srcs))

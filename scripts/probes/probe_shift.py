@@ -1,10 +1,21 @@
-"""Run the descriptor row-shift probe (csrc/dbg_probe.cu) and print which base_offset rule works."""
-import sys, os
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+"""Run the descriptor row-shift probe (scripts/probes/dbg_probe.cu) and print which base_offset rule works.
+
+The probe kernels are NOT part of libddl25_kernels.so: this script compiles them into their own shared object next to
+itself (linking the product library for the tensor-map encoder and error plumbing) and loads that."""
+import ctypes, os, subprocess, sys
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
 import torch
+from ddl25spring_b200 import build as _build
 from ddl25spring_b200.ops import _lib
 
-L = _lib.lib()
+_lib.lib()                                             # product library first (RTLD_GLOBAL symbols the probe links against)
+SO = os.path.join(HERE, "libddl25_probes.so")
+if not os.path.exists(SO) or os.path.getmtime(SO) < os.path.getmtime(os.path.join(HERE, "dbg_probe.cu")):
+    subprocess.run([_build.NVCC, *_build.ARCH_FLAGS, *_build.CFLAGS, "-shared", os.path.join(HERE, "dbg_probe.cu"), "-o", SO,
+                    "-L", str(_build.LIBDIR), "-lddl25_kernels", f"-Xlinker=-rpath={_build.LIBDIR}", "-cudart", "static"], check=True)
+L = ctypes.CDLL(SO)
 torch.manual_seed(0)
 A = torch.randn(256, 32, device="cuda")
 B = torch.randn(64, 32, device="cuda")
