@@ -29,7 +29,8 @@ from ..models.mnist_cnn import MnistCnn
 from .aggregators import Aggregator, WeightedMean
 from .client import materialize_client_data
 from .packed import MAX_G, P, PackedMnistEngine
-from .server import _RoundTimer, _dist_ready
+from ..utils.trace import span
+from .server import Server, _RoundTimer, _dist_ready
 
 
 class _NullCtx:
@@ -241,12 +242,19 @@ class PackedFedAvgServer:
             agg = self.aggregator(U, weights, out=self._agg_out, global_flat=gflat.detach())
             gflat.copy_(agg)
 
-    def run(self, nr_rounds: int) -> RunResult:
+    def run(self, nr_rounds: int, *, checkpointer=None, logger=None) -> RunResult:
+        """Rounds up to index ``nr_rounds``; ``checkpointer`` / ``logger`` as in :meth:`fl.server.Server.run` (a saved state
+        is resumed: the sampling RNG is stored as it was BEFORE the next round's prefetch draw)."""
         res = RunResult(self.algorithm, self.nr_clients, self.client_fraction, self.batch_size, self.nr_local_epochs,
                         self.lr, self.seed)
+        start = 0
+        if checkpointer is not None and checkpointer.exists():
+            start, saved = checkpointer.resume(self.arena, self.rng)
+            res = saved if saved is not None else res
+            self._prefetch = None                               # staged data of the interrupted run is gone
         timer = _RoundTimer(self.device)
-        elapsed = 0.0
-        for nr_round in range(nr_rounds):
+        elapsed = res.wall_time[-1] if res.wall_time else 0.0
+        for nr_round in range(start, nr_rounds):
             t0 = perf_counter()
             timer.start()
             if self._prefetch is not None:
@@ -261,10 +269,12 @@ class PackedFedAvgServer:
             W_local = None
             assert len(mine) <= MAX_G, "more than MAX_G clients per GPU per round: raise MAX_G or add ranks"
             if mine:
-                W_local = self._train_local_clients(nr_round, mine, staged)
+                with span("clients/packed_local_train"):
+                    W_local = self._train_local_clients(nr_round, mine, staged)
             # While the GPU trains: draw the NEXT round's clients (same rng order as drawing them later) and stage their
             # shards + permutations into the other staging set.  The next round is nr_round + 1 of this run(), or round 0
             # of a following run() call; a wrong guess only costs a re-stage.
+            rng_state = self.rng.bit_generator.state            # what a resumed run must start from
             if self.prefetch_next:
                 nxt_round = nr_round + 1 if nr_round + 1 < nr_rounds else 0
                 nxt = self.rng.choice(self.nr_clients, self.nr_clients_per_round, replace=False)
@@ -276,9 +286,10 @@ class PackedFedAvgServer:
                 self._prefetch = (nxt, st)
             if W_local is None:
                 W_local = torch.empty(0, P, device=self.device)
-            with torch.no_grad():
+            with torch.no_grad(), span("server/aggregate"):
                 self._aggregate(W_local, mine_pos, weights)
-            acc = self.test()
+            with span("server/test"):
+                acc = self.test()
             res.device_time_ms.append(timer.stop_ms())
             if self.collective is not None and self.world > 1:
                 self.collective.arena.check()          # the host is synchronised here anyway: a peer time-out raises instead of
@@ -288,4 +299,7 @@ class PackedFedAvgServer:
             res.message_count.append(message_count(nr_round, self.nr_clients_per_round))
             res.samples.append(int(counts.sum()) * self.nr_local_epochs)
             res.test_accuracy.append(acc)
+            Server._log_round(logger, res, nr_round)
+            if checkpointer is not None and self.rank == 0:
+                checkpointer.maybe_save(nr_round, self.arena, rng_state, res)
         return res

@@ -38,6 +38,7 @@ from .. import ops
 from ..core.results import RunResult, message_count
 from ..core.seeds import client_round_seed, clients_per_round
 from ..models.mnist_cnn import MnistCnn
+from ..utils.trace import span
 from .aggregators import Aggregator, WeightedMean
 from .attacks import Attack
 from .client import (Client, GradientClient, ModelSlot, WeightClient, default_device, materialize_client_data,
@@ -98,8 +99,22 @@ class Server(ABC):
         self._test_xy = (x.to(self.device), y.to(self.device))
 
     @abstractmethod
-    def run(self, nr_rounds: int) -> RunResult:
-        ...
+    def run(self, nr_rounds: int, *, checkpointer=None, logger=None) -> RunResult:
+        """Run rounds up to index ``nr_rounds``.  ``checkpointer`` (core.checkpoint.RoundCheckpointer): state is saved after
+        every ``checkpointer.every`` rounds and, if a saved state exists, the run CONTINUES from it (same RunResult and
+        weights as an uninterrupted run).  ``logger`` (utils.trace.JsonlLogger): one record per round."""
+
+    def _resume(self, checkpointer, rng, res: RunResult) -> tuple[int, RunResult]:
+        if checkpointer is None or not checkpointer.exists():
+            return 0, res
+        start, saved = checkpointer.resume(self.arena, rng)
+        return start, (saved if saved is not None else res)
+
+    @staticmethod
+    def _log_round(logger, res: RunResult, nr_round: int) -> None:
+        if logger is not None:
+            logger.log(event="round", algorithm=res.algorithm, round=nr_round + 1, test_accuracy=res.test_accuracy[-1],
+                       device_ms=res.device_time_ms[-1], samples=res.samples[-1], messages=res.message_count[-1])
 
     @torch.no_grad()
     def test(self) -> float:
@@ -142,21 +157,28 @@ class CentralizedServer(Server):
                                     slot=self.slot, loss_fn=self.loss_fn)
         self.clients = []
 
-    def run(self, nr_rounds: int) -> RunResult:
-        elapsed = 0.0
+    def run(self, nr_rounds: int, *, checkpointer=None, logger=None) -> RunResult:
         res = RunResult("Centralized", 1, 1, self.batch_size, 1, self.lr, self.seed)
+        rng = npr.default_rng(self.seed)                       # unused by the epochs; kept so checkpoints have one format
+        start, res = self._resume(checkpointer, rng, res)
+        elapsed = res.wall_time[-1] if res.wall_time else 0.0
         timer = _RoundTimer(self.device)
-        for epoch in range(nr_rounds):
+        for epoch in range(start, nr_rounds):
             t0 = perf_counter()
             timer.start()
             # same reseeding rule as the reference: generator.manual_seed(seed + epoch + 1)
-            self.trainer.update_flat(self.slot.flat.detach().clone(), self.seed + epoch + 1, out=None)
+            with span("centralized/epoch"):
+                self.trainer.update_flat(self.slot.flat.detach().clone(), self.seed + epoch + 1, out=None)
             res.device_time_ms.append(timer.stop_ms())
             elapsed += perf_counter() - t0
             res.wall_time.append(round(elapsed, 1))
             res.message_count.append(0)
             res.samples.append(self.trainer.n)
-            res.test_accuracy.append(self.test())
+            with span("server/test"):
+                res.test_accuracy.append(self.test())
+            self._log_round(logger, res, epoch)
+            if checkpointer is not None:
+                checkpointer.maybe_save(epoch, self.arena, rng, res)
         return res
 
 
@@ -235,12 +257,13 @@ class DecentralizedServer(Server):
         return sum(self.client_sample_counts[int(i)] for i in chosen) * getattr(self, "nr_local_epochs", 1)
 
     # ------------------------------------------------------------------ the round loop
-    def run(self, nr_rounds: int) -> RunResult:
-        elapsed = 0.0
+    def run(self, nr_rounds: int, *, checkpointer=None, logger=None) -> RunResult:
         res = self._result()
+        start, res = self._resume(checkpointer, self.rng, res)
+        elapsed = res.wall_time[-1] if res.wall_time else 0.0
         timer = _RoundTimer(self.device)
         agg_out = torch.empty(self.arena.size, device=self.device)
-        for nr_round in range(nr_rounds):
+        for nr_round in range(start, nr_rounds):
             t_setup = perf_counter()
             timer.start()
             self.model.train()
@@ -248,10 +271,11 @@ class DecentralizedServer(Server):
             chosen = self.rng.choice(self.nr_clients, self.nr_clients_per_round, replace=False)
             weights = self._round_weights(chosen)
             elapsed += perf_counter() - t_setup
-            U, slowest = self._collect_updates(nr_round, chosen, gflat)
+            with span("clients/local_update"):
+                U, slowest = self._collect_updates(nr_round, chosen, gflat)
             elapsed += slowest
             t_agg = perf_counter()
-            with torch.no_grad():
+            with torch.no_grad(), span("server/aggregate"):
                 if self.collective is not None and self.world > 1:
                     mine_pos = [p for p in range(len(chosen)) if p % self.world == self.rank]
                     # gradient messages are aggregated around 0, weight messages around the current global model (Krum scores
@@ -271,9 +295,13 @@ class DecentralizedServer(Server):
             res.wall_time.append(round(elapsed, 1))
             res.message_count.append(message_count(nr_round, self.nr_clients_per_round))
             res.samples.append(self.samples_per_round(chosen))
-            res.test_accuracy.append(self.test())
+            with span("server/test"):
+                res.test_accuracy.append(self.test())
             if self.collective is not None and self.world > 1:
                 self.collective.arena.check()      # test() synchronised the host: raise on a peer time-out instead of going on
+            self._log_round(logger, res, nr_round)
+            if checkpointer is not None and self.rank == 0:
+                checkpointer.maybe_save(nr_round, self.arena, self.rng, res)
         return res
 
 

@@ -141,3 +141,35 @@ def test_centralized_runs(mnist):
     srv = CentralizedServer(0.05, 100, 10, train_set=mnist.train, test_set=mnist.test, device="cpu")
     res = srv.run(2)
     assert res.message_count == [0, 0] and res.test_accuracy[-1] > 30
+
+
+def test_killed_run_resumes_to_the_same_result(mnist, tmp_path):
+    """Round-level checkpoint / resume: a run interrupted after round 2 and continued by a NEW server object
+    from the checkpoint file gives the same RunResult and the same final weights as the uninterrupted run - with dropout
+    on, so torch's RNG state has to be part of the checkpoint, and with a JSONL logger attached."""
+    import json
+
+    from ddl25spring_b200.core.checkpoint import RoundCheckpointer
+    from ddl25spring_b200.utils.trace import JsonlLogger, TRACER
+
+    subsets = split(mnist.train, 8, True, 10)
+
+    def make():
+        return FedAvgServer(0.05, 50, subsets, 0.5, 1, 10, test_set=mnist.test, device="cpu")
+
+    full = make()
+    ref = full.run(4)
+    ck = RoundCheckpointer(str(tmp_path / "ck"), every=1)
+    log = str(tmp_path / "rounds.jsonl")
+    first = make()
+    part = first.run(2, checkpointer=ck, logger=JsonlLogger(log, rank=0))        # "killed" after round 2
+    assert part.test_accuracy == ref.test_accuracy[:2]
+    del first
+    second = make()                                                             # fresh process state: new model, new RNGs
+    res = second.run(4, checkpointer=ck, logger=JsonlLogger(log, rank=0))
+    assert res.test_accuracy == ref.test_accuracy and res.message_count == ref.message_count
+    assert torch.equal(second.arena.flat, full.arena.flat)
+    recs = [json.loads(l) for l in open(log)]
+    assert [r["round"] for r in recs] == [1, 2, 3, 4] and recs[-1]["test_accuracy"] == ref.test_accuracy[-1]
+    rep = TRACER.report()
+    assert rep["server/aggregate"]["calls"] >= 4 and rep["clients/local_update"]["calls"] >= 4

@@ -137,3 +137,28 @@ def test_u8_transport_is_bit_identical_to_resident_floats():
             assert srv.h2d_bytes_last_round == 4 * 200 * 784 + 4 * 200 * 8 + 4 * 200 * 4      # u8 pixels + int64 labels + int32 perms
         flats.append(srv.arena.flat.detach().clone())
     assert torch.equal(flats[0], flats[1])
+
+
+def test_packed_server_resumes_from_checkpoint(cuda_lib, tmp_path):
+    """PackedFedAvgServer.run(checkpointer=...): a run stopped after 2 rounds and continued by a new server object equals
+    the uninterrupted 4-round run bit for bit (the sampling RNG is saved as it was before the next round's prefetch draw)."""
+    from ddl25spring_b200.core.checkpoint import RoundCheckpointer
+    from ddl25spring_b200.core.data import SyntheticMNIST, split
+    from ddl25spring_b200.fl.packed_server import PackedFedAvgServer
+    ds = SyntheticMNIST(n_train=2000, n_test=500, seed=4, noise=0.8)
+    subsets = split(ds.train, 10, True, 3)
+
+    def make():
+        return PackedFedAvgServer(0.05, 50, subsets, 0.4, 1, 7, test_set=ds.test, device="cuda")
+
+    full = make()
+    ref = full.run(4)
+    ck = RoundCheckpointer(str(tmp_path), every=1)
+    a = make()
+    a.run(2, checkpointer=ck)
+    del a
+    b = make()
+    res = b.run(4, checkpointer=ck)
+    torch.cuda.synchronize()
+    assert res.test_accuracy == ref.test_accuracy
+    assert torch.equal(b.arena.flat, full.arena.flat)
