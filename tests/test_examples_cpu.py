@@ -17,6 +17,37 @@ def test_hfl_experiment_driver():
     assert len(res.test_accuracy) == 2 and res.message_count == [6, 12]
 
 
+def test_hfl_sweep_writes_one_frame_and_plots(tmp_path):
+    """The homework-1 grid (N x C x E, IID vs non-IID; lab/homework-1.ipynb cells 24-36) in its --quick form: one DataFrame,
+    one SVG line plot per sweep."""
+    sys.path.insert(0, os.path.join(ROOT, "examples"))
+    import hfl_experiments
+    df = hfl_experiments.main(["--sweep", "--quick", "--nr_rounds", "2", "--out", str(tmp_path)], n_train=480, n_test=120)
+    assert set(df["Sweep"]) == {"N", "C", "E", "iid"} and set(df["Algorithm"]) == {"FedSGDGradient", "FedAvg"}
+    assert len(df) == 2 * (4 + 4 + 2 + 4)
+    assert os.path.exists(tmp_path / "sweep.csv")
+    for name in ("N", "C", "E", "iid"):
+        svg = open(tmp_path / f"sweep_{name}.svg").read()
+        assert svg.startswith("<svg") and svg.count("<polyline") >= 2
+
+
+def test_package_launcher_spawns_ranks(tmp_path):
+    """utils.launch.spawn: the in-notebook multi-rank launcher (intro_DP_GA_notebook.ipynb cell 1) with per-rank stdout files."""
+    from ddl25spring_b200.utils.launch import spawn
+    outs = spawn(_rank_job, 2, (3,), timeout=120, backend="gloo", log_dir=str(tmp_path))
+    assert outs == [6.0, 6.0]
+    assert "rank 1 of 2" in open(tmp_path / "out1.txt").read()
+
+
+def _rank_job(rank, world, k):
+    import torch
+    import torch.distributed as dist
+    print(f"rank {rank} of {world}", flush=True)
+    t = torch.tensor([float(k)])
+    dist.all_reduce(t)
+    return float(t)
+
+
 def test_llm_primer_loss_decreases():
     sys.path.insert(0, os.path.join(ROOT, "examples"))
     import llm_primer
