@@ -4,7 +4,8 @@
   torchrun --nproc-per-node S benchmarks/bench_pp_llama.py [--schedule 1f1b --micro 8 --kernels]
 
 S stages, `--micro` micro-batches of one sequence per iteration; reports tokens/s (device-timed, max over ranks) for the
-plain PyTorch stage modules and for the kernel path (`ops/nn.use_kernels`)."""
+plain PyTorch stage modules, for the kernel path (`ops/nn.use_kernels`) and for the kernel path with every micro-batch op
+replayed from a CUDA graph (`PipelineStage(graph=True)`: forward graph + recomputing forward-backward graph per stage)."""
 import argparse, json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -30,15 +31,16 @@ def main():
     tokens = torch.randint(0, V, (a.micro, 256), generator=torch.Generator().manual_seed(1)).cuda()
     mbs = list(tokens.split(1))
     out = {"stages": world, "schedule": a.schedule, "micro_batches": a.micro, "ms_per_iter": {}, "tokens_per_s": {}}
-    for arm in ("torch", "kernels"):
+    for arm in ("torch", "kernels", "kernels_graphed"):
         torch.manual_seed(0)
         mesh = Mesh(world, 1)
         stage = LLama(None, V, 288, 6, "cuda", 6, 256).split_stages(world)[mesh.stage_id]
-        if arm == "kernels":
+        if arm.startswith("kernels"):
             use_kernels(stage)
-        loss_fn = (lambda o, t: kernel_causal_lm_loss(o, t)) if arm == "kernels" else (lambda o, t: causalLLMLoss(o, t, V))
-        st = PipelineStage(stage, mesh, (1, 256, 288), schedule=a.schedule, n_micro=a.micro, loss_fn=loss_fn, device="cuda")
-        arena = FlatArena.from_module(stage, with_grad=True)
+        loss_fn = (lambda o, t: kernel_causal_lm_loss(o, t)) if arm.startswith("kernels") else (lambda o, t: causalLLMLoss(o, t, V))
+        st = PipelineStage(stage, mesh, (1, 256, 288), schedule=a.schedule, n_micro=a.micro, loss_fn=loss_fn, device="cuda",
+                           graph=arm.endswith("graphed"))
+        arena = st.arena                      # the stage keeps parameters / gradients in one flat arena each
         m, v = torch.zeros_like(arena.flat), torch.zeros_like(arena.flat)
 
         def it(step):

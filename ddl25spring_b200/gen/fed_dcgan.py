@@ -140,7 +140,7 @@ def _pad4(n: int) -> int:
 class FederatedDCGAN:
     def __init__(self, client_images: list[torch.Tensor], client_fraction: float = 1.0, local_steps: int = 2, batch_size: int = 16,
                  lr: float = 2e-4, seed: int = 0, device=None, ngf: int = 64, ndf: int = 64, kernel_convs: bool | None = None,
-                 graph: bool | None = None):
+                 graph: bool | None = None, collective=None):
         self.device = torch.device(device) if device is not None else torch.device("cuda" if torch.cuda.is_available() else "cpu")
         self.clients = client_images
         self.counts = [len(c) for c in client_images]
@@ -159,6 +159,22 @@ class FederatedDCGAN:
         self.rank, self.world = (dist.get_rank(), dist.get_world_size()) if dist.is_initialized() else (0, 1)
         pg, pd = self.glob.n_param_elems()
         z = lambda n: torch.zeros(_pad4(n), device=self.device)
+        # Multi-GPU aggregation.  collective = a parallel.symm_impl.SymmetricArena: each rank pre-reduces ITS clients' G and D
+        # (one [G | D] row, HBM speed), then ONE fused peer-memory kernel per rank sums the W partial rows shard by shard and
+        # stores the result into every rank's replica - which IS the global G / D arena (rebased onto the symmetric buffer),
+        # so the new global model needs no further copy.  None: torch.distributed all_reduce (the baseline).
+        self.collective = collective if (collective is not None and self.world > 1) else None
+        if self.collective is not None:
+            a = self.collective
+            self._pg, self._pd = self.glob.ga.size, self.glob.da.size
+            n = self._pg + self._pd
+            self._part = a.alloc("dcgan_partial", n * 4)
+            res = a.alloc("dcgan_global", n * 4)
+            self._part_ptrs, self._res_ptrs = a.peer_ptrs("dcgan_partial"), a.peer_ptrs("dcgan_global")
+            self.glob.ga.rebase(res[:self._pg])
+            self.glob.da.rebase(res[self._pg:n])
+            self._n_sym = n
+            a.barrier()
         self._adam = {}                      # per-client Adam moments persist across rounds
         self._zeros = z
         self.history: list[tuple[float, float]] = []
@@ -200,14 +216,28 @@ class FederatedDCGAN:
                 UD[i].copy_(self.work.da.flat.detach())
             lw = [float(w[pos]) for pos, _ in mine] or [0.0]
             with torch.no_grad():
-                aggG = ops.weighted_sum(UG, lw)
-                aggD = ops.weighted_sum(UD, lw)
-                if self.world > 1:
-                    dist.all_reduce(aggG); dist.all_reduce(aggD)
-                self.glob.ga.flat.copy_(aggG)
-                self.glob.da.flat.copy_(aggD)
+                if self.collective is not None:
+                    from ..parallel.symm_impl import shard_bounds
+                    a = self.collective
+                    if mine:
+                        ops.weighted_sum(UG, lw, self._part[:self._pg])
+                        ops.weighted_sum(UD, lw, self._part[self._pg:self._n_sym])
+                    else:
+                        self._part.zero_()
+                    d0, d1 = shard_bounds(self._n_sym, a.world, a.rank)
+                    a.reduce(0, self._part_ptrs, [1.0] * a.world, self._res_ptrs, d0, d1)     # writes the global G | D everywhere
+                else:
+                    aggG = ops.weighted_sum(UG, lw)
+                    aggD = ops.weighted_sum(UD, lw)
+                    if self.world > 1:
+                        dist.all_reduce(aggG); dist.all_reduce(aggD)
+                    self.glob.ga.flat.copy_(aggG)
+                    self.glob.da.flat.copy_(aggD)
             if losses:
                 self.history.append(tuple(np.mean(losses, axis=0)))
+        if self.collective is not None:
+            torch.cuda.synchronize()
+            self.collective.check()
         return self.history
 
     @torch.no_grad()

@@ -234,8 +234,31 @@ class PipelineStage:
     """
 
     def __init__(self, module: nn.Module, mesh: Mesh, act_shape: Sequence[int], *, schedule: str = "1f1b",
-                 n_micro: int = 1, loss_fn=None, act_dtype=torch.float32, device=None):
+                 n_micro: int = 1, loss_fn=None, act_dtype=torch.float32, device=None, flat_arena: bool = True,
+                 grad_reducer=None, graph: bool = False):
         self.module, self.mesh, self.n_micro = module, mesh, n_micro
+        # graph=True (CUDA only): a micro-batch's compute is two CUDA graphs per stage - "forward" (no autograd state kept)
+        # and "forward + backward" (the activations are RECOMPUTED inside the backward graph), replayed per op with static
+        # input / output buffers; the last stage needs only the second one.  The lab-sized stages are launch-bound (a few
+        # hundred ~5 us kernels per op), so one cudaGraphLaunch per op is worth far more than the extra forward costs.
+        # NCCL p2p stays outside the graphs.  Needs a deterministic forward without batch statistics (no Dropout, no BatchNorm).
+        self.graph = bool(graph) and torch.cuda.is_available()
+        self._g_fwd = self._g_bwd = None
+        if self.graph:
+            for mod in module.modules():
+                if isinstance(mod, nn.modules.batchnorm._BatchNorm) or (isinstance(mod, nn.Dropout) and mod.p > 0):
+                    raise ValueError("PipelineStage(graph=True) recomputes the forward: the stage must not contain BatchNorm / Dropout")
+            assert flat_arena, "graph mode accumulates into the static flat gradient arena"
+        # the stage's parameters and gradients live in one flat arena each, so the per-stage DP reduction of PP x DP is ONE
+        # collective over one buffer (NCCL all-reduce, or `grad_reducer`: parallel.symm_impl.SymmetricGradReducer built on an
+        # arena of the stage's DP group) instead of one call per parameter (intro_PP_1F1B_MP.py:232-235)
+        from ..core.arena import FlatArena
+        self.arena = FlatArena.from_module(module, with_grad=True) if flat_arena else None
+        self.grad_reducer = grad_reducer
+        if grad_reducer is not None and self.arena is not None and hasattr(grad_reducer, "grad"):
+            self.arena.grad = grad_reducer.grad[:self.arena.size]
+            self.arena.grad.zero_()
+            self.arena.bind_grads()
         self.schedule = SCHEDULES[schedule](mesh.n_stages, mesh.stage_id, n_micro)
         self.loss_fn = loss_fn
         self.act_shape, self.act_dtype = tuple(act_shape), act_dtype
@@ -246,9 +269,97 @@ class PipelineStage:
     def _buf(self):
         return torch.empty(self.act_shape, dtype=self.act_dtype, device=self.device)
 
+    # ------------------------------------------------------------------ CUDA-graph mode
+    def _build_graphs(self, x_example: torch.Tensor, tgt_example: torch.Tensor | None) -> None:
+        from ..utils.graphs import GraphedStep
+        mod = self.module
+        self._rebind_grads()
+        saved_grad = self.arena.grad.clone()
+
+        def fwd(x):
+            with torch.no_grad():
+                return mod(x)
+
+        def fwd_bwd(x, gout):
+            xin = x.detach().requires_grad_(x.is_floating_point())
+            mod(xin).backward(gout)
+            return xin.grad if xin.grad is not None else gout.new_zeros(1)
+
+        def fwd_loss_bwd(x, tgt):
+            xin = x.detach().requires_grad_(x.is_floating_point())
+            loss = self.loss_fn(mod(xin), tgt) / self.n_micro
+            loss.backward()
+            return (xin.grad if xin.grad is not None else loss.new_zeros(1)), loss.detach()
+
+        if self.is_last:
+            self._g_bwd = GraphedStep(fwd_loss_bwd, (x_example, tgt_example))
+        else:
+            self._g_fwd = GraphedStep(fwd, (x_example,))
+            gout = torch.zeros(self.act_shape, dtype=self.act_dtype, device=self.device)
+            self._g_bwd = GraphedStep(fwd_bwd, (x_example, gout))
+        torch.cuda.synchronize()
+        with torch.no_grad():
+            self.arena.grad.copy_(saved_grad)        # warm-up / capture runs accumulated gradients of the example batch
+
+    def _run_graphed(self, inputs, targets) -> list[float]:
+        m = self.mesh
+        saved_in: dict[int, torch.Tensor] = {}
+        pending_send: list = []
+        recv_f: dict[int, tuple] = {}
+        recv_b: dict[int, tuple] = {}
+        loss_vals: list[torch.Tensor] = []
+        if self._g_bwd is None:
+            # capture before any transfer of this iteration is posted (no communication is in flight during a capture)
+            ex = inputs[0].to(self.device) if self.is_first else torch.zeros(self.act_shape, dtype=self.act_dtype, device=self.device)
+            self._build_graphs(ex, targets[0].to(self.device) if self.is_last else None)
+
+        def post_recv(op: Op):
+            if op.kind == F and not self.is_first and op.mb not in recv_f:
+                t = self._buf()
+                recv_f[op.mb] = (t, dist.irecv(t, src=m.prev_rank, group=m.fwd_group))
+            if op.kind == B and not self.is_last and op.mb not in recv_b:
+                t = self._buf()
+                recv_b[op.mb] = (t, dist.irecv(t, src=m.next_rank, group=m.bwd_group))
+
+        ops = self.schedule
+        if ops:
+            post_recv(ops[0])
+        for i, op in enumerate(ops):
+            if i + 1 < len(ops):
+                post_recv(ops[i + 1])
+            if op.kind == F:
+                if self.is_first:
+                    x = inputs[op.mb].to(self.device)
+                else:
+                    t, req = recv_f.pop(op.mb)
+                    req.wait()
+                    x = t
+                saved_in[op.mb] = x
+                if not self.is_last:                   # the last stage does forward + loss + backward in its B op
+                    payload = self._g_fwd(x).clone()
+                    pending_send.append((dist.isend(payload, dst=m.next_rank, group=m.fwd_group), payload))
+            else:
+                x = saved_in.pop(op.mb)
+                if self.is_last:
+                    gin, loss = self._g_bwd(x, targets[op.mb].to(self.device))
+                    loss_vals.append(loss.clone())
+                else:
+                    t, req = recv_b.pop(op.mb)
+                    req.wait()
+                    gin = self._g_bwd(x, t)
+                if not self.is_first:
+                    payload = gin.clone()
+                    pending_send.append((dist.isend(payload, dst=m.prev_rank, group=m.bwd_group), payload))
+        for r, _keepalive in pending_send:
+            r.wait()
+        self.losses = (torch.stack(loss_vals) * self.n_micro).tolist() if loss_vals else []
+        return self.losses
+
     def run(self, inputs: Sequence[torch.Tensor] | None = None, targets: Sequence[torch.Tensor] | None = None) -> list[float]:
         """One training iteration (all micro-batches, forward and backward).  Gradients accumulate in
         ``module.parameters()``; the caller zeroes them and steps its optimizer."""
+        if self.graph and self.device.type == "cuda":
+            return self._run_graphed(inputs, targets)
         m = self.mesh
         saved_in: dict[int, torch.Tensor] = {}
         saved_out: dict[int, torch.Tensor] = {}
@@ -256,6 +367,7 @@ class PipelineStage:
         recv_f: dict[int, tuple] = {}
         recv_b: dict[int, tuple] = {}
         self.losses = []
+        loss_vals: list[torch.Tensor] = []        # kept on the device: ONE read-back per iteration, not one per micro-batch
 
         def post_recv(op: Op):
             if op.kind == F and not self.is_first and op.mb not in recv_f:
@@ -283,7 +395,7 @@ class PipelineStage:
                 if self.is_last:
                     loss = self.loss_fn(out, targets[op.mb].to(self.device)) / self.n_micro
                     saved_out[op.mb] = loss
-                    self.losses.append(float(loss.detach()) * self.n_micro)
+                    loss_vals.append(loss.detach())
                 else:
                     saved_out[op.mb] = out
                     payload = out.detach().contiguous()
@@ -302,20 +414,49 @@ class PipelineStage:
                     pending_send.append((dist.isend(payload, dst=m.prev_rank, group=m.bwd_group), payload))
         for r, _keepalive in pending_send:
             r.wait()
+        if loss_vals:
+            self.losses = (torch.stack(loss_vals) * self.n_micro).tolist()
         return self.losses
 
+    def zero_grad(self) -> None:
+        if self.arena is not None:
+            self.arena.grad.zero_()
+            self._rebind_grads()
+        else:
+            for p in self.module.parameters():
+                p.grad = None
+
+    def _rebind_grads(self) -> None:
+        """Make every ``p.grad`` the arena view again (an optimizer's ``zero_grad(set_to_none=True)`` drops the binding;
+        gradients autograd then allocated elsewhere are copied in)."""
+        a = self.arena
+        params = dict(self.module.named_parameters())
+        for sp in a.specs:
+            if sp.is_buffer:
+                continue
+            p = params[sp.name]
+            view = a.grad[sp.offset:sp.offset + sp.numel].view(sp.shape)
+            if p.grad is None:
+                view.zero_()
+            elif p.grad.data_ptr() != view.data_ptr():
+                view.copy_(p.grad)
+            p.grad = view
+
     def allreduce_grads(self) -> None:
-        """Average gradients over the stage's DP group (PP x DP; intro_PP_1F1B_MP.py:232-235) — one flat
-        all-reduce over the stage's gradient arena instead of one call per parameter."""
+        """Average gradients over the stage's DP group (PP x DP; intro_PP_1F1B_MP.py:232-235): one collective over the
+        stage's flat gradient arena, in place."""
         if self.mesh.dp_group is None:
             return
-        grads = [p.grad for p in self.module.parameters() if p.grad is not None]
-        if not grads:
+        if self.arena is None:
+            grads = [p.grad for p in self.module.parameters() if p.grad is not None]
+            for g in grads:
+                dist.all_reduce(g, group=self.mesh.dp_group)
+                g.div_(self.mesh.n_pipelines)
             return
-        flat = torch.cat([g.reshape(-1) for g in grads])
-        dist.all_reduce(flat, group=self.mesh.dp_group)
-        flat.div_(self.mesh.n_pipelines)
-        off = 0
-        for g in grads:
-            g.copy_(flat[off:off + g.numel()].view_as(g))
-            off += g.numel()
+        self._rebind_grads()
+        g = self.arena.grad
+        if self.grad_reducer is not None:
+            self.grad_reducer(g, 0, g.numel()).wait()        # fused peer-memory reduce over the DP group's arena
+        else:
+            dist.all_reduce(g, group=self.mesh.dp_group)
+        g.div_(self.mesh.n_pipelines)

@@ -393,7 +393,7 @@ def test_nvls_allreduce_matches_nccl():
     print("NVLS all-reduce 44.7 MB: ours %.3f ms, NCCL %.3f ms" % (outs[0]["nvls_ms"], outs[0]["nccl_ms"]))
 
 
-def _pp_nccl_worker(rank, world, schedule, n_micro):
+def _pp_nccl_worker(rank, world, schedule, n_micro, graph=False):
     """Two-stage pipeline over NCCL p2p with the stage modules on the hand-written kernels."""
     from ddl25spring_b200.models.llama import LLama, causalLLMLoss
     from ddl25spring_b200.ops.nn import use_kernels
@@ -405,9 +405,13 @@ def _pp_nccl_worker(rank, world, schedule, n_micro):
     mesh = pp.Mesh(world, 1)
     stage_mod = use_kernels(model.split_stages(world)[mesh.stage_id])
     st = pp.PipelineStage(stage_mod, mesh, (1, T, D), schedule=schedule, n_micro=n_micro,
-                          loss_fn=lambda out, tgt: causalLLMLoss(out, tgt, V), device="cuda")
+                          loss_fn=lambda out, tgt: causalLLMLoss(out, tgt, V), device="cuda", graph=graph)
     mbs = list(tokens.split(1))
+    st.zero_grad()
     losses = st.run(inputs=mbs, targets=mbs)
+    if graph:                                           # replay once more: the graphs must be reusable across iterations
+        st.zero_grad()
+        losses = st.run(inputs=mbs, targets=mbs)
     torch.cuda.synchronize()
     # oracle on this rank: the unsplit model in plain PyTorch
     torch.manual_seed(0)
@@ -423,9 +427,140 @@ def _pp_nccl_worker(rank, world, schedule, n_micro):
 
 
 @pytest.mark.timeout(300)
-@pytest.mark.parametrize("schedule,n_micro", [("gpipe", 3), ("1f1b", 4)])
-def test_pipeline_over_nccl_on_kernels_matches_unsplit_model(schedule, n_micro):
-    outs = run_distributed(_pp_nccl_worker, 2, (schedule, n_micro), timeout=240, backend="nccl")
+@pytest.mark.parametrize("schedule,n_micro,graph", [("gpipe", 3, False), ("1f1b", 4, False), ("1f1b", 4, True)])
+def test_pipeline_over_nccl_on_kernels_matches_unsplit_model(schedule, n_micro, graph):
+    outs = run_distributed(_pp_nccl_worker, 2, (schedule, n_micro, graph), timeout=240, backend="nccl")
     for o in outs:
         assert o["worst_rel"] < 5e-3, o
     assert [o for o in outs if o["stage"] == 1][0]["n_losses"] == n_micro
+
+
+def _pp_conv_worker(rank, world, which):
+    """2-stage model-parallel split of the conv models (BASELINE config 5) over NCCL p2p, stages on the NHWC tcgen05 stack;
+    gradients must equal the unsplit model's."""
+    import torch.nn.functional as Fn
+    from ddl25spring_b200.parallel import pp
+    torch.manual_seed(0)
+    n_micro, mb = 2, 16
+    if which == "resnet":
+        from ddl25spring_b200.models.resnet_nhwc import resnet18_nhwc, split_resnet18_nhwc_two_stage
+        full = resnet18_nhwc().cuda()
+        torch.manual_seed(0)
+        ref = resnet18_nhwc().cuda()
+        stages = split_resnet18_nhwc_two_stage(full)
+        ref_stages = split_resnet18_nhwc_two_stage(ref)
+        act_shape = (mb, 4, 4, 128)
+        g = torch.Generator().manual_seed(1)
+        xs = [torch.randn(mb, 3, 32, 32, generator=g).cuda() for _ in range(n_micro)]
+        ys = [torch.randint(0, 10, (mb,), generator=g).cuda() for _ in range(n_micro)]
+        loss_fn = lambda out, tgt: Fn.cross_entropy(out, tgt)
+        fwd_full = lambda x: ref(x)
+    else:
+        from ddl25spring_b200.models.dcgan_nhwc import DiscriminatorNHWC
+        full = DiscriminatorNHWC(16).cuda()
+        torch.manual_seed(0)
+        ref = DiscriminatorNHWC(16).cuda()
+        stages, ref_stages = full.stages(), ref.stages()
+        g = torch.Generator().manual_seed(1)
+        xs = [(torch.rand(mb, 3, 64, 64, generator=g) * 2 - 1).cuda() for _ in range(n_micro)]
+        ys = [torch.randint(0, 2, (mb,), generator=g).float().cuda() for _ in range(n_micro)]
+        with torch.no_grad():
+            act_shape = tuple(stages[0](xs[0]).shape)
+        loss_fn = lambda out, tgt: Fn.binary_cross_entropy_with_logits(out.view(-1), tgt)
+        fwd_full = lambda x: ref(x)
+    mesh = pp.Mesh(2, 1)
+    st = pp.PipelineStage(stages[mesh.stage_id], mesh, act_shape, schedule="1f1b", n_micro=n_micro, loss_fn=loss_fn, device="cuda")
+    st.zero_grad()
+    losses = st.run(inputs=xs, targets=ys)
+    torch.cuda.synchronize()
+    # oracle on this rank: the unsplit model, micro-batch by micro-batch (BatchNorm statistics are per micro-batch in both)
+    for x, y in zip(xs, ys):
+        (loss_fn(fwd_full(x), y) / n_micro).backward()
+    worst = 0.0
+    refp = dict(ref_stages[mesh.stage_id].named_parameters())
+    for n, p in stages[mesh.stage_id].named_parameters():
+        r = refp[n].grad
+        worst = max(worst, float((p.grad - r).norm() / r.norm().clamp_min(1e-12)))
+    return {"worst_rel": worst, "stage": mesh.stage_id, "n_losses": len(losses)}
+
+
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize("which", ["resnet", "dcgan_d"])
+def test_conv_model_two_stage_split_over_nccl_matches_unsplit(which):
+    outs = run_distributed(_pp_conv_worker, 2, (which,), timeout=240, backend="nccl")
+    for o in outs:
+        assert o["worst_rel"] < 2e-3, o
+    assert [o for o in outs if o["stage"] == 1][0]["n_losses"] == 2
+
+
+def _pp_dp_worker(rank, world, n_stages, schedule):
+    """PP x DP hybrid on GPUs (the configuration the reference deadlocks on, lab/homework-1.ipynb cell 48): n_stages pipeline
+    stages x world/n_stages pipelines; after allreduce_grads every replica of a stage holds the mean gradient over pipelines,
+    equal to the unsplit model's gradient on the union of the pipelines' batches."""
+    from ddl25spring_b200.models.llama import LLama, causalLLMLoss
+    from ddl25spring_b200.ops.nn import use_kernels
+    from ddl25spring_b200.parallel import pp
+    V, D, T, n_micro = 512, 96, 64, 2
+    n_pipe = world // n_stages
+    mesh = pp.Mesh(n_stages, n_pipe)
+    torch.manual_seed(0)
+    model = LLama(None, V, D, 6, "cuda", 2 * n_stages, T)
+    stage_mod = use_kernels(model.split_stages(n_stages)[mesh.stage_id])
+    st = pp.PipelineStage(stage_mod, mesh, (1, T, D), schedule=schedule, n_micro=n_micro,
+                          loss_fn=lambda out, tgt: causalLLMLoss(out, tgt, V), device="cuda")
+    all_tokens = torch.randint(0, V, (n_pipe, n_micro, T), generator=torch.Generator().manual_seed(1)).cuda()
+    mine = list(all_tokens[mesh.pipeline_id].split(1))
+    st.zero_grad()
+    for _ in range(2):                                  # two iterations: communicators / schedules are reusable
+        st.zero_grad()
+        st.run(inputs=mine, targets=mine)
+        st.allreduce_grads()
+    torch.cuda.synchronize()
+    torch.manual_seed(0)
+    ref = LLama(None, V, D, 6, "cuda", 2 * n_stages, T)
+    loss = sum(causalLLMLoss(ref(t), t, V) for p in range(n_pipe) for t in all_tokens[p].split(1)) / (n_micro * n_pipe)
+    loss.backward()
+    ref_stage = dict(ref.split_stages(n_stages)[mesh.stage_id].named_parameters())
+    worst = 0.0
+    for n, p in stage_mod.named_parameters():
+        r = ref_stage[n].grad
+        worst = max(worst, float((p.grad - r).norm() / r.norm().clamp_min(1e-12)))
+    return {"worst_rel": worst, "stage": mesh.stage_id, "pipeline": mesh.pipeline_id}
+
+
+@pytest.mark.timeout(400)
+@pytest.mark.parametrize("schedule", ["gpipe", "1f1b"])
+def test_pp_dp_hybrid_over_nccl(schedule):
+    n = torch.cuda.device_count()
+    if n < 4:
+        pytest.skip("PP x DP needs >= 4 GPUs (2 stages x 2 pipelines)")
+    world = 8 if n >= 8 else 4
+    outs = run_distributed(_pp_dp_worker, world, (2, schedule), timeout=300, backend="nccl")
+    for o in outs:
+        assert o["worst_rel"] < 5e-3, o
+    assert {o["pipeline"] for o in outs} == set(range(world // 2))
+
+
+def _fed_dcgan_worker(rank, world):
+    from ddl25spring_b200.gen.fed_dcgan import FederatedDCGAN
+    from ddl25spring_b200.parallel.symm_impl import SymmetricArena
+    g = torch.Generator().manual_seed(0)
+    clients = [torch.rand(24, 3, 64, 64, generator=g) * 2 - 1 for _ in range(2 * world)]
+    out = {}
+    for name in ("fused", "nccl"):
+        fed = FederatedDCGAN(clients, 1.0, local_steps=1, batch_size=8, seed=3, device="cuda", ngf=16, ndf=16,
+                             collective=SymmetricArena() if name == "fused" else None)
+        fed.run(2)
+        torch.cuda.synchronize()
+        out[name] = (fed.glob.ga.flat.clone().cpu(), fed.glob.da.flat.clone().cpu())
+    return out
+
+
+@pytest.mark.timeout(400)
+def test_federated_dcgan_fused_aggregation_equals_nccl():
+    world = min(torch.cuda.device_count(), 8)
+    outs = run_distributed(_fed_dcgan_worker, world, timeout=300, backend="nccl")
+    for o in outs:
+        torch.testing.assert_close(o["fused"][0], o["nccl"][0], rtol=1e-4, atol=1e-5)
+        torch.testing.assert_close(o["fused"][1], o["nccl"][1], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(outs[0]["fused"][0], outs[-1]["fused"][0], rtol=0, atol=0)
