@@ -54,7 +54,30 @@ def main():
         e1.record(); torch.cuda.synchronize()
         return max_over_ranks(e0.elapsed_time(e1) / a.iters * 1e3, "cuda")
 
-    r = {"world": world, "batch": a.batch, "emb_per_party": a.emb, "top_fc1_out": a.out, "us": {"fused": round(t(fused), 2), "nccl_allgather_cat_linear": round(t(nccl), 2)}}
+    # ---- whole training step of the split network (bottom MLP per party, gather, top model, CE, backward, AdamW)
+    from ddl25spring_b200.ops.nn import kernel_cross_entropy, use_kernels
+    from ddl25spring_b200.ops.optim import ArenaOptimizer
+    from ddl25spring_b200.parallel import vfl
+    from ddl25spring_b200.parallel.symm_impl import FusedVFLGather
+    g = torch.Generator().manual_seed(rank)
+    x_local = torch.randn(a.batch, a.emb // 2, generator=g).cuda()
+    y = torch.randint(0, 2, (a.batch,), generator=torch.Generator().manual_seed(0)).cuda()
+    step_ms = {}
+    for arm in ("fused_kernels", "allgather_aten"):
+        hook = FusedVFLGather(arena, a.batch, dims, a.out) if arm == "fused_kernels" else None
+        net = vfl.DistributedVFL(a.emb // 2, dims, act_on_logits=False, seed=3, gather_linear=hook).cuda()
+        if arm == "fused_kernels":
+            use_kernels(net)
+            opt, lf = ArenaOptimizer(net, "adamw"), kernel_cross_entropy
+        else:
+            opt, lf = torch.optim.AdamW(net.parameters()), torch.nn.functional.cross_entropy
+
+        def step():
+            opt.zero_grad()
+            lf(net(x_local), y).backward()
+            opt.step()
+        step_ms[arm] = round(t(step) / 1e3, 4)
+    r = {"world": world, "train_step_ms": step_ms, "train_samples_per_s": {k: round(a.batch / v * 1e3, 1) for k, v in step_ms.items()}, "batch": a.batch, "emb_per_party": a.emb, "top_fc1_out": a.out, "us": {"fused": round(t(fused), 2), "nccl_allgather_cat_linear": round(t(nccl), 2)}}
     ref = nccl()
     fused()
     r["max_abs_err_vs_fp32"] = float((out - ref).abs().max())

@@ -15,6 +15,8 @@ from torch import nn, optim
 
 from .. import ops
 from ..core.checkpoint import snapshot
+from ..ops.nn import kernel_cross_entropy, use_kernels
+from ..ops.optim import make_optimizer
 from ..models.tabular import Autoencoder, HeartDiseaseNN, vae_loss
 
 
@@ -41,14 +43,16 @@ def fused_vae_loss(x_recon, x, mu, logvar):
 def train_evaluator(x_train, y_train, x_test, y_test, epochs: int = 49, model: nn.Module | None = None, log=None):
     """Returns ``(model with best-on-test weights, best test accuracy, history)``."""
     net = model or HeartDiseaseNN(x_train.shape[1]).to(x_train.device)
-    opt = optim.AdamW(net.parameters())
+    if x_train.is_cuda:            # B200 path: every Linear on the tcgen05 GEMM (forward + both gradients), fused cross-entropy,
+        use_kernels(net)           # one fused AdamW launch over the flat parameter arena
+    opt = make_optimizer(net, "adamw")
     best_acc, best = -1.0, snapshot(net)
     hist = []
     for epoch in range(1, epochs + 1):
         net.train()
         opt.zero_grad()
         out = net(x_train)
-        loss = F.cross_entropy(out, y_train)
+        loss = kernel_cross_entropy(out, y_train)
         loss.backward()
         opt.step()
         net.eval()
@@ -66,7 +70,9 @@ def train_evaluator(x_train, y_train, x_test, y_test, epochs: int = 49, model: n
 def train_tabular_vae(real_data: torch.Tensor, H: int = 48, H2: int = 32, latent_dim: int = 16, epochs: int = 200,
                       batch_size: int = 64, lr: float = 1e-3, zero_grad_per_step: bool = True, log=None) -> Autoencoder:
     model = Autoencoder(real_data.shape[1], H, H2, latent_dim).to(real_data.device)
-    opt = optim.Adam(model.parameters(), lr=lr)
+    if real_data.is_cuda:          # Linear + BatchNorm1d on kernels, fused VAE loss, fused Adam over the arena
+        use_kernels(model)
+    opt = make_optimizer(model, "adam", lr=lr)
     model.train()
     model.train_with_settings(epochs, batch_size, real_data, opt, fused_vae_loss, zero_grad_per_step=zero_grad_per_step, log=log)
     return model

@@ -16,33 +16,91 @@ from . import _lib
 from .gemm import gemm
 
 
+def _ceil32(n: int) -> int:
+    return (n + 31) // 32 * 32
+
+
+def pad2d(src: torch.Tensor, rows_dst: int, cols_dst: int, fill_col: int = -1, fill_vec: torch.Tensor | None = None,
+          fill_val: float = 0.0) -> torch.Tensor:
+    """Zero-padded copy of a 2-D fp32 CUDA tensor (row-contiguous), optionally with one filled column (csrc/elementwise.cu)."""
+    assert src.dim() == 2 and src.stride(1) == 1
+    dst = torch.empty(rows_dst, cols_dst, device=src.device, dtype=torch.float32)
+    _lib.check(_lib.lib().ddl_pad2d(_lib.p(src), _lib.i64(src.stride(0)), int(src.shape[0]), int(src.shape[1]), _lib.p(dst),
+                                    _lib.i64(cols_dst), int(rows_dst), int(cols_dst), int(fill_col), _lib.p(fill_vec), _lib.f32(fill_val),
+                                    _lib.stream()), "ddl_pad2d")
+    return dst
+
+
+def col_sum(x: torch.Tensor) -> torch.Tensor:
+    """``x.sum(0)`` of a 2-D fp32 CUDA tensor (bias gradients), deterministic."""
+    assert x.dim() == 2 and x.stride(1) == 1
+    out = torch.empty(x.shape[1], device=x.device, dtype=torch.float32)
+    _lib.check(_lib.lib().ddl_col_sum(_lib.p(x), _lib.i64(x.stride(0)), int(x.shape[0]), int(x.shape[1]), _lib.p(out), _lib.f32(1.0),
+                                      _lib.f32(0.0), _lib.stream()), "ddl_col_sum")
+    return out
+
+
 class _LinearFn(torch.autograd.Function):
+    """nn.Linear on the tcgen05 GEMM, forward + both gradients, for ANY layer width.
+
+    Widths that are multiples of 32 (LLaMA, the ResNet head's input) use the operands as they are.  Ragged widths (the tabular
+    models: 30 -> 64 -> ... -> 2, party slabs of 6 .. 26 columns) are handled by operand preparation, one pad2d launch each:
+    X and W are zero-padded to multiples of 32 along the reduction, and the bias is FOLDED INTO THE GEMM - X gets a column of
+    ones, W the bias vector in the same column - so the forward needs no bias epilogue and the weight-gradient GEMM
+    ``dY^T [X | 1]`` delivers ``db`` in that column for free.  No ATen / cuBLAS GEMM on either path."""
+
     @staticmethod
     def forward(ctx, x, w, b, precise):
-        x2 = x.reshape(-1, x.shape[-1]).contiguous()
-        y = gemm(x2, w, bias=b, precise=precise)
-        ctx.save_for_backward(x2, w)
+        x2 = x.reshape(-1, x.shape[-1])
+        if x2.stride(1) != 1:
+            x2 = x2.contiguous()
+        N, K = w.shape
+        M = x2.shape[0]
         ctx.has_bias, ctx.precise, ctx.shape = b is not None, precise, x.shape
-        return y.view(*x.shape[:-1], w.shape[0])
+        ctx.aligned = K % 32 == 0 and N % 32 == 0 and w.stride(1) == 1 and (w.stride(0) * 4) % 16 == 0 and (x2.stride(0) * 4) % 16 == 0
+        if ctx.aligned:
+            y = gemm(x2, w, bias=b, precise=precise)
+            ctx.save_for_backward(x2, w)
+        else:
+            Kp, Np = _ceil32(K + (1 if b is not None else 0)), _ceil32(N)
+            xp = pad2d(x2, M, Kp, K if b is not None else -1, None, 1.0)
+            wp = pad2d(w if w.stride(1) == 1 else w.contiguous(), Np, Kp, K if b is not None else -1, b, 0.0)
+            y = gemm(xp, wp[:N], precise=precise)                   # [M, N] contiguous; rows N.. of wp only serve the backward
+            ctx.save_for_backward(xp, wp)
+        ctx.dims = (M, N, K)
+        return y.view(*x.shape[:-1], N)
 
     @staticmethod
     def backward(ctx, gy):
-        x2, w = ctx.saved_tensors
-        g2 = gy.reshape(-1, gy.shape[-1]).contiguous()
-        n_out, n_in = w.shape
-        mn_ok = n_in % 32 == 0 and n_out % 32 == 0 and (w.stride(0) * 4) % 16 == 0
+        M, N, K = ctx.dims
+        g2 = gy.reshape(-1, N)
         gx = gw = gb = None
+        if ctx.aligned:
+            x2, w = ctx.saved_tensors
+            g2 = g2.contiguous()
+            if ctx.needs_input_grad[0]:
+                gx = gemm(g2, w, b_mn=True, precise=ctx.precise).view(ctx.shape)
+            if ctx.needs_input_grad[1]:
+                gw = gemm(g2, x2, a_mn=True, b_mn=True, precise=ctx.precise)
+            if ctx.has_bias and ctx.needs_input_grad[2]:
+                gb = col_sum(g2)
+            return gx, gw, gb, None
+        xp, wp = ctx.saved_tensors
+        Np, Kp = wp.shape
+        g2p = pad2d(g2 if g2.stride(1) == 1 else g2.contiguous(), M, Np)
         if ctx.needs_input_grad[0]:
-            gx = (gemm(g2, w, b_mn=True, precise=ctx.precise) if mn_ok else g2 @ w).view(ctx.shape)
-        if ctx.needs_input_grad[1]:
-            gw = gemm(g2, x2, a_mn=True, b_mn=True, precise=ctx.precise) if mn_ok else g2.t() @ x2
-        if ctx.has_bias and ctx.needs_input_grad[2]:
-            gb = g2.sum(0)
+            gx = gemm(g2p, wp, b_mn=True, precise=ctx.precise)[:, :K].reshape(ctx.shape)
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            dwp = gemm(g2p, xp, a_mn=True, b_mn=True, precise=ctx.precise)          # [Np, Kp]; column K holds dY^T 1 = db
+            if ctx.needs_input_grad[1]:
+                gw = dwp[:N, :K]
+            if ctx.has_bias and ctx.needs_input_grad[2]:
+                gb = dwp[:N, K]
         return gx, gw, gb, None
 
 
 def kernel_linear(x, w, b=None, precise: bool = True):
-    if not x.is_cuda or x.dtype != torch.float32 or (w.stride(0) * 4) % 16 != 0 or w.stride(1) != 1:
+    if not x.is_cuda or x.dtype != torch.float32 or w.dtype != torch.float32 or x.numel() == 0:
         return F.linear(x, w, b)
     return _LinearFn.apply(x, w, b, precise)
 
@@ -74,6 +132,28 @@ def kernel_cross_entropy(logits: torch.Tensor, target: torch.Tensor, ignore_inde
     if not logits.is_cuda or logits.dtype != torch.float32:
         return F.cross_entropy(logits, target, ignore_index=ignore_index)
     return _XentFn.apply(logits.contiguous(), target.contiguous(), ignore_index)
+
+
+class _SoftXentFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target):
+        from . import softmax_xent
+        loss, grad = softmax_xent(logits, target, reduction="mean", want_grad=True)
+        ctx.save_for_backward(grad)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (grad,) = ctx.saved_tensors
+        return grad * g, None
+
+
+def kernel_soft_cross_entropy(logits: torch.Tensor, target: torch.Tensor):
+    """Mean cross-entropy against float (one-hot / soft) targets - ``nn.CrossEntropyLoss()(logits, probs)`` as used by
+    lab/tutorial_2b/vfl.py:51,79 - value and gradient from one launch of the fused kernel."""
+    if not logits.is_cuda or logits.dtype != torch.float32:
+        return F.cross_entropy(logits, target)
+    return _SoftXentFn.apply(logits.contiguous(), target.contiguous().float())
 
 
 def kernel_causal_lm_loss(logits: torch.Tensor, tokens: torch.Tensor):

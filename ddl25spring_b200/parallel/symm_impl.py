@@ -415,14 +415,16 @@ class FusedVFLGather:
     Forward: every party writes its embedding into a (double-buffered) symmetric buffer, a GPU-side barrier
     orders the writes, and ONE tcgen05 GEMM per rank computes ``cat(E_0..E_{W-1}) @ fc1.weight.T + bias`` with
     its k-blocks TMA-loaded directly from the owning GPUs — the concatenated embedding matrix never exists.
-    Backward: the embedding gradient needs only this party's weight slab (local GEMM = the scatter of
-    lab/tutorial_2b/vfl.py:81); the weight gradient is slab-sparse per rank and is summed with one fused
-    peer-memory reduce so every replica of the top model takes the same step.
+    Backward (all on the tcgen05 GEMM, no library matmul): the embedding gradient needs only this party's weight slab
+    (``dY W[:, slab]``, the scatter of lab/tutorial_2b/vfl.py:81; the slab is consumed MN-major from a 32-column padded
+    copy); the weight gradient ``dY^T E_p`` reads the party's embedding straight out of the symmetric buffer (MN-major,
+    zero-padded to 32 columns), lands in this rank's slab of a full-width partial that is zero elsewhere, and the partials
+    are summed with one fused peer-memory reduce so every replica of the top model takes the same step.
     """
 
     def __init__(self, arena: SymmetricArena, max_batch: int, dims, n_out: int):
         self.arena, self.dims = arena, [int(d) for d in dims]
-        self.ld = (max(self.dims) + 3) // 4 * 4
+        self.ld = (max(self.dims) + 31) // 32 * 32          # 32-column multiples: the buffer doubles as an MN-major GEMM operand
         self.max_batch = max_batch
         self.bufs = [arena.alloc(f"vfl_emb_{i}", max_batch * self.ld * 4).view(max_batch, self.ld) for i in range(2)]
         self.ptrs = [arena.peer_ptrs(f"vfl_emb_{i}") for i in range(2)]
@@ -447,24 +449,35 @@ class _FusedGatherLinear(torch.autograd.Function):
         h.bufs[slot][:B, :d].copy_(emb.detach())
         h.arena.barrier()                                   # all parties' embeddings are in place
         out = gather_linear_ptrs(h.ptrs[slot], h.dims, [h.ld] * len(h.dims), B, weight.detach(), bias.detach(), precise=True)
-        ctx.save_for_backward(emb.detach(), weight.detach())
-        ctx.h, ctx.rank = h, rank
+        ctx.save_for_backward(weight.detach())
+        ctx.h, ctx.rank, ctx.slot, ctx.B = h, rank, slot, B
         return out
 
     @staticmethod
     def backward(ctx, gout):
-        emb, weight = ctx.saved_tensors
-        h, rank = ctx.h, ctx.rank
+        from ..ops.gemm import gemm
+        from ..ops.nn import col_sum, pad2d
+        (weight,) = ctx.saved_tensors
+        h, rank, B = ctx.h, ctx.rank, ctx.B
         a = h.arena
         off = sum(h.dims[:rank])
         d = h.dims[rank]
-        gout = gout.contiguous()
-        demb = gout @ weight[:, off:off + d]                # scatter: only this party's slab is needed
+        d32 = (d + 31) // 32 * 32
         n_out, ktot = weight.shape
-        part = h.dw_part[:n_out * ktot].view(n_out, ktot)
-        part.zero_()
-        part[:, off:off + d] = gout.t() @ emb
+        gout = gout.contiguous()
+        if n_out % 32:                                       # top models here have 128 outputs; anything else: pad dY once
+            gout = pad2d(gout, B, (n_out + 31) // 32 * 32)
+        no32 = gout.shape[1]
+        # scatter: only this party's slab of the weight is needed -> dE_p = dY W[:, slab]
+        wslab = pad2d(weight[:, off:off + d], no32, d32)
+        demb = gemm(gout, wslab, b_mn=True, precise=True)[:, :d]
+        # weight gradient of the slab from the embedding that still sits in the symmetric buffer (columns >= d are zero)
+        emb_p = h.bufs[ctx.slot][:B, :d32]
+        dws = gemm(gout, emb_p, a_mn=True, b_mn=True, precise=True)            # [no32, d32]
+        part = h.dw_part[:n_out * ktot].view(n_out, ktot)                      # zero outside this rank's slab, always
+        _lib.check(_lib.lib().ddl_pad2d(_lib.p(dws), _lib.i64(dws.stride(0)), int(n_out), int(d), _lib.p(part[:, off:]), _lib.i64(ktot),
+                                        int(n_out), int(d), -1, None, _lib.f32(0.0), _lib.stream()), "ddl_pad2d")
         d0, d1 = shard_bounds(h.nw, a.world, a.rank)
         a.reduce(0, h.dw_part_ptrs, [1.0] * a.world, h.dw_sum_ptrs, d0, d1)
         dw = h.dw_sum[:n_out * ktot].view(n_out, ktot).clone()
-        return demb, dw, gout.sum(0), None, None
+        return demb, dw, col_sum(gout)[:n_out], None, None

@@ -107,6 +107,22 @@ class VFLNetwork(nn.Module):
         self.top_model = TopModel(local_models, n_outs, act_on_logits=act_on_logits)
         self.optimizer = optim.AdamW(self.parameters())
         self.criterion = nn.CrossEntropyLoss()
+        self._on_kernels = False
+
+    def _kernel_path(self, device) -> None:
+        """On a GPU: every Linear of the bottoms and the top model runs on the tcgen05 GEMM (forward, dgrad, wgrad with the
+        bias folded in), the soft-target cross-entropy is the fused kernel and AdamW is ONE launch over the flat arena of the
+        registered parameters (the frozen-bottoms quirk is kept: unregistered bottoms are not in the arena)."""
+        if self._on_kernels or torch.device(device).type != "cuda":
+            return
+        from ..ops.nn import kernel_soft_cross_entropy, use_kernels
+        from ..ops.optim import ArenaOptimizer
+        use_kernels(self)
+        for m in self.bottom_models:
+            use_kernels(m)
+        self.optimizer = ArenaOptimizer(self, "adamw")
+        self.criterion = kernel_soft_cross_entropy
+        self._on_kernels = True
 
     def forward(self, x: Sequence[torch.Tensor]) -> torch.Tensor:
         local_outs = [m(xi) for m, xi in zip(self.bottom_models, x)]
@@ -116,8 +132,10 @@ class VFLNetwork(nn.Module):
                             zero_grad_per_step: bool = True, log_loss: Callable[[int, float], None] | None = None,
                             verbose: bool = False) -> list[float]:
         self.num_cli, self.cli_features = n_cli, cli_features
-        x_train = [_select(x, feats, self.columns) for feats in cli_features]
-        y_train = _targets(y)
+        dev = next(self.top_model.parameters()).device
+        self._kernel_path(dev)
+        x_train = [_select(x, feats, self.columns).to(dev) for feats in cli_features]
+        y_train = _targets(y).to(dev)
         n = len(y_train)
         history = []
         for epoch in range(epochs):
@@ -145,8 +163,9 @@ class VFLNetwork(nn.Module):
     @torch.no_grad()
     def test(self, x, y):
         was = self.training
-        x_test = [_select(x, feats, self.columns) for feats in self.cli_features]
-        y_test = _targets(y)
+        dev = next(self.top_model.parameters()).device
+        x_test = [_select(x, feats, self.columns).to(dev) for feats in self.cli_features]
+        y_test = _targets(y).to(dev)
         outs = self.forward(x_test)
         acc = (outs.argmax(1) == y_test.argmax(1)).float().mean()
         loss = self.criterion(outs, y_test)
@@ -163,7 +182,11 @@ def build_vfl(table: HeartTable, client_feature_names: Sequence[Sequence[str]], 
 def train_vfl_vae(model: VFLVAE, x_clients: Sequence[torch.Tensor], epochs: int = 1000, lr: float = 1e-3,
                   log: Callable[[int, float], None] | None = None) -> list[float]:
     """Full-batch Adam loop of exercise_3.py:191-203; returns the per-epoch combined loss."""
-    opt = optim.Adam(model.parameters(), lr=lr)
+    if next(model.parameters()).is_cuda:       # Linear / BatchNorm1d on kernels, fused Adam over the arena
+        from ..ops.nn import use_kernels
+        use_kernels(model)
+    from ..ops.optim import make_optimizer
+    opt = make_optimizer(model, "adam", lr=lr)
     losses = []
     for epoch in range(epochs):
         model.train()
@@ -227,3 +250,81 @@ class DistributedVFL(nn.Module):
             h = t.fc3(t.act(t.fc2(h)))
             return t.dropout(t.act(h)) if t.act_on_logits else h
         return self.top_model.forward_from_concat(_GatherCat.apply(emb, self.dims, self.rank, self.group))
+
+
+# ------------------------------------------------------------------------------------------ distributed VFL-VAE
+class _SliceScatter(torch.autograd.Function):
+    """The server -> party crossing of the vertical VAE (exercise_3.py:132-137).  Forward: party ``rank`` takes its column
+    slice of the (replicated) reconstructed latent.  Backward: the gradient of the replicated tensor is the CONCATENATION of
+    every party's slice gradient, so the slices are all-gathered - afterwards every replica of the server VAE back-propagates
+    the same, complete gradient and the replicas stay identical without any parameter all-reduce."""
+
+    @staticmethod
+    def forward(ctx, recon_concat: torch.Tensor, rank: int, width: int, n_parties: int, group):
+        ctx.rank, ctx.width, ctx.n, ctx.group = rank, width, n_parties, group
+        return recon_concat[:, rank * width:(rank + 1) * width].contiguous()
+
+    @staticmethod
+    def backward(ctx, g):
+        parts = [torch.empty_like(g) for _ in range(ctx.n)]
+        dist.all_gather(parts, g.contiguous(), group=ctx.group)
+        return torch.cat(parts, dim=1), None, None, None, None
+
+
+class DistributedVFLVAE(nn.Module):
+    """The vertical VAE of lab/tutorial_2b/exercise_3.py:115-147 with one party per rank (GPU).
+
+    Each rank owns its party's encoder and decoder - private features and reconstructions never leave it - and a replica of
+    the server VAE.  Two crossings per forward: the party latents are all-gathered into ``concat_latent`` (its backward keeps
+    the own slice: :class:`_GatherCat`), and the reconstructed latent is sliced per party (its backward all-gathers the slice
+    gradients: :class:`_SliceScatter`).  The server replicas see identical inputs and identical noise (same seed, same RNG
+    consumption), compute identical gradients and therefore need no all-reduce.  The gather is NOT fused into the server's
+    first GEMM here: the loss needs ``concat_latent`` itself (the latent reconstruction term), so it has to exist anyway.
+    ``loss()`` returns this rank's share (own reconstruction + the replicated server terms) whose backward is exact;
+    ``total_loss`` all-reduces the party terms for reporting."""
+
+    def __init__(self, in_features: int, n_parties: int, client_latent_dim: int = 8, *, group=None, seed: int = 0):
+        super().__init__()
+        from ..models.tabular import ClientDecoder, ClientEncoder, ServerVAE
+        self.group, self.n, self.L = group, n_parties, client_latent_dim
+        self.rank = dist.get_rank(group)
+        torch.manual_seed(seed + 1000 + self.rank)
+        self.encoder = ClientEncoder(in_features, client_latent_dim)
+        self.decoder = ClientDecoder(client_latent_dim, in_features)
+        torch.manual_seed(seed)                                  # identical server replica (and noise stream) everywhere
+        self.server_vae = ServerVAE(n_parties * client_latent_dim)
+
+    def forward(self, x_local: torch.Tensor):
+        latent = self.encoder(x_local)
+        concat = _GatherCat.apply(latent, (self.L,) * self.n, self.rank, self.group)
+        recon_concat, mu, logvar = self.server_vae(concat)
+        mine = _SliceScatter.apply(recon_concat, self.rank, self.L, self.n, self.group)
+        return self.decoder(mine), mu, logvar, concat, recon_concat
+
+    def loss(self, x_local, out):
+        recon, mu, logvar, concat, recon_concat = out
+        party = F.mse_loss(recon, x_local, reduction="sum")
+        server = F.mse_loss(recon_concat, concat, reduction="sum") - 0.5 * torch.sum(1 + logvar - mu.pow(2) - logvar.exp())
+        return party + server, party.detach(), server.detach()
+
+
+def train_distributed_vfl_vae(model: DistributedVFLVAE, x_local: torch.Tensor, epochs: int = 1000, lr: float = 1e-3, log=None) -> list[float]:
+    """Full-batch Adam loop of exercise_3.py:191-203 on every rank; returns the per-epoch TOTAL combined loss."""
+    if next(model.parameters()).is_cuda:
+        from ..ops.nn import use_kernels
+        use_kernels(model)
+    from ..ops.optim import make_optimizer
+    opt = make_optimizer(model, "adam", lr=lr)
+    losses = []
+    for epoch in range(epochs):
+        model.train()
+        opt.zero_grad()
+        loss, party, server = model.loss(x_local, model(x_local))
+        loss.backward()
+        opt.step()
+        tot = party.clone()
+        dist.all_reduce(tot, group=model.group)
+        losses.append(float(tot + server))
+        if log is not None:
+            log(epoch, losses[-1])
+    return losses

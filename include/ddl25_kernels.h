@@ -126,6 +126,17 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
 int ddl_gram_tcgen05(const float* updates, int64_t ld, int K, int64_t D, const float* center, float* gram, int64_t ldg,
                      int precise, int n_split, float* scratch, void* stream);
 
+/* ---- operand preparation for ragged layer widths (csrc/elementwise.cu) ------------------------------------------------
+ * (ref: the nn.Linear layers of the tabular models, lab/tutorial_2a/centralized.py:24-28, lab/tutorial_2b/vfl.py:21-22,37-39,
+ *  lab/tutorial_2a/generative-modeling.py:50-75: widths 2..256 that are not multiples of the GEMM's 32-column k-block.)
+ * ddl_pad2d: dst[rows_dst, cols_dst] (row stride ld_dst) = src[rows, cols] zero-padded; column fill_col (>= cols, or -1 for
+ *            none) of the first `rows` rows is set to fill_vec[r] (if non-NULL) else fill_val - a ones column in X / the bias
+ *            in W folds the bias into the GEMM and makes the weight-gradient GEMM produce the bias gradient as well.
+ * ddl_col_sum: out[c] = alpha * sum_r x[r, c] + beta * out[c]  (deterministic). */
+int ddl_pad2d(const float* src, int64_t ld_src, int rows, int cols, float* dst, int64_t ld_dst, int rows_dst, int cols_dst,
+              int fill_col, const float* fill_vec, float fill_val, void* stream);
+int ddl_col_sum(const float* x, int64_t ld, int rows, int cols, float* out, float alpha, float beta, void* stream);
+
 /* ---- Packed MnistCnn engine: G clients trained in lock-step, grouped kernels -------------------
  * (ref: MnistCnn forward/backward + train_epoch, lab/tutorial_1a/hfl_complete.py:39-80, executed
  *  for all clients packed on the GPU at once instead of one client at a time, :365-375).

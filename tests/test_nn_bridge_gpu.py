@@ -122,3 +122,83 @@ def test_kernel_rope_qkv_and_swiglu_match_torch(cuda_lib):
     dh = torch.randn_like(h)
     for a, b in zip(torch.autograd.grad(h, (g, u), dh), torch.autograd.grad(hr, (g, u), dh)):
         assert torch.allclose(a, b, atol=1e-5, rtol=1e-4)
+
+
+@pytest.mark.parametrize("M,K,N,bias", [(64, 30, 64, True), (37, 60, 2, True), (256, 13, 26, True), (100, 48, 31, False), (8, 256, 2, True),
+                                        (1025, 31, 48, True)])
+def test_kernel_linear_ragged_widths(cuda_lib, M, K, N, bias):
+    """The tabular models' layer widths (30 -> 64, 256 -> 2, party slabs of 13 / 26 columns ...): forward, input gradient,
+    weight gradient and bias gradient all come from the tcgen05 GEMM (padded, bias-augmented operands), vs fp32 autograd."""
+    torch.manual_seed(M + K + N)
+    x = torch.randn(M, K, device=DEV, requires_grad=True)
+    lin = torch.nn.Linear(K, N, bias=bias).to(DEV)
+    y0 = lin(x); (y0.sin()).sum().backward()
+    g0 = [x.grad.clone(), lin.weight.grad.clone()] + ([lin.bias.grad.clone()] if bias else [])
+    x.grad = None; lin.zero_grad()
+    from ddl25spring_b200 import ops
+    ops.reset_launch_count()
+    y1 = knn.kernel_linear(x, lin.weight, lin.bias); (y1.sin()).sum().backward()
+    assert ops.launch_count() >= 6                      # pad2d x2 + gemm, pad2d + 2 gemms: all ours
+    torch.testing.assert_close(y1, y0, rtol=1e-4, atol=1e-4)
+    g1 = [x.grad, lin.weight.grad] + ([lin.bias.grad] if bias else [])
+    for a, b in zip(g1, g0):
+        torch.testing.assert_close(a, b, rtol=3e-4, atol=3e-4)
+
+
+def test_tabular_models_train_on_kernels_like_torch(cuda_lib):
+    """HeartDiseaseNN / Autoencoder / VFLNetwork with use_kernels + the fused arena optimizer follow the ATen + torch.optim
+    trajectories (same seeds, dropout off)."""
+    import copy
+    from ddl25spring_b200.models.tabular import Autoencoder, BottomModel, HeartDiseaseNN
+    from ddl25spring_b200.ops.optim import ArenaOptimizer
+    from ddl25spring_b200.parallel import vfl
+    torch.manual_seed(0)
+    x = torch.randn(256, 30, device=DEV)
+    y = torch.randint(0, 2, (256,), device=DEV)
+    a = HeartDiseaseNN(30, p_drop=0.0).to(DEV)
+    b = knn.use_kernels(copy.deepcopy(a))
+    oa, ob = torch.optim.AdamW(a.parameters()), ArenaOptimizer(b, "adamw")
+    for _ in range(5):
+        for net, opt, lf in ((a, oa, F.cross_entropy), (b, ob, knn.kernel_cross_entropy)):
+            opt.zero_grad()
+            loss = lf(net(x), y)
+            loss.backward()
+            opt.step()
+    for p, q in zip(a.parameters(), b.parameters()):
+        torch.testing.assert_close(q, p, rtol=2e-3, atol=2e-4)
+    # VAE: Linear + BatchNorm1d + fused loss + fused Adam
+    from ddl25spring_b200.gen.vae import fused_vae_loss
+    data = torch.randn(192, 31, device=DEV)
+    va = Autoencoder(31, 48, 32, 16).to(DEV)
+    vb = knn.use_kernels(copy.deepcopy(va))
+    oa, ob = torch.optim.Adam(va.parameters(), lr=1e-3), ArenaOptimizer(vb, "adam", lr=1e-3)
+    la = lb = None
+    for i in range(4):
+        for net, opt in ((va, oa), (vb, ob)):
+            torch.manual_seed(100 + i)                      # same reparameterisation noise
+            opt.zero_grad()
+            rec, mu, lv = net(data)
+            loss = fused_vae_loss(rec, data, mu, lv)
+            loss.backward()
+            opt.step()
+            if net is va:
+                la = float(loss)
+            else:
+                lb = float(loss)
+    assert lb == pytest.approx(la, rel=2e-3)
+
+
+def test_vfl_network_runs_on_kernels(cuda_lib):
+    from ddl25spring_b200 import ops
+    from ddl25spring_b200.core.data import SyntheticHeart
+    from ddl25spring_b200.parallel import vfl
+    tab = SyntheticHeart().encoded()
+    parts = vfl.contiguous_raw_partition(tab, 4)
+    torch.manual_seed(0)
+    net = vfl.build_vfl(tab, parts).to(DEV)
+    ops.reset_launch_count()
+    hist = net.train_with_settings(6, 64, 4, parts, tab.x[:640], tab.y[:640])
+    assert net._on_kernels and ops.launch_count() > 100
+    assert hist[-1] < hist[0]
+    acc, loss = net.test(tab.x[640:840], tab.y[640:840])
+    assert float(acc) > 0.5

@@ -111,3 +111,37 @@ def test_distributed_vfl_equals_single_process():
             torch.testing.assert_close(top_sd[k], v, rtol=1e-5, atol=1e-6)
         for k, v in bottoms[r].state_dict().items():
             torch.testing.assert_close(bot_sd[k], v, rtol=1e-5, atol=1e-6)
+
+
+def _dvae_worker(rank, world, epochs):
+    xs = list(torch.randn(200, 28, generator=torch.Generator().manual_seed(11)).split(7, dim=1))   # well-conditioned columns
+    model = vfl.DistributedVFLVAE(7, world, 8, seed=5)
+    torch.manual_seed(99)                                    # the reparameterisation noise stream, identical on every rank
+    losses = vfl.train_distributed_vfl_vae(model, xs[rank], epochs=epochs)
+    return losses, {k: v.clone() for k, v in model.state_dict().items()}
+
+
+@pytest.mark.timeout(200)
+def test_distributed_vfl_vae_equals_single_process():
+    """One party per rank (gather of latents up, slice-scatter of reconstructed latents down, exercise_3.py:128-137) gives the
+    same losses and the same weights as the single-process VFLVAE built from the same initialisation."""
+    world, epochs = 4, 3
+    outs = run_distributed(_dvae_worker, world, (epochs,), timeout=150)
+    xs = list(torch.randn(200, 28, generator=torch.Generator().manual_seed(11)).split(7, dim=1))
+    torch.set_num_threads(1)                                 # same reduction order as the single-threaded worker ranks
+    encs, decs = [], []
+    for r in range(world):
+        torch.manual_seed(5 + 1000 + r)
+        encs.append(ClientEncoder(7, 8)); decs.append(ClientDecoder(8, 7))
+    torch.manual_seed(5)
+    ref = VFLVAE(encs, ServerVAE(32), decs, 8)
+    torch.manual_seed(99)
+    ref_losses = vfl.train_vfl_vae(ref, xs, epochs=epochs)
+    for r, (losses, sd) in enumerate(outs):
+        assert losses == pytest.approx(ref_losses, rel=1e-4)
+        for k, v in ref.server_vae.state_dict().items():
+            torch.testing.assert_close(sd["server_vae." + k], v, rtol=1e-4, atol=1e-5)
+        for k, v in ref.client_encoders[r].state_dict().items():
+            torch.testing.assert_close(sd["encoder." + k], v, rtol=1e-4, atol=1e-5)
+        for k, v in ref.client_decoders[r].state_dict().items():
+            torch.testing.assert_close(sd["decoder." + k], v, rtol=1e-4, atol=1e-5)
