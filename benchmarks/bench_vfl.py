@@ -63,21 +63,38 @@ def main():
     x_local = torch.randn(a.batch, a.emb // 2, generator=g).cuda()
     y = torch.randint(0, 2, (a.batch,), generator=torch.Generator().manual_seed(0)).cuda()
     step_ms = {}
-    for arm in ("fused_kernels", "allgather_aten"):
-        hook = FusedVFLGather(arena, a.batch, dims, a.out) if arm == "fused_kernels" else None
-        net = vfl.DistributedVFL(a.emb // 2, dims, act_on_logits=False, seed=3, gather_linear=hook).cuda()
-        if arm == "fused_kernels":
-            use_kernels(net)
-            opt, lf = ArenaOptimizer(net, "adamw"), kernel_cross_entropy
-        else:
-            opt, lf = torch.optim.AdamW(net.parameters()), torch.nn.functional.cross_entropy
+    from ddl25spring_b200.utils.graphs import GraphedStep
+    hook = None
+    for arm in ("fused_kernels", "fused_kernels_graphed", "allgather_aten", "allgather_aten_graphed"):
+        try:
+            ours, graphed = arm.startswith("fused"), arm.endswith("graphed")
+            if ours and hook is None:
+                hook = FusedVFLGather(arena, a.batch, dims, a.out)
+            net = vfl.DistributedVFL(a.emb // 2, dims, act_on_logits=False, seed=3, gather_linear=hook if ours else None).cuda()
+            net.bottom.dropout.p = 0.0
+            if ours:
+                use_kernels(net)
+                opt, lf = ArenaOptimizer(net, "adamw", capturable=graphed), kernel_cross_entropy
+            else:
+                opt, lf = torch.optim.AdamW(net.parameters(), capturable=graphed), torch.nn.functional.cross_entropy
 
-        def step():
-            opt.zero_grad()
-            lf(net(x_local), y).backward()
-            opt.step()
-        step_ms[arm] = round(t(step) / 1e3, 4)
-    r = {"world": world, "train_step_ms": step_ms, "train_samples_per_s": {k: round(a.batch / v * 1e3, 1) for k, v in step_ms.items()}, "batch": a.batch, "emb_per_party": a.emb, "top_fc1_out": a.out, "us": {"fused": round(t(fused), 2), "nccl_allgather_cat_linear": round(t(nccl), 2)}}
+            def one(xb, yb):
+                opt.zero_grad()
+                loss = lf(net(xb), yb)
+                loss.backward()
+                opt.step()
+                return loss.detach()
+            if graphed:                       # forward, gather, backward, fused reduce and optimizer replayed as ONE graph per rank
+                gs = GraphedStep(one, (x_local, y))
+                step = lambda: gs(x_local, y)
+            else:
+                step = lambda: one(x_local, y)
+            step_ms[arm] = round(t(step) / 1e3, 4)
+        except Exception as e:
+            step_ms[arm] = None
+            r_err = f"{type(e).__name__}: {e}"[:200]
+            print(f"[bench_vfl] arm {arm} failed: {r_err}", file=sys.stderr)
+    r = {"world": world, "train_step_ms": step_ms, "train_samples_per_s": {k: (round(a.batch / v * 1e3, 1) if v else None) for k, v in step_ms.items()}, "batch": a.batch, "emb_per_party": a.emb, "top_fc1_out": a.out, "us": {"fused": round(t(fused), 2), "nccl_allgather_cat_linear": round(t(nccl), 2)}}
     ref = nccl()
     fused()
     r["max_abs_err_vs_fp32"] = float((out - ref).abs().max())

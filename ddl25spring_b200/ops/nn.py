@@ -156,6 +156,13 @@ def kernel_soft_cross_entropy(logits: torch.Tensor, target: torch.Tensor):
     return _SoftXentFn.apply(logits.contiguous(), target.contiguous().float())
 
 
+class KernelSoftCrossEntropy(nn.Module):
+    """Drop-in for ``nn.CrossEntropyLoss()`` with float targets (module form of :func:`kernel_soft_cross_entropy`)."""
+
+    def forward(self, logits, target):
+        return kernel_soft_cross_entropy(logits, target)
+
+
 def kernel_causal_lm_loss(logits: torch.Tensor, tokens: torch.Tensor):
     """Shifted next-token loss (lab/tutorial_1b/primer/intro.py:29) through the fused kernel."""
     V = logits.shape[-1]

@@ -22,8 +22,12 @@ _DEFAULT_WD = {"sgd": 0.0, "adam": 0.0, "adamw": 0.01}
 
 class ArenaOptimizer:
     def __init__(self, module: nn.Module, kind: str = "adamw", lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
-                 weight_decay: float | None = None, momentum: float = 0.0):
+                 weight_decay: float | None = None, momentum: float = 0.0, capturable: bool = False):
         assert kind in ("sgd", "adam", "adamw")
+        # capturable: the Adam step counter lives in a device int (bumped by a one-element kernel), so zero_grad() + step() are
+        # plain launches with no per-call host value and a whole training step can be captured into a CUDA graph
+        self.capturable = capturable
+        self.step_t = None
         self.module, self.kind, self.lr, self.betas, self.eps, self.momentum = module, kind, lr, betas, eps, momentum
         self.wd = _DEFAULT_WD[kind] if weight_decay is None else weight_decay
         self.arena: FlatArena | None = None
@@ -40,6 +44,8 @@ class ArenaOptimizer:
                 self.m = torch.zeros_like(a.flat)
             if self.kind != "sgd":
                 self.v = torch.zeros_like(a.flat)
+            if self.capturable and a.flat.is_cuda:
+                self.step_t = torch.zeros((), dtype=torch.int32, device=a.flat.device)
         return a
 
     def _rebind_grads(self, a: FlatArena) -> None:
@@ -67,7 +73,11 @@ class ArenaOptimizer:
         if self.kind == "sgd":
             sgd_step(a.flat, a.grad, self.lr, self.wd, self.momentum, self.m)
         else:
-            adam_step(a.flat, a.grad, self.m, self.v, self.steps, self.lr, self.betas[0], self.betas[1], self.eps, self.wd,
+            step = self.steps
+            if self.step_t is not None:
+                self.step_t.add_(1)
+                step = self.step_t
+            adam_step(a.flat, a.grad, self.m, self.v, step, self.lr, self.betas[0], self.betas[1], self.eps, self.wd,
                       decoupled=self.kind == "adamw")
 
     def state_dict(self) -> dict:

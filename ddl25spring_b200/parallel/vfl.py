@@ -115,13 +115,13 @@ class VFLNetwork(nn.Module):
         registered parameters (the frozen-bottoms quirk is kept: unregistered bottoms are not in the arena)."""
         if self._on_kernels or torch.device(device).type != "cuda":
             return
-        from ..ops.nn import kernel_soft_cross_entropy, use_kernels
+        from ..ops.nn import KernelSoftCrossEntropy, use_kernels
         from ..ops.optim import ArenaOptimizer
         use_kernels(self)
         for m in self.bottom_models:
             use_kernels(m)
         self.optimizer = ArenaOptimizer(self, "adamw")
-        self.criterion = kernel_soft_cross_entropy
+        self.criterion = KernelSoftCrossEntropy()
         self._on_kernels = True
 
     def forward(self, x: Sequence[torch.Tensor]) -> torch.Tensor:
