@@ -16,21 +16,27 @@ namespace {
 template <bool BWD>
 __global__ void __launch_bounds__(256) rope_qkv_kernel(float* __restrict__ qkv, const float* __restrict__ cs, const float* __restrict__ sn,
                                                        float* __restrict__ q, float* __restrict__ k, float* __restrict__ v, int B, int T,
-                                                       int H, int hd) {
+                                                       int H, int hd, int hp) {
+  // hp >= hd: row pitch of q / k / v.  Forward writes zeros into the pad columns [hd, hp) so the tensors are directly usable as
+  // MN-major operands of the attention GEMMs (attention_tc.cu); backward ignores them.
   pdl_launch_dependents();
   pdl_wait();
-  const int P = hd / 2;
-  const int64_t total = (int64_t)B * T * 3 * H * P;
+  const int P = hd / 2, PP = hp / 2;
+  const int64_t total = (int64_t)B * T * 3 * H * PP;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
     int64_t r = e;
-    const int p = (int)(r % P); r /= P;
+    const int p = (int)(r % PP); r /= PP;
     const int h = (int)(r % H); r /= H;
     const int w = (int)(r % 3); r /= 3;
     const int t = (int)(r % T);
     const int b = (int)(r / T);
-    float2* src = reinterpret_cast<float2*>(qkv) + e;                                   // [b, t, w, h, p] pairs are contiguous
     float* dstbase = w == 0 ? q : (w == 1 ? k : v);
-    float2* dst = reinterpret_cast<float2*>(dstbase + (((int64_t)b * H + h) * T + t) * hd) + p;
+    float2* dst = reinterpret_cast<float2*>(dstbase + (((int64_t)b * H + h) * T + t) * hp) + p;
+    if (p >= P) {
+      if (!BWD) *dst = make_float2(0.f, 0.f);
+      continue;
+    }
+    float2* src = reinterpret_cast<float2*>(qkv) + ((((int64_t)b * T + t) * 3 + w) * H + h) * P + p;   // [b, t, w, h, p] pairs
     const float c = w < 2 ? cs[t * P + p] : 1.f, s = w < 2 ? sn[t * P + p] : 0.f;
     if (!BWD) {
       const float2 x = *src;
@@ -88,15 +94,17 @@ int blocks_for(int64_t work) {
 extern "C" {
 
 int ddl_rope_qkv(float* qkv, const float* cos_tab, const float* sin_tab, float* q, float* k, float* v, int B, int T, int H, int hd,
-                 int backward, void* stream) {
+                 int hd_pitch, int backward, void* stream) {
   DDL_REQUIRE(hd % 2 == 0 && B > 0 && T > 0 && H > 0, "rope_qkv: head dim must be even");
-  const int64_t total = (int64_t)B * T * 3 * H * (hd / 2);
+  if (hd_pitch <= 0) hd_pitch = hd;
+  DDL_REQUIRE(hd_pitch >= hd && hd_pitch % 2 == 0, "rope_qkv: row pitch %d must be even and >= head dim %d", hd_pitch, hd);
+  const int64_t total = (int64_t)B * T * 3 * H * (hd_pitch / 2);
   if (backward)
     DDL_CUDA_CHECK(ddl_launch_pdl(rope_qkv_kernel<true>, dim3(blocks_for(total)), dim3(256), 0, (cudaStream_t)stream, qkv, cos_tab, sin_tab,
-                                  q, k, v, B, T, H, hd));
+                                  q, k, v, B, T, H, hd, hd_pitch));
   else
     DDL_CUDA_CHECK(ddl_launch_pdl(rope_qkv_kernel<false>, dim3(blocks_for(total)), dim3(256), 0, (cudaStream_t)stream, qkv, cos_tab, sin_tab,
-                                  q, k, v, B, T, H, hd));
+                                  q, k, v, B, T, H, hd, hd_pitch));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

@@ -263,11 +263,73 @@ class _CausalAttnFn(torch.autograd.Function):
         return dq, dk, dv, None
 
 
+def _padded_heads(t: torch.Tensor, HP: int):
+    """[B, H, T, hd] -> ([G, T, HP] zero-padded, contiguous).  Free when ``t`` is the [..., :hd] view of a padded buffer written
+    by the fused QKV split + RoPE kernel; otherwise one pad2d launch."""
+    B, H, T, hd = t.shape
+    if hd == HP and t.is_contiguous():
+        return t.view(B * H, T, HP)
+    if t.stride() == (H * T * HP, T * HP, HP, 1):
+        return t.as_strided((B * H, T, HP), (T * HP, HP, 1))
+    tc = t.contiguous().view(B * H * T, hd)
+    return pad2d(tc, B * H * T, HP).view(B * H, T, HP)
+
+
+class _CausalAttnGemmFn(torch.autograd.Function):
+    """Causal attention with every product on the tcgen05 GEMM (csrc/attention_tc.cu explains the kernel sequence)."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, scale):
+        B, H, T, hd = q.shape
+        HP = _ceil32(hd)
+        qp, kp, vp = _padded_heads(q, HP), _padded_heads(k, HP), _padded_heads(v, HP)
+        L = _lib.lib()
+        S = gemm(qp, kp, alpha=scale, precise=True)                                   # [G, T, T] = scale Q K^T
+        _lib.check(L.ddl_causal_softmax(_lib.p(S), _lib.i64(B * H * T), int(T), _lib.stream()), "ddl_causal_softmax")
+        op = gemm(S, vp, b_mn=True, precise=True)                                     # [G, T, HP] = P V
+        ctx.save_for_backward(qp, kp, vp, S, op)
+        ctx.dims, ctx.scale = (B, H, T, hd, HP), scale
+        return op.view(B, H, T, HP)[..., :hd]
+
+    @staticmethod
+    def backward(ctx, go):
+        qp, kp, vp, P, op = ctx.saved_tensors
+        B, H, T, hd, HP = ctx.dims
+        G = B * H
+        L = _lib.lib()
+        if go.stride(3) != 1:
+            go = go.contiguous()
+        dop = torch.empty(G, T, HP, device=go.device, dtype=torch.float32)
+        delta = torch.empty(G * T, device=go.device, dtype=torch.float32)
+        _lib.check(L.ddl_attn_bwd_prep(_lib.p(go), _lib.i64(go.stride(0)), _lib.i64(go.stride(1)), _lib.i64(go.stride(2)), _lib.p(op),
+                                       _lib.p(dop), _lib.p(delta), int(B), int(H), int(T), int(hd), int(HP), _lib.stream()),
+                   "ddl_attn_bwd_prep")
+        dS = gemm(dop, vp, precise=True)                                              # dP = dO V^T
+        _lib.check(L.ddl_attn_ds(_lib.p(P), _lib.p(dS), _lib.p(delta), _lib.i64(G * T), int(T), _lib.f32(ctx.scale), _lib.stream()),
+                   "ddl_attn_ds")
+        dv = gemm(P, dop, a_mn=True, b_mn=True, precise=True)                         # P^T dO
+        dq = gemm(dS, kp, b_mn=True, precise=True)                                    # dS K
+        dk = gemm(dS, qp, a_mn=True, b_mn=True, precise=True)                         # dS^T Q
+        view = lambda t: t.view(B, H, T, HP)[..., :hd]
+        return view(dq), view(dk), view(dv), None
+
+
 def kernel_causal_attention(q, k, v):
-    """softmax(q k^T / sqrt(D) + causal mask) v for [B, H, T, D] tensors (K16)."""
-    D = q.shape[-1]
-    if not q.is_cuda or q.dtype != torch.float32 or D not in (16, 32, 48, 64):
+    """softmax(q k^T / sqrt(D) + causal mask) v for [B, H, T, D] tensors (K16).  T a multiple of 32: grouped tcgen05 GEMMs +
+    row-wise softmax kernels; other T (D in 16/32/48/64): the CUDA-core flash kernels."""
+    D, T = q.shape[-1], q.shape[-2]
+    if not q.is_cuda or q.dtype != torch.float32:
         return F.scaled_dot_product_attention(q, k, v, is_causal=True)
+    if T % 32 == 0 and D % 2 == 0:
+        return _CausalAttnGemmFn.apply(q, k, v, 1.0 / (D ** 0.5))
+    if D not in (16, 32, 48, 64):
+        return F.scaled_dot_product_attention(q, k, v, is_causal=True)
+    return _CausalAttnFn.apply(q, k, v, 1.0 / (D ** 0.5))
+
+
+def kernel_causal_attention_simt(q, k, v):
+    """The CUDA-core flash kernels (attention.cu), kept selectable for comparisons."""
+    D = q.shape[-1]
     return _CausalAttnFn.apply(q, k, v, 1.0 / (D ** 0.5))
 
 
@@ -276,27 +338,37 @@ class _RopeQkvFn(torch.autograd.Function):
     def forward(ctx, qkv, cos, sin, H):
         B, T, C3 = qkv.shape
         hd = C3 // (3 * H)
-        qkv = qkv.contiguous()
-        q = torch.empty((B, H, T, hd), device=qkv.device, dtype=torch.float32)
+        HP = _ceil32(hd)                    # q, k, v are written with the head dim zero-padded to a multiple of 32: legal
+        qkv = qkv.contiguous()              # MN-major operands for the attention GEMMs; callers see [..., :hd] views
+        q = torch.empty((B, H, T, HP), device=qkv.device, dtype=torch.float32)
         k, v = torch.empty_like(q), torch.empty_like(q)
         _lib.check(_lib.lib().ddl_rope_qkv(_lib.p(qkv), _lib.p(cos), _lib.p(sin), _lib.p(q), _lib.p(k), _lib.p(v), int(B), int(T), int(H),
-                                           int(hd), 0, _lib.stream()), "ddl_rope_qkv")
+                                           int(hd), int(HP), 0, _lib.stream()), "ddl_rope_qkv")
         ctx.save_for_backward(cos, sin)
-        ctx.dims = (B, T, H, hd)
-        return q, k, v
+        ctx.dims = (B, T, H, hd, HP)
+        return q[..., :hd], k[..., :hd], v[..., :hd]
 
     @staticmethod
     def backward(ctx, gq, gk, gv):
         cos, sin = ctx.saved_tensors
-        B, T, H, hd = ctx.dims
+        B, T, H, hd, HP = ctx.dims
         g = torch.empty((B, T, 3 * H * hd), device=gq.device, dtype=torch.float32)
-        _lib.check(_lib.lib().ddl_rope_qkv(_lib.p(g), _lib.p(cos), _lib.p(sin), _lib.p(gq.contiguous()), _lib.p(gk.contiguous()),
-                                           _lib.p(gv.contiguous()), int(B), int(T), int(H), int(hd), 1, _lib.stream()), "ddl_rope_qkv")
+
+        def pitched(t):                     # gradients arrive either as [..., :hd] views of HP-pitched buffers, or dense
+            if t.stride() == (H * T * HP, T * HP, HP, 1):
+                return t, HP
+            return t.contiguous(), hd
+        (gq, pq), (gk, pk), (gv, pv) = pitched(gq), pitched(gk), pitched(gv)
+        if not (pq == pk == pv):
+            gq, gk, gv, pq = gq.contiguous(), gk.contiguous(), gv.contiguous(), hd
+        _lib.check(_lib.lib().ddl_rope_qkv(_lib.p(g), _lib.p(cos), _lib.p(sin), _lib.p(gq), _lib.p(gk), _lib.p(gv), int(B), int(T), int(H),
+                                           int(hd), int(pq), 1, _lib.stream()), "ddl_rope_qkv")
         return g, None, None, None
 
 
 def kernel_rope_qkv(qkv, cos, sin, n_heads: int):
-    """``qkv`` [B, T, 3*H*hd] -> rotary-embedded q, k and v, each [B, H, T, hd] contiguous (one kernel each way)."""
+    """``qkv`` [B, T, 3*H*hd] -> rotary-embedded q, k and v, each [B, H, T, hd] (one kernel each way); the returned tensors
+    are views of buffers whose head dim is zero-padded to a multiple of 32."""
     return _RopeQkvFn.apply(qkv, cos.contiguous(), sin.contiguous(), n_heads)
 
 

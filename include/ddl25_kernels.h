@@ -263,6 +263,17 @@ int ddl_causal_attention_fwd(const float* q, const float* k, const float* v, flo
 int ddl_causal_attention_bwd(const float* q, const float* k, const float* v, const float* o, const float* dO, const float* lse,
                              float* dq, float* dk, float* dv, float* delta_scratch, int BH, int T, int D, float scale, void* stream);
 
+/* ---- K16 on the tensor cores (csrc/attention_tc.cu): the row-wise kernels between the grouped tcgen05 GEMMs of causal attention
+ * (ref: attention inside simplellm's LLaMA blocks, lab/tutorial_1b/primer/intro.py:17,28).  S, P, dP, dS: [rows = G*T, T];
+ * O, dO_padded: [G*T, HP] (head dim zero-padded to HP).
+ * ddl_causal_softmax: row r of S (already scaled) becomes softmax over columns 0 .. r % T, zeros after (in place).
+ * ddl_attn_bwd_prep : dO_padded = zero-padded copy of dO[b, h, t, 0:hd] (element strides given); delta[row] = sum_d dO * O.
+ * ddl_attn_ds       : dP <- scale * P * (dP - delta[row])  (in place). */
+int ddl_causal_softmax(float* S, int64_t rows, int T, void* stream);
+int ddl_attn_bwd_prep(const float* dO, int64_t stride_b, int64_t stride_h, int64_t stride_t, const float* O_padded, float* dO_padded,
+                      float* delta, int B, int H, int T, int hd, int HP, void* stream);
+int ddl_attn_ds(const float* P, float* dP_inout, const float* delta, int64_t rows, int T, float scale, void* stream);
+
 /* ---- K3 fused: all-gather of client updates + Gram GEMM in one kernel [north star] --------------------------------------
  * gram[K x K] = U[:, d0:d1] U[:, d0:d1]^T with K = n_parts * rows_per_part and the rows of U spread over GPUs: part_ptrs[p]
  * (HOST array of device pointers, may be peer-mapped) is the base of GPU p's rows_per_part rows (row stride ld floats).
@@ -288,7 +299,7 @@ int ddl_u8_normalize(const unsigned char* in, float* out, int64_t n, float mean,
  * qkv: [B, T, 3, H, hd]; q, k, v: [B, H, T, hd]; cos/sin: [>= T, hd/2].  backward == 0: qkv -> q, k, v (q, k rotated);
  * backward != 0: dq, dk, dv (passed as q, k, v) -> d(qkv) written into `qkv`. */
 int ddl_rope_qkv(float* qkv, const float* cos_tab, const float* sin_tab, float* q, float* k, float* v, int B, int T, int H, int hd,
-                 int backward, void* stream);
+                 int hd_pitch /* row pitch of q, k, v (>= hd; pad columns are written as zeros); <= 0: hd */, int backward, void* stream);
 int ddl_swiglu_fwd(const float* g, const float* u, float* h, int64_t n, void* stream);               /* h = silu(g) * u */
 int ddl_swiglu_bwd(const float* g, const float* u, const float* dh, float* dg, float* du, int64_t n, void* stream);
 

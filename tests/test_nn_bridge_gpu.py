@@ -81,8 +81,9 @@ def test_kernel_batchnorm_matches_torch(cuda_lib, shape):
         torch.testing.assert_close(knn.kernel_batch_norm(x, b), a(x), rtol=1e-4, atol=1e-5)
 
 
-@pytest.mark.parametrize("B,H,T,D", [(3, 6, 256, 48), (2, 2, 100, 32), (1, 4, 300, 64)])
+@pytest.mark.parametrize("B,H,T,D", [(3, 6, 256, 48), (2, 2, 100, 32), (1, 4, 300, 64), (2, 4, 128, 64), (1, 2, 64, 16), (1, 3, 512, 48)])
 def test_kernel_causal_attention(cuda_lib, B, H, T, D):
+    """T % 32 == 0: grouped tcgen05 GEMMs (3xTF32) + row-wise softmax kernels; other T: the CUDA-core flash kernels."""
     torch.manual_seed(0)
     q, k, v = (torch.randn(B, H, T, D, device=DEV, requires_grad=True) for _ in range(3))
     ref = F.scaled_dot_product_attention(q.double(), k.double(), v.double(), is_causal=True)
@@ -96,6 +97,26 @@ def test_kernel_causal_attention(cuda_lib, B, H, T, D):
     torch.testing.assert_close(out.double(), ref, rtol=1e-4, atol=1e-5)
     for t, gg in zip((q, k, v), g):
         torch.testing.assert_close(t.grad.double(), gg.double(), rtol=1e-3, atol=2e-5)
+
+
+def test_rope_then_tensor_core_attention_chain(cuda_lib):
+    """The fused QKV split + RoPE kernel hands 32-column-padded q / k / v to the attention GEMMs as views: the chain equals
+    the PyTorch statement, forward and gradient of the packed qkv."""
+    from ddl25spring_b200.models.llama import apply_rope, rope_tables
+    torch.manual_seed(0)
+    B, T, H, hd = 2, 128, 6, 48
+    cos, sin = rope_tables(hd, 256, device=DEV)
+    qkv = torch.randn(B, T, 3 * H * hd, device=DEV, requires_grad=True)
+    q, k, v = knn.kernel_rope_qkv(qkv, cos, sin, H)
+    assert q.shape == (B, H, T, hd) and q.stride(2) == 64
+    o = knn.kernel_causal_attention(q, k, v)
+    w = torch.randn(B, H, T, hd, device=DEV)
+    (g1,) = torch.autograd.grad((o * w).sum(), qkv)
+    qr, kr, vr = qkv.view(B, T, 3, H, hd).permute(2, 0, 3, 1, 4)
+    orf = F.scaled_dot_product_attention(apply_rope(qr, cos, sin), apply_rope(kr, cos, sin), vr, is_causal=True)
+    (g2,) = torch.autograd.grad((orf * w).sum(), qkv)
+    torch.testing.assert_close(o, orf, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(g1, g2, rtol=1e-3, atol=2e-5)
 
 
 @pytest.mark.gpu
