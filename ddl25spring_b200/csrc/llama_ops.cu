@@ -127,3 +127,61 @@ int ddl_swiglu_bwd(const float* g, const float* u, const float* dh, float* dg, f
 }
 
 }  // extern "C"
+
+// ---- embedding: out[n, :] = W[tok[n], :] and its scatter-add backward dW[tok[n], :] += g[n, :] (rows equal to padding_idx get
+// no gradient).  One warp per token row, 128-bit accesses; the backward uses red.global.add (token rows repeat within a batch).
+// Replaces (reference): nn.Embedding inside simplellm's LLama / LLamaFirstStage.embed (lab/tutorial_1b/PP/1F1B/intro_PP_1F1B.py:53).
+namespace {
+
+__global__ void __launch_bounds__(256) embedding_fwd_kernel(const float* __restrict__ W, const int64_t* __restrict__ tok, float* __restrict__ out,
+                                                            int64_t n, int d4, int64_t vocab) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int lane = threadIdx.x & 31;
+  const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= n) return;
+  int64_t t = tok[r];
+  t = t < 0 ? 0 : (t >= vocab ? vocab - 1 : t);
+  const float4* src = reinterpret_cast<const float4*>(W) + t * d4;
+  float4* dst = reinterpret_cast<float4*>(out) + r * d4;
+  for (int c = lane; c < d4; c += 32) dst[c] = src[c];
+}
+
+__global__ void __launch_bounds__(256) embedding_bwd_kernel(const float* __restrict__ g, const int64_t* __restrict__ tok, float* __restrict__ dW,
+                                                            int64_t n, int d, int64_t vocab, int64_t padding_idx) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int lane = threadIdx.x & 31;
+  const int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= n) return;
+  const int64_t t = tok[r];
+  if (t == padding_idx || t < 0 || t >= vocab) return;
+  const float* src = g + r * d;
+  float* dst = dW + t * d;
+  for (int c = lane; c < d; c += 32) atomicAdd(dst + c, src[c]);
+}
+
+}  // namespace
+
+extern "C" {
+
+int ddl_embedding_fwd(const float* W, const int64_t* tokens, float* out, int64_t n_tokens, int d, int64_t vocab, void* stream) {
+  DDL_REQUIRE(d % 4 == 0 && d > 0 && vocab > 0, "embedding dim must be a multiple of 4");
+  if (n_tokens == 0) return DDL_OK;
+  DDL_CUDA_CHECK(ddl_launch_pdl(embedding_fwd_kernel, dim3((unsigned)((n_tokens + 7) / 8)), dim3(256), 0, (cudaStream_t)stream, W, tokens, out,
+                                n_tokens, d / 4, vocab));
+  DDL_LAUNCH_CHECK();
+  return DDL_OK;
+}
+
+int ddl_embedding_bwd(const float* grad_out, const int64_t* tokens, float* dW_accum, int64_t n_tokens, int d, int64_t vocab,
+                      int64_t padding_idx, void* stream) {
+  DDL_REQUIRE(d > 0 && vocab > 0, "bad embedding shape");
+  if (n_tokens == 0) return DDL_OK;
+  DDL_CUDA_CHECK(ddl_launch_pdl(embedding_bwd_kernel, dim3((unsigned)((n_tokens + 7) / 8)), dim3(256), 0, (cudaStream_t)stream, grad_out, tokens,
+                                dW_accum, n_tokens, d, vocab, padding_idx));
+  DDL_LAUNCH_CHECK();
+  return DDL_OK;
+}
+
+}  // extern "C"

@@ -114,24 +114,27 @@ class KernelLinear(nn.Linear):
 
 class _XentFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, logits, target, ignore_index):
+    def forward(ctx, logits, target, ignore_index, n_valid):
         from . import softmax_xent
-        n_valid = (target != ignore_index).sum().clamp_min(1)
+        if n_valid is None:
+            n_valid = (target != ignore_index).sum().clamp_min(1)
         loss, grad = softmax_xent(logits, target, reduction="sum", want_grad=True, ignore_index=ignore_index)
-        ctx.save_for_backward(grad, n_valid)
+        ctx.save_for_backward(grad)
+        ctx.n_valid = n_valid
         return loss / n_valid
 
     @staticmethod
     def backward(ctx, g):
-        grad, n_valid = ctx.saved_tensors
-        return grad * (g / n_valid), None, None
+        (grad,) = ctx.saved_tensors
+        return grad * (g / ctx.n_valid), None, None, None
 
 
-def kernel_cross_entropy(logits: torch.Tensor, target: torch.Tensor, ignore_index: int = -100):
-    """mean cross-entropy over the rows whose target != ignore_index (``F.cross_entropy`` semantics)."""
+def kernel_cross_entropy(logits: torch.Tensor, target: torch.Tensor, ignore_index: int = -100, n_valid: int | None = None):
+    """mean cross-entropy over the rows whose target != ignore_index (``F.cross_entropy`` semantics).  ``n_valid``: the number
+    of such rows when the caller knows it (saves the device-side count)."""
     if not logits.is_cuda or logits.dtype != torch.float32:
         return F.cross_entropy(logits, target, ignore_index=ignore_index)
-    return _XentFn.apply(logits.contiguous(), target.contiguous(), ignore_index)
+    return _XentFn.apply(logits.contiguous(), target.contiguous(), ignore_index, n_valid)
 
 
 class _SoftXentFn(torch.autograd.Function):
@@ -164,9 +167,14 @@ class KernelSoftCrossEntropy(nn.Module):
 
 
 def kernel_causal_lm_loss(logits: torch.Tensor, tokens: torch.Tensor):
-    """Shifted next-token loss (lab/tutorial_1b/primer/intro.py:29) through the fused kernel."""
-    V = logits.shape[-1]
-    return kernel_cross_entropy(logits[:, :-1].reshape(-1, V), tokens.to(logits.device)[:, 1:].reshape(-1))
+    """Shifted next-token loss (lab/tutorial_1b/primer/intro.py:29) through the fused kernel.  The logits are used in place
+    ([B*T, V], no sliced copy): row (b, t) is scored against token t + 1 and the last position of every sequence is ignored."""
+    B, T, V = logits.shape
+    if not logits.is_cuda:
+        return kernel_cross_entropy(logits[:, :-1].reshape(-1, V), tokens.to(logits.device)[:, 1:].reshape(-1))
+    tgt = torch.full((B, T), -100, dtype=torch.int64, device=logits.device)
+    tgt[:, :-1] = tokens.to(logits.device)[:, 1:]
+    return kernel_cross_entropy(logits.reshape(B * T, V), tgt.view(-1), n_valid=B * (T - 1))
 
 
 class _RMSNormFn(torch.autograd.Function):
@@ -397,6 +405,40 @@ def kernel_swiglu(g, u):
     return _SwiGluFn.apply(g, u)
 
 
+class _EmbeddingFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, tokens, weight, padding_idx):
+        tok = tokens.contiguous().view(-1)
+        V, d = weight.shape
+        out = torch.empty(tok.numel(), d, device=weight.device, dtype=torch.float32)
+        _lib.check(_lib.lib().ddl_embedding_fwd(_lib.p(weight), _lib.p(tok), _lib.p(out), _lib.i64(tok.numel()), int(d), _lib.i64(V),
+                                                _lib.stream()), "ddl_embedding_fwd")
+        ctx.save_for_backward(tok)
+        ctx.shape, ctx.pad = (V, d), -1 if padding_idx is None else int(padding_idx)
+        return out.view(*tokens.shape, d)
+
+    @staticmethod
+    def backward(ctx, g):
+        (tok,) = ctx.saved_tensors
+        V, d = ctx.shape
+        g2 = g.reshape(-1, d)
+        if g2.stride(1) != 1 or g2.stride(0) != d:
+            g2 = g2.contiguous()
+        dW = torch.zeros(V, d, device=g.device, dtype=torch.float32)
+        _lib.check(_lib.lib().ddl_embedding_bwd(_lib.p(g2), _lib.p(tok), _lib.p(dW), _lib.i64(tok.numel()), int(d), _lib.i64(V),
+                                                _lib.i64(ctx.pad), _lib.stream()), "ddl_embedding_bwd")
+        return None, dW, None
+
+
+def kernel_embedding(tokens: torch.Tensor, emb: nn.Embedding):
+    """``nn.Embedding`` forward (row gather) and backward (scatter-add into the weight gradient) on kernels."""
+    w = emb.weight
+    if not w.is_cuda or w.dtype != torch.float32 or w.shape[1] % 4 or tokens.dtype != torch.int64 or emb.max_norm is not None \
+            or not w.is_contiguous():
+        return F.embedding(tokens, w, emb.padding_idx)
+    return _EmbeddingFn.apply(tokens.to(w.device), w, emb.padding_idx)
+
+
 def use_kernels(model: nn.Module, precise: bool = True) -> nn.Module:
     """Route every ``nn.Linear`` (and RMSNorm of models/llama.py) of ``model`` through the kernels, in place."""
     from ..models.llama import Attention, GatedMLP, RMSNorm
@@ -408,6 +450,8 @@ def use_kernels(model: nn.Module, precise: bool = True) -> nn.Module:
             mod.forward = (lambda m: (lambda x: kernel_rms_norm(x, m.weight, m.eps)))(mod)
         elif isinstance(mod, (nn.BatchNorm1d, nn.BatchNorm2d)):
             mod.forward = (lambda m: (lambda x: kernel_batch_norm(x, m)))(mod)
+        elif type(mod) is nn.Embedding:
+            mod.forward = (lambda m: (lambda tokens: kernel_embedding(tokens, m)))(mod)
         elif isinstance(mod, Attention):
             mod.attn_fn = kernel_causal_attention
             mod.qkv_fn = kernel_rope_qkv

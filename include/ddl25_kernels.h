@@ -300,6 +300,11 @@ int ddl_u8_normalize(const unsigned char* in, float* out, int64_t n, float mean,
  * backward != 0: dq, dk, dv (passed as q, k, v) -> d(qkv) written into `qkv`. */
 int ddl_rope_qkv(float* qkv, const float* cos_tab, const float* sin_tab, float* q, float* k, float* v, int B, int T, int H, int hd,
                  int hd_pitch /* row pitch of q, k, v (>= hd; pad columns are written as zeros); <= 0: hd */, int backward, void* stream);
+/* embedding gather out[n, :] = W[tokens[n], :] and its scatter-add backward dW[tokens[n], :] += grad_out[n, :] (dW_accum is
+ * accumulated into: zero it first; rows equal to padding_idx, or -1 for none, receive nothing).  d % 4 == 0. */
+int ddl_embedding_fwd(const float* W, const int64_t* tokens, float* out, int64_t n_tokens, int d, int64_t vocab, void* stream);
+int ddl_embedding_bwd(const float* grad_out, const int64_t* tokens, float* dW_accum, int64_t n_tokens, int d, int64_t vocab,
+                      int64_t padding_idx, void* stream);
 int ddl_swiglu_fwd(const float* g, const float* u, float* h, int64_t n, void* stream);               /* h = silu(g) * u */
 int ddl_swiglu_bwd(const float* g, const float* u, const float* dh, float* dg, float* du, int64_t n, void* stream);
 
