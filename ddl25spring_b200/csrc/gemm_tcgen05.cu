@@ -37,6 +37,13 @@ struct Epilogue {
   float* C;             // output (or partials scratch when n_split > 1)
   int64_t ldc;
   int64_t c_group_stride;
+  // split-K with in-kernel fix-up: every split CTA stores its raw partial tile, bumps the tile's counter, and the CTA that
+  // arrives LAST sums the partials in split order (deterministic), applies bias + activation and writes the final tile -
+  // no separate reduce launch.  counters == nullptr: the caller runs splitk_reduce_kernel afterwards.
+  int* counters;        // one int per output tile (zero before the launch; the last CTA resets it)
+  float* C_final;       // final output of the fix-up (C then points at the partials)
+  int64_t ldc_final;
+  int64_t c_group_stride_final;
   const float* bias;    // per-N bias or null
   int64_t bias_group_stride;
   int act;              // 0 none, 1 relu, 2 leaky relu
@@ -368,6 +375,51 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
       }
       __syncwarp();
     }
+    if (n_split > 1 && epi.counters != nullptr) {
+      // ---- split-K fix-up by the last-arriving CTA of this output tile
+      int* flag = reinterpret_cast<int*>(tmem_slot + 1);
+      __threadfence();                                           // this CTA's partial tile is visible device-wide ...
+      asm volatile("bar.sync 1, 128;" ::: "memory");             // ... for all four epilogue warps, before the arrival is counted
+      const int G = gridDim.z / n_split;
+      const int tile = (g * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+      if (et == 0) *flag = (atomicAdd(epi.counters + tile, 1) == n_split - 1);
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (*flag) {
+        __threadfence();
+        const int rows = (M - m0) < BM ? (M - m0) : BM;
+        const int cols = (N - n0) < BN ? (N - n0) : BN;
+        const int64_t sstride = (int64_t)G * M * N;
+        const float* pbase = epi.C + (int64_t)g * M * N + (int64_t)m0 * N + n0;
+        float* fin = epi.C_final + (int64_t)g * epi.c_group_stride_final + (int64_t)m0 * epi.ldc_final + n0;
+        const float* fbias = epi.bias ? epi.bias + (int64_t)g * epi.bias_group_stride + n0 : nullptr;
+        const bool v4 = (N % 4 == 0) && (n0 % 4 == 0) && (epi.ldc_final % 4 == 0) && (epi.c_group_stride_final % 4 == 0) &&
+                        ((reinterpret_cast<uintptr_t>(epi.C) & 15) == 0) && ((reinterpret_cast<uintptr_t>(epi.C_final) & 15) == 0);
+        if (v4) {
+          const int c4 = cols / 4;
+          for (int i = et; i < rows * c4; i += 32 * kEpiWarps) {
+            const int r = i / c4, c = (i - r * c4) * 4;
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int sp = 0; sp < n_split; ++sp) {
+              const float4 x = __ldcg(reinterpret_cast<const float4*>(pbase + sp * sstride + (int64_t)r * N + c));
+              acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
+            }
+            if (fbias) { acc.x += fbias[c]; acc.y += fbias[c + 1]; acc.z += fbias[c + 2]; acc.w += fbias[c + 3]; }
+            acc.x = apply_act(acc.x, epi.act, epi.slope); acc.y = apply_act(acc.y, epi.act, epi.slope);
+            acc.z = apply_act(acc.z, epi.act, epi.slope); acc.w = apply_act(acc.w, epi.act, epi.slope);
+            *reinterpret_cast<float4*>(fin + (int64_t)r * epi.ldc_final + c) = acc;
+          }
+        } else {
+          for (int i = et; i < rows * cols; i += 32 * kEpiWarps) {
+            const int r = i / cols, c = i - r * cols;
+            float acc = 0.f;
+            for (int sp = 0; sp < n_split; ++sp) acc += __ldcg(pbase + sp * sstride + (int64_t)r * N + c);
+            if (fbias) acc += fbias[c];
+            fin[(int64_t)r * epi.ldc_final + c] = apply_act(acc, epi.act, epi.slope);
+          }
+        }
+        if (et == 0) epi.counters[tile] = 0;                     // ready for the next launch that uses these counters
+      }
+    }
     fence_before_thread_sync();
   }
   __syncthreads();
@@ -507,7 +559,7 @@ static int gemm_impl(const void* A, int64_t lda, int64_t a_group_stride, int a_m
                      int64_t b_group_stride, int b_mn_major, float* C, int64_t ldc, int64_t c_group_stride,
                      const float* bias, int64_t bias_group_stride, int act, float slope, float alpha, float beta,
                      int M, int N, int K, int G, int dtype_bytes, int precise, int n_split, float* scratch,
-                     const float* center, void* stream) {
+                     const float* center, int* tile_counters, void* stream) {
   DDL_REQUIRE(M > 0 && N > 0 && K > 0 && G > 0, "empty GEMM");
   DDL_REQUIRE(dtype_bytes == 4 || dtype_bytes == 2, "operands must be fp32 (tf32 math) or bf16");
   DDL_REQUIRE(!(precise && dtype_bytes != 4), "precise (3xTF32) mode needs fp32 operands");
@@ -544,6 +596,8 @@ static int gemm_impl(const void* A, int64_t lda, int64_t a_group_stride, int a_m
   Epilogue epi;
   epi.C = n_split > 1 ? scratch : C;
   epi.ldc = ldc; epi.c_group_stride = c_group_stride;
+  epi.counters = n_split > 1 ? tile_counters : nullptr;
+  epi.C_final = C; epi.ldc_final = ldc; epi.c_group_stride_final = c_group_stride;
   epi.bias = bias; epi.bias_group_stride = bias_group_stride;
   epi.act = act; epi.slope = slope; epi.alpha = alpha; epi.beta = beta; epi.n_split = n_split;
   // Gram / SYRK: identical operands that fit one tile in both dimensions are staged once
@@ -569,7 +623,7 @@ static int gemm_impl(const void* A, int64_t lda, int64_t a_group_stride, int a_m
   else { DDL_GEMM_CASE(128) }
 #undef DDL_GEMM_CASE
   if (rc) return rc;
-  if (n_split > 1) {
+  if (n_split > 1 && tile_counters == nullptr) {
     const int64_t ge = (int64_t)M * N;
     int64_t blocks = (ge * G + 255) / 256;
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
@@ -586,7 +640,24 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
                      int M, int N, int K, int G, int dtype_bytes, int precise, int n_split, float* scratch,
                      void* stream) {
   return gemm_impl(A, lda, a_group_stride, a_mn_major, B, ldb, b_group_stride, b_mn_major, C, ldc, c_group_stride, bias,
-                   bias_group_stride, act, slope, alpha, beta, M, N, K, G, dtype_bytes, precise, n_split, scratch, nullptr, stream);
+                   bias_group_stride, act, slope, alpha, beta, M, N, K, G, dtype_bytes, precise, n_split, scratch, nullptr, nullptr, stream);
+}
+
+// Same GEMM with the split-K reduction done INSIDE the kernel by the last-arriving CTA of every output tile (no second launch).
+// tile_counters: ddl_gemm_tile_count(M, N, G) ints, zero before the call and zero again after it; launches that may overlap on
+// the GPU must not share them.
+int ddl_gemm_tile_count(int M, int N, int G) {
+  const int BN = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
+  return ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * G;
+}
+int ddl_gemm_tcgen05_fixup(const void* A, int64_t lda, int64_t a_group_stride, int a_mn_major, const void* B, int64_t ldb,
+                           int64_t b_group_stride, int b_mn_major, float* C, int64_t ldc, int64_t c_group_stride,
+                           const float* bias, int64_t bias_group_stride, int act, float slope, float alpha, float beta,
+                           int M, int N, int K, int G, int dtype_bytes, int precise, int n_split, float* scratch,
+                           int* tile_counters, void* stream) {
+  return gemm_impl(A, lda, a_group_stride, a_mn_major, B, ldb, b_group_stride, b_mn_major, C, ldc, c_group_stride, bias,
+                   bias_group_stride, act, slope, alpha, beta, M, N, K, G, dtype_bytes, precise, n_split, scratch, nullptr, tile_counters,
+                   stream);
 }
 
 // K3: Gram matrix of update DELTAS, G = (U - 1 c^T)(U - 1 c^T)^T, without materialising the deltas: the 3xTF32 splitter
@@ -596,7 +667,7 @@ int ddl_gram_tcgen05(const float* updates, int64_t ld, int K, int64_t D, const f
   DDL_REQUIRE(K >= 1 && K <= BM, "K=%d outside [1, %d] (one tile of clients)", K, BM);
   DDL_REQUIRE(D >= 4 && D <= 0x7fffffff - 64, "D=%lld out of range", (long long)D);
   return gemm_impl(updates, ld, 0, 0, updates, ld, 0, 0, gram, ldg, 0, nullptr, 0, 0, 0.f, 1.f, 0.f, K, K, (int)D, 1, 4,
-                   center != nullptr ? 1 : precise, n_split, scratch, center, stream);
+                   center != nullptr ? 1 : precise, n_split, scratch, center, nullptr, stream);
 }
 
 // K7 host side: A = cat_p(parts[p]) along K, parts may be peer-mapped device pointers.
@@ -641,6 +712,7 @@ int ddl_gather_gemm_tcgen05(const float* const* parts, const int* part_dims, con
   epi.ldc = ldc; epi.c_group_stride = 0; epi.bias = bias; epi.bias_group_stride = 0;
   epi.act = act; epi.slope = slope; epi.alpha = 1.f; epi.beta = 0.f; epi.n_split = n_split; epi.same_ab = 0;
   epi.center = nullptr; epi.center_len = 0;
+  epi.counters = nullptr; epi.C_final = C; epi.ldc_final = ldc; epi.c_group_stride_final = 0;
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, n_split);
 #define DDL_GATHER_CASE(BN_, P_)                                                                              \
@@ -697,6 +769,7 @@ int ddl_gram_rowgather_tcgen05(const float* const* part_ptrs, int n_parts, int r
   epi.act = 0; epi.slope = 0.f; epi.alpha = 1.f; epi.beta = 0.f; epi.n_split = n_split; epi.same_ab = 1;
   DDL_REQUIRE(center == nullptr || (precise && (reinterpret_cast<uintptr_t>(center + d0) & 15) == 0), "re-centring needs precise != 0 and an aligned centre vector");
   epi.center = center ? center + d0 : nullptr; epi.center_len = Kdim;
+  epi.counters = nullptr; epi.C_final = gram; epi.ldc_final = ldg; epi.c_group_stride_final = 0;
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(1, 1, n_split);
 #define DDL_ROWG_CASE2(BN_, P_)                                                                                \

@@ -23,6 +23,18 @@ from . import _lib
 
 ACT = {"none": 0, None: 0, "relu": 1, "leaky_relu": 2}
 PRECISE_CHAIN = 1024
+MAX_FIXUP_TILES = 8192
+_TILE_COUNTERS: dict = {}
+
+
+def _tile_counters(device: torch.device) -> torch.Tensor:
+    """Zeroed per-(device, stream) tile counters of the in-kernel split-K fix-up (the kernel leaves them zero; launches on one
+    stream are ordered, so they can share the buffer)."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    t = _TILE_COUNTERS.get(key)
+    if t is None:
+        t = _TILE_COUNTERS[key] = torch.zeros(MAX_FIXUP_TILES, dtype=torch.int32, device=device)
+    return t
 
 
 def _grouped(t: torch.Tensor):
@@ -72,15 +84,21 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         if 2 * ctas <= 148 and kb >= 16:
             n_split = max(1, min(kb // 4, 148 // ctas))
     L = _lib.lib()
-    scratch = None
+    scratch = counters = None
     if n_split > 1:
         scratch = torch.empty(n_split * G * M * N, device=a.device, dtype=torch.float32)
-    rc = L.ddl_gemm_tcgen05(
-        _lib.p(A), _lib.i64(A.stride(1)), _lib.i64(A.stride(0)), int(a_mn),
-        _lib.p(B), _lib.i64(B.stride(1)), _lib.i64(B.stride(0)), int(b_mn),
-        _lib.p(O), _lib.i64(O.stride(1)), _lib.i64(O.stride(0)),
-        _lib.p(bias), _lib.i64(bias_stride), ACT[act], _lib.f32(slope), _lib.f32(alpha), _lib.f32(beta),
-        int(M), int(N), int(K), int(G), int(eb), int(precise), int(n_split), _lib.p(scratch), _lib.stream())
+        # split-K partials are reduced inside the kernel by the last-arriving CTA of each tile (no splitk_reduce launch)
+        if L.ddl_gemm_tile_count(int(M), int(N), int(G)) <= MAX_FIXUP_TILES:
+            counters = _tile_counters(a.device)
+    args = (_lib.p(A), _lib.i64(A.stride(1)), _lib.i64(A.stride(0)), int(a_mn),
+            _lib.p(B), _lib.i64(B.stride(1)), _lib.i64(B.stride(0)), int(b_mn),
+            _lib.p(O), _lib.i64(O.stride(1)), _lib.i64(O.stride(0)),
+            _lib.p(bias), _lib.i64(bias_stride), ACT[act], _lib.f32(slope), _lib.f32(alpha), _lib.f32(beta),
+            int(M), int(N), int(K), int(G), int(eb), int(precise), int(n_split), _lib.p(scratch))
+    if counters is not None:
+        rc = L.ddl_gemm_tcgen05_fixup(*args, _lib.p(counters), _lib.stream())
+    else:
+        rc = L.ddl_gemm_tcgen05(*args, _lib.stream())
     _lib.check(rc, "ddl_gemm_tcgen05")
     return out[0] if (squeeze and out.dim() == 3) else out
 

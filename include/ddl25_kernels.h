@@ -119,6 +119,17 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
                      int M, int N, int K, int G, int dtype_bytes, int precise, int n_split, float* scratch,
                      void* stream);
 
+/* Same GEMM, split-K reduced INSIDE the kernel: every split CTA stores its partial tile, and the CTA that arrives last at a
+ * tile sums the partials in split order (deterministic), applies bias + activation and writes C - no second launch.
+ * tile_counters: ddl_gemm_tile_count(M, N, G) ints, zero before the call (the kernel leaves them zero again); launches that
+ * can overlap on the GPU must not share them. */
+int ddl_gemm_tile_count(int M, int N, int G);
+int ddl_gemm_tcgen05_fixup(const void* A, int64_t lda, int64_t a_group_stride, int a_mn_major, const void* B, int64_t ldb,
+                           int64_t b_group_stride, int b_mn_major, float* C, int64_t ldc, int64_t c_group_stride,
+                           const float* bias, int64_t bias_group_stride, int act, float slope, float alpha, float beta,
+                           int M, int N, int K, int G, int dtype_bytes, int precise, int n_split, float* scratch,
+                           int* tile_counters, void* stream);
+
 /* K3: G = (U - 1 c^T)(U - 1 c^T)^T for U = [K <= 128, D] (row stride ld): the Gram matrix of the update DELTAS u_k - c
  * [north star: Krum].  The centre c (the global model, [D], 16-byte aligned; NULL = plain U U^T) is subtracted from the
  * staged tiles in shared memory (3xTF32 mode is implied), so no K x D delta matrix is written to HBM.  Split-K scratch:
