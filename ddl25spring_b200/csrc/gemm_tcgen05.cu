@@ -376,49 +376,72 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
       __syncwarp();
     }
     if (n_split > 1 && epi.counters != nullptr) {
-      // ---- split-K fix-up by the last-arriving CTA of this output tile
-      int* flag = reinterpret_cast<int*>(tmem_slot + 1);
+      // ---- cooperative split-K fix-up.  The host only enables it when the whole grid is one wave (<= 148 CTAs, one per SM),
+      // so the n_split CTAs of a tile are co-resident: each stores its raw partial tile, they meet at the tile's counter, and
+      // then EVERY one of them reduces its 1/n_split share of the tile's rows over all partials (in split order:
+      // deterministic), applies bias + activation and writes the final rows.  (A last-arriving-CTA reduction was measured
+      // 3x slower than the separate reduce kernel: one CTA cannot keep enough loads in flight for n_split x 64 KB.)
       __threadfence();                                           // this CTA's partial tile is visible device-wide ...
       asm volatile("bar.sync 1, 128;" ::: "memory");             // ... for all four epilogue warps, before the arrival is counted
       const int G = gridDim.z / n_split;
-      const int tile = (g * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-      if (et == 0) *flag = (atomicAdd(epi.counters + tile, 1) == n_split - 1);
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (*flag) {
-        __threadfence();
-        const int rows = (M - m0) < BM ? (M - m0) : BM;
-        const int cols = (N - n0) < BN ? (N - n0) : BN;
-        const int64_t sstride = (int64_t)G * M * N;
-        const float* pbase = epi.C + (int64_t)g * M * N + (int64_t)m0 * N + n0;
-        float* fin = epi.C_final + (int64_t)g * epi.c_group_stride_final + (int64_t)m0 * epi.ldc_final + n0;
-        const float* fbias = epi.bias ? epi.bias + (int64_t)g * epi.bias_group_stride + n0 : nullptr;
-        const bool v4 = (N % 4 == 0) && (n0 % 4 == 0) && (epi.ldc_final % 4 == 0) && (epi.c_group_stride_final % 4 == 0) &&
-                        ((reinterpret_cast<uintptr_t>(epi.C) & 15) == 0) && ((reinterpret_cast<uintptr_t>(epi.C_final) & 15) == 0);
-        if (v4) {
-          const int c4 = cols / 4;
-          for (int i = et; i < rows * c4; i += 32 * kEpiWarps) {
-            const int r = i / c4, c = (i - r * c4) * 4;
-            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int sp = 0; sp < n_split; ++sp) {
-              const float4 x = __ldcg(reinterpret_cast<const float4*>(pbase + sp * sstride + (int64_t)r * N + c));
-              acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
-            }
-            if (fbias) { acc.x += fbias[c]; acc.y += fbias[c + 1]; acc.z += fbias[c + 2]; acc.w += fbias[c + 3]; }
-            acc.x = apply_act(acc.x, epi.act, epi.slope); acc.y = apply_act(acc.y, epi.act, epi.slope);
-            acc.z = apply_act(acc.z, epi.act, epi.slope); acc.w = apply_act(acc.w, epi.act, epi.slope);
-            *reinterpret_cast<float4*>(fin + (int64_t)r * epi.ldc_final + c) = acc;
-          }
-        } else {
-          for (int i = et; i < rows * cols; i += 32 * kEpiWarps) {
-            const int r = i / cols, c = i - r * cols;
-            float acc = 0.f;
-            for (int sp = 0; sp < n_split; ++sp) acc += __ldcg(pbase + sp * sstride + (int64_t)r * N + c);
-            if (fbias) acc += fbias[c];
-            fin[(int64_t)r * epi.ldc_final + c] = apply_act(acc, epi.act, epi.slope);
-          }
+      int* cnt = epi.counters + (g * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+      if (et == 0) {
+        atomicAdd(cnt, 1);
+        const long long t0 = clock64();
+        while (*reinterpret_cast<volatile int*>(cnt) < n_split) {
+          if (clock64() - t0 > 4000000000ll) __trap();           // ~2 s: a sibling CTA never arrived
         }
-        if (et == 0) epi.counters[tile] = 0;                     // ready for the next launch that uses these counters
       }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      __threadfence();
+      const int rows = (M - m0) < BM ? (M - m0) : BM;
+      const int cols = (N - n0) < BN ? (N - n0) : BN;
+      const int per = (rows + n_split - 1) / n_split;
+      const int r0 = split * per;
+      const int nr = (rows - r0) < per ? (rows - r0) : per;      // may be <= 0 for the last splits of a short tile
+      const int64_t sstride = (int64_t)G * M * N;
+      const float* pbase = epi.C + (int64_t)g * M * N + (int64_t)(m0 + r0) * N + n0;
+      float* fin = epi.C_final + (int64_t)g * epi.c_group_stride_final + (int64_t)(m0 + r0) * epi.ldc_final + n0;
+      const float* fbias = epi.bias ? epi.bias + (int64_t)g * epi.bias_group_stride + n0 : nullptr;
+      const bool v4 = (N % 4 == 0) && (epi.ldc_final % 4 == 0) && (epi.c_group_stride_final % 4 == 0) &&
+                      ((reinterpret_cast<uintptr_t>(epi.C) & 15) == 0) && ((reinterpret_cast<uintptr_t>(epi.C_final) & 15) == 0);
+      if (v4) {
+        const int c4 = cols / 4;                                 // N % 4 == 0 and BN % 4 == 0 -> cols % 4 == 0
+        for (int i = et; i < nr * c4; i += 32 * kEpiWarps) {
+          const int r = i / c4, c = (i - r * c4) * 4;
+          const float* p0 = pbase + (int64_t)r * N + c;
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+          int sp = 0;
+          for (; sp + 4 <= n_split; sp += 4) {                   // four independent loads in flight, added in split order
+            const float4 x0 = __ldcg(reinterpret_cast<const float4*>(p0 + (sp + 0) * sstride));
+            const float4 x1 = __ldcg(reinterpret_cast<const float4*>(p0 + (sp + 1) * sstride));
+            const float4 x2 = __ldcg(reinterpret_cast<const float4*>(p0 + (sp + 2) * sstride));
+            const float4 x3 = __ldcg(reinterpret_cast<const float4*>(p0 + (sp + 3) * sstride));
+            acc.x += x0.x; acc.y += x0.y; acc.z += x0.z; acc.w += x0.w;
+            acc.x += x1.x; acc.y += x1.y; acc.z += x1.z; acc.w += x1.w;
+            acc.x += x2.x; acc.y += x2.y; acc.z += x2.z; acc.w += x2.w;
+            acc.x += x3.x; acc.y += x3.y; acc.z += x3.z; acc.w += x3.w;
+          }
+          for (; sp < n_split; ++sp) {
+            const float4 x = __ldcg(reinterpret_cast<const float4*>(p0 + sp * sstride));
+            acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
+          }
+          if (fbias) { acc.x += fbias[c]; acc.y += fbias[c + 1]; acc.z += fbias[c + 2]; acc.w += fbias[c + 3]; }
+          acc.x = apply_act(acc.x, epi.act, epi.slope); acc.y = apply_act(acc.y, epi.act, epi.slope);
+          acc.z = apply_act(acc.z, epi.act, epi.slope); acc.w = apply_act(acc.w, epi.act, epi.slope);
+          *reinterpret_cast<float4*>(fin + (int64_t)r * epi.ldc_final + c) = acc;
+        }
+      } else {
+        for (int i = et; i < nr * cols; i += 32 * kEpiWarps) {
+          const int r = i / cols, c = i - r * cols;
+          float acc = 0.f;
+          for (int sp = 0; sp < n_split; ++sp) acc += __ldcg(pbase + sp * sstride + (int64_t)r * N + c);
+          if (fbias) acc += fbias[c];
+          fin[(int64_t)r * epi.ldc_final + c] = apply_act(acc, epi.act, epi.slope);
+        }
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (et == 0 && atomicAdd(cnt, 1) == 2 * n_split - 1) *cnt = 0;   // last one out re-arms the counter for the next launch
     }
     fence_before_thread_sync();
   }
@@ -596,7 +619,9 @@ static int gemm_impl(const void* A, int64_t lda, int64_t a_group_stride, int a_m
   Epilogue epi;
   epi.C = n_split > 1 ? scratch : C;
   epi.ldc = ldc; epi.c_group_stride = c_group_stride;
-  epi.counters = n_split > 1 ? tile_counters : nullptr;
+  // the cooperative fix-up needs all CTAs of the grid co-resident: one wave of one CTA per SM
+  const int64_t grid_ctas = (int64_t)((M + BM - 1) / BM) * ((N + (N <= 32 ? 32 : (N <= 64 ? 64 : 128)) - 1) / (N <= 32 ? 32 : (N <= 64 ? 64 : 128))) * G * n_split;
+  epi.counters = (n_split > 1 && grid_ctas <= kNumSMs) ? tile_counters : nullptr;
   epi.C_final = C; epi.ldc_final = ldc; epi.c_group_stride_final = c_group_stride;
   epi.bias = bias; epi.bias_group_stride = bias_group_stride;
   epi.act = act; epi.slope = slope; epi.alpha = alpha; epi.beta = beta; epi.n_split = n_split;
@@ -623,7 +648,7 @@ static int gemm_impl(const void* A, int64_t lda, int64_t a_group_stride, int a_m
   else { DDL_GEMM_CASE(128) }
 #undef DDL_GEMM_CASE
   if (rc) return rc;
-  if (n_split > 1 && tile_counters == nullptr) {
+  if (n_split > 1 && epi.counters == nullptr) {
     const int64_t ge = (int64_t)M * N;
     int64_t blocks = (ge * G + 255) / 256;
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
@@ -643,9 +668,10 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
                    bias_group_stride, act, slope, alpha, beta, M, N, K, G, dtype_bytes, precise, n_split, scratch, nullptr, nullptr, stream);
 }
 
-// Same GEMM with the split-K reduction done INSIDE the kernel by the last-arriving CTA of every output tile (no second launch).
-// tile_counters: ddl_gemm_tile_count(M, N, G) ints, zero before the call and zero again after it; launches that may overlap on
-// the GPU must not share them.
+// Same GEMM with the split-K reduction done INSIDE the kernel (no second launch) whenever the whole grid is a single wave
+// (tiles x G x n_split <= 148): the CTAs of a tile meet at its counter and each reduces its share of the rows.  Larger grids
+// fall back to the separate reduce kernel.  tile_counters: ddl_gemm_tile_count(M, N, G) ints, zero before the call and zero
+// again after it; launches that may overlap on the GPU must not share them.
 int ddl_gemm_tile_count(int M, int N, int G) {
   const int BN = N <= 32 ? 32 : (N <= 64 ? 64 : 128);
   return ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * G;

@@ -119,8 +119,9 @@ int ddl_gemm_tcgen05(const void* A, int64_t lda, int64_t a_group_stride, int a_m
                      int M, int N, int K, int G, int dtype_bytes, int precise, int n_split, float* scratch,
                      void* stream);
 
-/* Same GEMM, split-K reduced INSIDE the kernel: every split CTA stores its partial tile, and the CTA that arrives last at a
- * tile sums the partials in split order (deterministic), applies bias + activation and writes C - no second launch.
+/* Same GEMM, split-K reduced INSIDE the kernel when the grid is one wave (tiles x G x n_split <= 148 CTAs): the CTAs of a tile
+ * store their partial tiles, meet at the tile's counter, and each sums its share of the rows over all partials in split order
+ * (deterministic), applies bias + activation and writes C - no second launch.  Larger grids use the separate reduce kernel.
  * tile_counters: ddl_gemm_tile_count(M, N, G) ints, zero before the call (the kernel leaves them zero again); launches that
  * can overlap on the GPU must not share them. */
 int ddl_gemm_tile_count(int M, int N, int G);
