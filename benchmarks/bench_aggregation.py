@@ -67,44 +67,62 @@ def main():
         out["roofline_ms_read_once"] = round(bytes_in / hbm * 1e3, 4)
         out["frac_of_measured_hbm"] = {k: round(bytes_in / hbm * 1e3 / v, 3) for k, v in rows.items() if "ours" in k and "select" not in k}
     else:
-        from ddl25spring_b200.parallel.symm_impl import SymmetricArena, shard_bounds
+        # one rank per GPU, 8 client rows per GPU: the product path (SymmetricAggregator.aggregate) for every rule, next to
+        # NCCL all_gather + torch for the same rule
+        from ddl25spring_b200.fl.aggregators import CoordinateMedian, Krum, TrimmedMean, WeightedMean
+        from ddl25spring_b200.parallel.symm_impl import SymmetricAggregator
         G_, K = 8, 8 * world
-        a = SymmetricArena()
-        rows_t = a.alloc("rows", G_ * DP * 4).view(G_, DP)
-        res = a.alloc("res", DP * 4)
-        rows_t.copy_(0.01 * torch.randn(G_, DP, device="cuda"))
-        ptrs = [a.peer_ptrs("rows")[k % world] + (k // world) * DP * 4 for k in range(K)]
-        w = [1.0 / K] * K
-        d0, d1 = shard_bounds(DP, world, rank)
+        f = max(1, int(0.2 * K))
+        coll = SymmetricAggregator(max_rows_per_rank=G_, row_elems=DP)
+        rows_t = coll.row_buffer(G_)
+        gen = torch.Generator(device="cuda").manual_seed(rank)
+        gflat = 0.05 * torch.randn(DP, device="cuda", generator=torch.Generator(device="cuda").manual_seed(1234))
+        rows_t.copy_(gflat[None, :] + 0.01 * torch.randn(G_, DP, device="cuda", generator=gen))
+        mine_pos = [p for p in range(K) if p % world == rank]
+        w = torch.full((K,), 1.0 / K)
+        g = gflat.clone()
         t = {}
-        t["mean_fused"] = timeit(lambda: a.reduce(0, ptrs, w, a.peer_ptrs("res"), d0, d1), fl)
-        part = a.alloc("part", DP * 4)
-        lw = [1.0 / K] * G_
+        rules = {"mean": WeightedMean(), "median": CoordinateMedian(), "trimmed_mean": TrimmedMean(0.2),
+                 "krum": Krum(f, multi=K - 2 * f), "krum_fused_gather": Krum(f, multi=K - 2 * f, fused_gather=True)}
+        sel = {}
+        for name, agg in rules.items():
+            t[name + "_fused"] = timeit(lambda: coll.aggregate(agg, rows_t, mine_pos, w, g), fl)
+            if isinstance(agg, Krum):
+                sel[name] = sorted(agg.last_selected.cpu().tolist())
+        coll.arena.check()
+        allrows = torch.empty(world, G_, DP, device="cuda")
 
-        def mean_hier():
-            ops.weighted_sum(rows_t, lw, part)
-            a.reduce(0, a.peer_ptrs("part"), [1.0] * world, a.peer_ptrs("res"), d0, d1)
-        t["mean_fused_hierarchical"] = timeit(mean_hier, fl)
-        t["median_fused"] = timeit(lambda: a.reduce(1, ptrs, w, a.peer_ptrs("res"), d0, d1, rank_lo=K // 2 - 1, rank_hi=K // 2 + 1), fl)
-        part2 = torch.empty(DP, device="cuda")
-        wl = torch.full((G_,), 1.0 / K, device="cuda")
+        def gather():
+            dist.all_gather_into_tensor(allrows.view(-1), rows_t.reshape(-1))
+            return allrows.view(K, DP)
+        tt = int(-(-0.2 * K // 1))
 
-        def nccl_mean():
-            torch.mv(rows_t.t(), wl, out=part2)
-            dist.all_reduce(part2)
-        t["mean_nccl"] = timeit(nccl_mean, fl)
-        allrows = torch.empty(K, DP, device="cuda") if K * DP * 4 < 60e9 else None
-
-        def nccl_median():
-            dist.all_gather_into_tensor(allrows.view(-1), rows_t.view(-1))
-            torch.median(allrows, dim=0)
-        if allrows is not None:
-            t["median_nccl_allgather_torch"] = timeit(nccl_median, fl, iters=3, warm=1)
-        a.check()
+        def base(name):
+            A = gather()
+            if name == "mean":
+                return A.mean(0)
+            if name == "median":
+                return torch.median(A, dim=0).values
+            if name == "trimmed_mean":
+                return torch.sort(A, dim=0).values[tt:K - tt].mean(0)
+            Ad = A - gflat[None, :]
+            dd = torch.cdist(Ad, Ad).pow(2)
+            dd.fill_diagonal_(float("inf"))
+            sc = torch.sort(dd, dim=1).values[:, :K - f - 2].sum(1)
+            idx = torch.argsort(sc)[:K - 2 * f]
+            sel["krum_torch_fp32"] = sorted(idx.cpu().tolist())
+            return A[idx].mean(0)
+        for name in ("mean", "median", "trimmed_mean", "krum"):
+            t[name + "_nccl_allgather_torch"] = timeit(lambda: base(name), fl, iters=2, warm=1)
         out["K"] = K
         out["ms"] = {k: round(max_over_ranks(v, "cuda"), 4) for k, v in t.items()}
-        nv = 770e9
-        out["nvlink_roofline_ms"] = round((world - 1) / world * G_ * DP * 4 / nv * 1e3, 4)
+        local_bytes = G_ * DP * 4
+        roof = max(local_bytes / hbm, (world - 1) / world * local_bytes / 900e9) * 1e3
+        out["roofline_ms"] = round(roof, 4)
+        out["roofline"] = "max(8 local rows read once from HBM at the measured copy bandwidth, (W-1)/W of them over NVLink at 900 GB/s)"
+        out["frac_of_roofline"] = {k: round(roof / v, 3) for k, v in out["ms"].items() if k.endswith("_fused")}
+        out["krum_selected"] = sel
+        out["krum_selection_agrees"] = sel.get("krum") == sel.get("krum_torch_fp32") == sel.get("krum_fused_gather")
     if rank == 0:
         print(json.dumps(out))
     if world > 1:
