@@ -298,7 +298,7 @@ def section_robust(rank: int, world: int, flusher, coll_arena) -> dict:
     hbm = peaks.get("hbm_gbs", 6551.0) * 1e9
     srv = FedAvgServer(0.05, batch, subsets, 1.0, 1, 10, model_fn=resnet18_nhwc, test_set=ds.test, device="cuda",
                        loss_fn=F.cross_entropy, include_buffers=True, graph=True, attack=SignFlip(4.0), malicious=mal,
-                       test_batch_size=1000)
+                       test_batch_size=1000, concurrent_clients=CLIENTS_PER_GPU)
     D = srv.arena.size
     coll = None
     if world > 1:
@@ -309,7 +309,8 @@ def section_robust(rank: int, world: int, flusher, coll_arena) -> dict:
     link_bytes = (world - 1) / world * local_bytes
     roof_ms = max(local_bytes / hbm, link_bytes / 900e9) * 1e3
     out = {"model": "ResNet-18 (NHWC tcgen05 stack, BN statistics aggregated with the weights)", "clients_per_round": K,
-           "clients_per_gpu": CLIENTS_PER_GPU, "attackers": f, "attack": "sign-flip x4", "samples_per_client": samples,
+           "clients_per_gpu": CLIENTS_PER_GPU, "client_execution": "the 8 clients of a GPU train side by side: one model slot, stream and "
+                                                                   "captured step graph each", "attackers": f, "attack": "sign-flip x4", "samples_per_client": samples,
            "local_batch": batch, "rounds_timed": rounds, "row_floats": D,
            "aggregation_roofline_ms": round(roof_ms, 4),
            "roofline": "max(this GPU's 8 rows read once from HBM at the measured copy bandwidth, (W-1)/W of them over NVLink "

@@ -110,7 +110,8 @@ def main():
             dd.fill_diagonal_(float("inf"))
             sc = torch.sort(dd, dim=1).values[:, :K - f - 2].sum(1)
             idx = torch.argsort(sc)[:K - 2 * f]
-            sel["krum_torch_fp32"] = sorted(idx.cpu().tolist())
+            # the gathered matrix is rank-major (row = rank * 8 + local); report client indices k (rank k % W, local k // W)
+            sel["krum_torch_fp32"] = sorted(int(i % G_) * world + int(i // G_) for i in idx.cpu().tolist())
             return A[idx].mean(0)
         for name in ("mean", "median", "trimmed_mean", "krum"):
             t[name + "_nccl_allgather_torch"] = timeit(lambda: base(name), fl, iters=2, warm=1)

@@ -190,7 +190,7 @@ class DecentralizedServer(Server):
 
     def __init__(self, lr: float, batch_size: int, client_subsets: Sequence, client_fraction: float, seed: int, *,
                  aggregator: Aggregator | None = None, attack: Attack | None = None,
-                 malicious: np.ndarray | None = None, collective=None, **kw) -> None:
+                 malicious: np.ndarray | None = None, collective=None, concurrent_clients: int = 1, **kw) -> None:
         super().__init__(lr, batch_size, seed, **kw)
         self.nr_clients = len(client_subsets)
         self.client_fraction = client_fraction
@@ -204,6 +204,16 @@ class DecentralizedServer(Server):
         # one borrowed model slot for all of this rank's clients (they train one after another here;
         # the packed engine in fl/packed.py trains them concurrently with grouped kernels)
         self.worker_slot = ModelSlot(self.model_fn, self.device, include_buffers=self.include_buffers, graph=self.graph)
+        # concurrent_clients = S > 1 (CUDA): S model slots, each with its own stream, convolution workspace and step graph; the
+        # rank's clients of a round are dealt to the slots and train SIDE BY SIDE.  A ResNet-18 client step at the lab batch
+        # sizes is ~200 kernels that each fill a fraction of the 148 SMs, so several clients' graphs overlap on the GPU - the
+        # reference trains them strictly one after another (hfl_complete.py:365-375) and merely *reports* parallel time (:373-375).
+        self.worker_slots = [self.worker_slot]
+        self._slot_streams = None
+        if concurrent_clients > 1 and self.device.type == "cuda":
+            self.worker_slots += [ModelSlot(self.model_fn, self.device, include_buffers=self.include_buffers, graph=self.graph)
+                                  for _ in range(concurrent_clients - 1)]
+            self._slot_streams = [torch.cuda.Stream(device=self.device) for _ in self.worker_slots]
         self._updates: torch.Tensor | None = None
         # parallel.symm_impl.SymmetricAggregator(row_elems=arena.size): fused peer-memory aggregation across ranks
         self.collective = collective
@@ -222,6 +232,12 @@ class DecentralizedServer(Server):
         if self.world > 1 and not fused:
             U.zero_()
         slowest = 0.0
+        streams = self._slot_streams
+        main = torch.cuda.current_stream(self.device) if streams else None
+        if streams:
+            for st in streams:
+                st.wait_stream(main)                     # the global model (and U) are ready
+        n_local = 0
         for pos, c_i in enumerate(chosen):
             if pos % self.world != self.rank:
                 continue
@@ -229,12 +245,24 @@ class DecentralizedServer(Server):
             ind = int(c_i)
             seed = client_round_seed(self.seed, ind, nr_round, self.nr_clients_per_round)
             client = self.clients[ind]
-            client.bind(self.worker_slot)
+            si = n_local % len(self.worker_slots)
+            n_local += 1
+            client.bind(self.worker_slots[si])
             row = U[pos // self.world] if fused else U[pos]      # fused: this rank's rows only, in symmetric memory
-            client.update_flat(gflat, seed, out=row)
-            if self.attack is not None and self.malicious[ind]:
-                self.attack(row, None if self.message_is_gradient else gflat, client=ind, nr_round=nr_round, out=row)
+            if streams:
+                from ..ops.conv import workspace_scope
+                with torch.cuda.stream(streams[si]), workspace_scope(si):
+                    client.update_flat(gflat, seed, out=row)
+                    if self.attack is not None and self.malicious[ind]:
+                        self.attack(row, None if self.message_is_gradient else gflat, client=ind, nr_round=nr_round, out=row)
+            else:
+                client.update_flat(gflat, seed, out=row)
+                if self.attack is not None and self.malicious[ind]:
+                    self.attack(row, None if self.message_is_gradient else gflat, client=ind, nr_round=nr_round, out=row)
             slowest = max(slowest, perf_counter() - t0)
+        if streams:
+            for st in streams:
+                main.wait_stream(st)
         if self.world > 1 and not fused:
             # rows trained elsewhere are zero here: a SUM all-reduce assembles the full matrix on
             # every rank (gloo/NCCL path; parallel/symm.py replaces this with peer-memory kernels)
