@@ -27,14 +27,13 @@ import torch
 import torch.nn.functional as F
 
 import contextlib
-import threading
 
 from . import _lib
 from .gemm import gemm
 
 ACT = {None: 0, "none": 0, "relu": 1, "leaky_relu": 2, "tanh": 3}
 _WS: dict = {}
-_SCOPE = threading.local()
+_SCOPE = {"id": 0}      # a plain global, NOT thread-local: backward passes run on autograd's worker thread and must see the scope
 
 
 @contextlib.contextmanager
@@ -43,16 +42,16 @@ def workspace_scope(scope_id: int):
     BatchNorm partials).  Work that runs concurrently on different CUDA streams - e.g. the federated clients a server trains
     side by side (fl/server.py ``concurrent_clients``) - must not share scratch; a CUDA graph captured inside a scope keeps
     that scope's buffers."""
-    prev = getattr(_SCOPE, "id", 0)
-    _SCOPE.id = int(scope_id)
+    prev = _SCOPE["id"]
+    _SCOPE["id"] = int(scope_id)
     try:
         yield
     finally:
-        _SCOPE.id = prev
+        _SCOPE["id"] = prev
 
 
 def _workspace(device) -> dict:
-    key = (device.type, device.index, getattr(_SCOPE, "id", 0))
+    key = (device.type, device.index, _SCOPE["id"])
     ws = _WS.get(key)
     if ws is None:
         ws = {"scratch": torch.empty(16 << 20, device=device, dtype=torch.float32),      # split-K partial tiles (64 MB)

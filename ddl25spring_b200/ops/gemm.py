@@ -30,7 +30,8 @@ _TILE_COUNTERS: dict = {}
 def _tile_counters(device: torch.device) -> torch.Tensor:
     """Zeroed per-(device, stream) tile counters of the in-kernel split-K fix-up (the kernel leaves them zero; launches on one
     stream are ordered, so they can share the buffer)."""
-    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    from .conv import _SCOPE                 # concurrent client slots (fl/server.py) each work inside their own scope
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream, _SCOPE["id"])
     t = _TILE_COUNTERS.get(key)
     if t is None:
         t = _TILE_COUNTERS[key] = torch.zeros(MAX_FIXUP_TILES, dtype=torch.int32, device=device)
