@@ -550,9 +550,12 @@ def _fed_dcgan_worker(rank, world):
     for name in ("fused", "nccl"):
         fed = FederatedDCGAN(clients, 1.0, local_steps=1, batch_size=8, seed=3, device="cuda", ngf=16, ndf=16,
                              collective=SymmetricArena() if name == "fused" else None)
-        fed.run(2)
+        fed.run(1)
         torch.cuda.synchronize()
-        out[name] = (fed.glob.ga.flat.clone().cpu(), fed.glob.da.flat.clone().cpu())
+        first = (fed.glob.ga.flat.clone().cpu(), fed.glob.da.flat.clone().cpu())
+        fed.run(1)
+        torch.cuda.synchronize()
+        out[name] = first + (fed.glob.ga.flat.clone().cpu(), fed.glob.da.flat.clone().cpu())
     return out
 
 
@@ -561,6 +564,10 @@ def test_federated_dcgan_fused_aggregation_equals_nccl():
     world = min(torch.cuda.device_count(), 8)
     outs = run_distributed(_fed_dcgan_worker, world, timeout=300, backend="nccl")
     for o in outs:
-        torch.testing.assert_close(o["fused"][0], o["nccl"][0], rtol=1e-4, atol=1e-5)
-        torch.testing.assert_close(o["fused"][1], o["nccl"][1], rtol=1e-4, atol=1e-5)
-    torch.testing.assert_close(outs[0]["fused"][0], outs[-1]["fused"][0], rtol=0, atol=0)
+        # round 1: same local training, the two aggregation paths differ only in summation order
+        torch.testing.assert_close(o["fused"][0], o["nccl"][0], rtol=1e-5, atol=2e-6)
+        torch.testing.assert_close(o["fused"][1], o["nccl"][1], rtol=1e-5, atol=2e-6)
+        # round 2: Adam (lr 2e-4) turns last-bit differences of the averaged model into update differences of up to ~lr
+        torch.testing.assert_close(o["fused"][2], o["nccl"][2], rtol=1e-3, atol=1e-3)
+        torch.testing.assert_close(o["fused"][3], o["nccl"][3], rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(outs[0]["fused"][2], outs[-1]["fused"][2], rtol=0, atol=0)      # replicas stay identical
