@@ -493,6 +493,235 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restr
   }
 }
 
+
+// ------------------------------------------------------------------------------------------ K3: row-packed Gram (SYRK)
+// G = U U^T for K <= 64 clients.  A 128-row MMA tile that holds only K rows wastes (128 - K) / 128 of every TMA box, MMA
+// and splitter pass, and - worse - the kernel is bound by the per-k-block latency chain (TMA -> split -> MMA), not by
+// bytes: with K = 8 a k-block moves 1 KB.  So the tile's 128 rows are filled with S = 128 / Kp DIFFERENT 32-column slices
+// of the same Kp = pow2(K) rows (one 3-D TMA box {32, Kp, S} over the view [D/32 slices][K rows][32 cols]); one k-block
+// then covers S * 32 columns of every client.  T T^T is a 128 x 128 accumulator whose S diagonal Kp x Kp blocks are the
+// slice Grams: the epilogue sums them (fixed order) into the split's partial.  S x fewer k-blocks: 16 x at K = 8.
+// SPLIT3 = 3xTF32 with optional re-centring (see the splitter of gemm_tcgen05_body).
+struct GramPackedArgs {
+  float* partial;        // [n_split][K*K]
+  const float* center;   // may be null
+  int64_t D;
+  int K, Kp, S, kp_shift;
+  int total_kb, kb_per_split;
+};
+
+template <bool SPLIT3>
+struct GramPackedPlan {
+  static constexpr int TILE = 128 * ROW_BYTES;                    // 16 KB
+  static constexpr int STAGE_BYTES = TILE * (SPLIT3 ? 2 : 1);
+  static constexpr int STAGES = SPLIT3 ? 6 : 10;
+  static constexpr int TOTAL = STAGES * STAGE_BYTES + 1024 + 1024;
+};
+
+template <bool SPLIT3>
+__global__ void __launch_bounds__(kThreads, 1) gram_packed_kernel(const __grid_constant__ CUtensorMap tm, const GramPackedArgs a) {
+  using Plan = GramPackedPlan<SPLIT3>;
+  constexpr int STAGES = Plan::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Plan::STAGE_BYTES);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + STAGES;
+  uint64_t* split_bar = bars + 2 * STAGES;
+  uint64_t* accum_bar = bars + 3 * STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * STAGES + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int split = blockIdx.x;
+  const int kb_begin = split * a.kb_per_split;
+  int kb_end = kb_begin + a.kb_per_split;
+  if (kb_end > a.total_kb) kb_end = a.total_kb;
+  const int num_kb = kb_end > kb_begin ? kb_end - kb_begin : 0;
+
+  if (warp == 0 && lane == 0) tma_prefetch_desc(&tm);
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+      mbar_init(&split_bar[s], kEpiWarps);
+    }
+    mbar_init(accum_bar, 1);
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc<128>(tmem_slot);
+  fence_before_thread_sync();
+  __syncthreads();
+  fence_after_thread_sync();
+  const uint32_t tmem_acc = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait();
+
+  if (warp == 0) {
+    if (elect_one()) {
+      uint32_t phase = 0;
+      int s = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[s], phase ^ 1);
+        mbar_arrive_expect_tx(&full_bar[s], Plan::TILE);
+        tma_load_3d(smem + s * Plan::STAGE_BYTES, &tm, &full_bar[s], 0, 0, (kb_begin + kb) * a.S);
+        if (++s == STAGES) { s = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = make_idesc(FMT_TF32, 128, 128, false, false);
+    uint32_t phase = 0;
+    int s = 0;
+    for (int kb = 0; kb < num_kb; ++kb) {
+      mbar_wait(SPLIT3 ? &split_bar[s] : &full_bar[s], phase);
+      fence_after_thread_sync();
+      if (elect_one()) {
+        const uint64_t d_hi0 = smem_desc_sw128(smem_u32(smem + s * Plan::STAGE_BYTES), 16, 1024, LAYOUT_SW128);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          const bool acc = (kb > 0) || (kk > 0);
+          const uint64_t d_hi = desc_advance(d_hi0, kk * 32);
+          if constexpr (SPLIT3) {
+            const uint64_t d_lo = desc_advance(d_hi, Plan::TILE);
+            mma_tf32(tmem_acc, d_lo, d_hi, idesc, acc);
+            mma_tf32(tmem_acc, d_hi, d_lo, idesc, true);
+            mma_tf32(tmem_acc, d_hi, d_hi, idesc, true);
+          } else {
+            mma_tf32(tmem_acc, d_hi, d_hi, idesc, acc);
+          }
+        }
+        mma_commit(&empty_bar[s]);
+        if (kb == num_kb - 1) mma_commit(accum_bar);
+      }
+      __syncwarp();
+      if (++s == STAGES) { s = 0; phase ^= 1; }
+    }
+  } else {
+    const int et = (warp - 2) * 32 + lane;      // 0..127
+    if constexpr (SPLIT3) {
+      uint32_t phase = 0;
+      int s = 0;
+      const int cchunk = ((et & 7) ^ ((et >> 3) & 7)) * 4;          // logical columns of this thread's float4s (see gemm body)
+      for (int kb = 0; kb < num_kb; ++kb) {
+        // float4 i = et + 128 it lives in row et/8 + 16 it, i.e. slice (row >> kp_shift) of this k-block
+        float4 cv[8];
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          cv[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (a.center != nullptr) {
+            const int row = (et >> 3) + 16 * it;
+            const int64_t c0 = ((int64_t)(kb_begin + kb) * a.S + (row >> a.kp_shift)) * 32 + cchunk;
+            if (c0 + 3 < a.D) cv[it] = __ldg(reinterpret_cast<const float4*>(a.center + c0));
+          }
+        }
+        mbar_wait(&full_bar[s], phase);
+        float4* hi = reinterpret_cast<float4*>(smem + s * Plan::STAGE_BYTES);
+        float4* lo = hi + Plan::TILE / 16;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const int i = et + 128 * it;
+          const int row = (et >> 3) + 16 * it;
+          float4 x = hi[i], h, l;
+          if ((row & (a.Kp - 1)) < a.K) {                            // padding rows (k >= K) stay exactly zero
+            x.x -= cv[it].x; x.y -= cv[it].y; x.z -= cv[it].z; x.w -= cv[it].w;
+          }
+          h.x = __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u); l.x = x.x - h.x;
+          h.y = __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u); l.y = x.y - h.y;
+          h.z = __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u); l.z = x.z - h.z;
+          h.w = __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u); l.w = x.w - h.w;
+          hi[i] = h;
+          lo[i] = l;
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&split_bar[s]);
+        if (++s == STAGES) { s = 0; phase ^= 1; }
+      }
+    }
+    // ---- epilogue: diagonal Kp x Kp blocks of the 128 x 128 accumulator -> smem -> ordered sum over the S slices
+    const int quarter = warp & 3;
+    const int r = quarter * 32 + lane;           // accumulator row (TMEM lane) of this thread
+    const int sblk = r >> a.kp_shift;            // its slice
+    float* diag = reinterpret_cast<float*>(smem);   // [128][Kp]; the operand ring is idle by now
+    if (num_kb > 0) {
+      mbar_wait(accum_bar, 0);
+      fence_after_thread_sync();
+#pragma unroll 1
+      for (int c0 = 0; c0 < 128; c0 += 32) {
+        float v[32];
+        tmem_ld_32x32(tmem_acc + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0, v);
+#pragma unroll
+        for (int jj = 0; jj < 32; ++jj) {
+          const int col = c0 + jj;
+          if ((col >> a.kp_shift) == sblk) diag[r * a.Kp + (col & (a.Kp - 1))] = v[jj];
+        }
+      }
+    } else {
+      for (int j = 0; j < a.Kp; ++j) diag[r * a.Kp + j] = 0.f;
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    float* out = a.partial + (int64_t)split * a.K * a.K;
+    for (int idx = et; idx < a.K * a.K; idx += 32 * kEpiWarps) {
+      const int i = idx / a.K, j = idx - i * a.K;
+      float acc = 0.f;
+      for (int sl = 0; sl < a.S; ++sl) acc += diag[((sl << a.kp_shift) + i) * a.Kp + j];
+      out[idx] = acc;
+    }
+    fence_before_thread_sync();
+  }
+  __syncthreads();
+  if (warp == 2) {
+    fence_after_thread_sync();
+    tmem_dealloc<128>(tmem_acc);
+  }
+}
+
+// Host side of the packed Gram.  Returns -1 when the shape is not eligible (the caller then uses the generic GEMM).
+int launch_gram_packed(const float* U, int64_t ld, int K, int64_t D, const float* center, float* gram, int64_t ldg, int precise,
+                       int n_split, float* scratch, cudaStream_t st) {
+  if (K > 64 || D % 32 != 0 || D < 32 || (ld * 4) % 16 != 0 || (reinterpret_cast<uintptr_t>(U) & 15) != 0) return -1;
+  int Kp = 8, shift = 3;
+  while (Kp < K) { Kp <<= 1; ++shift; }
+  const int S = 128 / Kp;
+  const int64_t slices = D / 32;
+  const int total_kb = (int)((slices + S - 1) / S);
+  if (n_split < 1) n_split = 1;
+  if (n_split > total_kb) n_split = total_kb;
+  if (n_split > kNumSMs) n_split = kNumSMs;
+  const int kbps = (total_kb + n_split - 1) / n_split;
+  n_split = (total_kb + kbps - 1) / kbps;
+  if (n_split > 1 && scratch == nullptr) return -1;
+  CUtensorMap tm;
+  uint64_t dims[3] = {32, (uint64_t)K, (uint64_t)slices};
+  uint64_t strides[2] = {(uint64_t)ld * 4, (uint64_t)ROW_BYTES};
+  uint32_t box[3] = {32, (uint32_t)Kp, (uint32_t)S};
+  if (int e = ddl_encode_tmap(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, U, dims, strides, box, 1)) return e;
+  GramPackedArgs a;
+  // a single split writes its K x K block straight to the output only when the output is dense; otherwise via scratch
+  const bool direct = (n_split == 1 && ldg == K);
+  if (!direct && scratch == nullptr) return -1;
+  a.partial = direct ? gram : scratch;
+  a.center = center; a.D = D; a.K = K; a.Kp = Kp; a.S = S; a.kp_shift = shift; a.total_kb = total_kb; a.kb_per_split = kbps;
+  const bool split3 = precise != 0 || center != nullptr;
+  if (split3) {
+    auto kern = gram_packed_kernel<true>;
+    static DdlOncePerDevice configured;
+    if (configured.need()) { DDL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GramPackedPlan<true>::TOTAL)); configured.done(); }
+    DDL_CUDA_CHECK(ddl_launch_pdl(kern, dim3(n_split), dim3(kThreads), GramPackedPlan<true>::TOTAL, st, tm, a));
+  } else {
+    auto kern = gram_packed_kernel<false>;
+    static DdlOncePerDevice configured;
+    if (configured.need()) { DDL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GramPackedPlan<false>::TOTAL)); configured.done(); }
+    DDL_CUDA_CHECK(ddl_launch_pdl(kern, dim3(n_split), dim3(kThreads), GramPackedPlan<false>::TOTAL, st, tm, a));
+  }
+  DDL_LAUNCH_CHECK();
+  if (!direct) {
+    const int64_t ge = (int64_t)K * K;
+    DDL_CUDA_CHECK(ddl_launch_pdl(splitk_reduce_kernel, dim3((unsigned)((ge + 255) / 256)), dim3(256), 0, st, (const float*)scratch, n_split, ge,
+                                  1, K, gram, ldg, (int64_t)0, (const float*)nullptr, (int64_t)0, 0, 0.f));
+    DDL_LAUNCH_CHECK();
+  }
+  return DDL_OK;
+}
+
 // ------------------------------------------------------------------------------------------ host
 struct OperandDesc {
   const void* ptr;
@@ -585,6 +814,13 @@ static int gemm_impl(const void* A, int64_t lda, int64_t a_group_stride, int a_m
                      const float* center, int* tile_counters, void* stream) {
   DDL_REQUIRE(M > 0 && N > 0 && K > 0 && G > 0, "empty GEMM");
   DDL_REQUIRE(dtype_bytes == 4 || dtype_bytes == 2, "operands must be fp32 (tf32 math) or bf16");
+  // Gram / SYRK of at most 64 rows: the row-packed kernel (S slices of the rows share one 128-row tile)
+  if (A == B && lda == ldb && G == 1 && M == N && M <= 64 && dtype_bytes == 4 && !a_mn_major && !b_mn_major && bias == nullptr &&
+      act == 0 && alpha == 1.f && beta == 0.f && K % 32 == 0) {
+    const int rc = launch_gram_packed(static_cast<const float*>(A), lda, M, K, center, C, ldc, precise, n_split, scratch,
+                                      (cudaStream_t)stream);
+    if (rc >= 0) return rc;
+  }
   DDL_REQUIRE(!(precise && dtype_bytes != 4), "precise (3xTF32) mode needs fp32 operands");
   const int eb = dtype_bytes, bk = ROW_BYTES / eb;
   DDL_REQUIRE((lda * eb) % 16 == 0 && (ldb * eb) % 16 == 0, "operand leading dimensions must be multiples of 16 bytes");

@@ -251,9 +251,14 @@ class SymmetricAggregator:
                 G = G[order][:, order].contiguous()                # back to client order
             sel, selw, scores = ops.krum_select(U, aggregator.f, aggregator.multi, gram_matrix=G)
             aggregator.last_selected, aggregator.last_scores = sel, scores
-            # selection weights stay on the device (no host round trip); every rank reduces its shard of the SELECTED rows
-            # only - zero-weight rows are not read
-            a.reduce(0, ptrs, None, self.res_ptrs, d0, d1, dev_weights=selw)
+            # selection weights stay on the device (no host round trip) and zero-weight rows are not read
+            if order is None:
+                # the deltas of THIS shard are already local (U, gathered above): new = global + sum_k w_k delta_k is an
+                # HBM-speed pass over local memory + the broadcast of the shard - the selected rows do not cross NVLink twice
+                lptrs = [U.data_ptr() + (k * U.stride(0) - d0) * 4 for k in range(K)]
+                a.reduce(0, lptrs, None, self.res_ptrs, d0, d1, base=gflat.detach(), alpha=1.0, beta=1.0, dev_weights=selw)
+            else:
+                a.reduce(0, ptrs, None, self.res_ptrs, d0, d1, dev_weights=selw)
         if gflat.data_ptr() != self.result.data_ptr():          # servers that adopt `result` as their global arena skip this copy
             gflat.copy_(self.result)
 

@@ -67,6 +67,28 @@ def test_gram(cuda_lib, K, D):
     assert torch.equal(G.gram_tcgen05(u), got), "Gram must be deterministic"
 
 
+@pytest.mark.parametrize("K,D", [(3, 4096), (8, 1_000_000 + 32 * 7), (16, 250_016), (33, 64_000), (64, 320_000), (5, 32), (8, 96)])
+def test_gram_row_packed(cuda_lib, K, D):
+    """K <= 64 rows, D % 32 == 0: the row-packed SYRK kernel (128 / pow2(K) column slices share one MMA tile), plain TF32,
+    3xTF32 and 3xTF32 with the centre subtracted in shared memory (Gram of the deltas), strided rows, vs fp64."""
+    torch.manual_seed(K + D)
+    buf = torch.randn(K, D + 64, device=DEV)                 # strided rows: ld = D + 64
+    u = buf[:, :D]
+    u.mul_(0.01)
+    exp = u.double() @ u.double().T
+    got = G.gram_tcgen05(u)
+    assert _rel_err(got, exp) < 3e-3
+    assert torch.equal(G.gram_tcgen05(u), got), "Gram must be deterministic"
+    assert _rel_err(G.gram_tcgen05(u, precise=True), exp) < 5e-5
+    c = 0.5 + 0.1 * torch.randn(D, device=DEV)               # large common offset: raw-weight Gram would lose the deltas
+    w = (u + c[None, :]).contiguous()
+    gotc = G.gram_tcgen05(w, center=c)
+    d = (w.double() - c.double()[None, :])
+    assert _rel_err(gotc, d @ d.T) < 5e-5
+    out = torch.full((K, K), 7.0, device=DEV)
+    assert G.gram_tcgen05(u, out=out, n_split=1) is out and _rel_err(out, exp) < 3e-3
+
+
 @pytest.mark.parametrize("dims", [[14, 16, 14, 16], [64, 32], [16, 8, 12], [7, 4, 6, 13, 40]])
 def test_gather_gemm_local_parts(cuda_lib, dims):
     """K7 with all parts in local memory: act(cat(parts) @ W.T + b)."""
