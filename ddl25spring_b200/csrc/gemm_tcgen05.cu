@@ -684,8 +684,7 @@ int launch_gram_packed(const float* U, int64_t ld, int K, int64_t D, const float
   const int64_t slices = D / 32;
   const int total_kb = (int)((slices + S - 1) / S);
   if (n_split < 1) n_split = 1;
-  if (n_split > total_kb) n_split = total_kb;
-  if (n_split > kNumSMs) n_split = kNumSMs;
+  if (n_split > total_kb) n_split = total_kb;          // (3xTF32 callers ask for many splits to keep accumulation chains short)
   const int kbps = (total_kb + n_split - 1) / n_split;
   n_split = (total_kb + kbps - 1) / kbps;
   if (n_split > 1 && scratch == nullptr) return -1;
