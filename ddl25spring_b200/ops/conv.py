@@ -33,7 +33,7 @@ from .gemm import gemm
 
 ACT = {None: 0, "none": 0, "relu": 1, "leaky_relu": 2, "tanh": 3}
 _WS: dict = {}
-_SCOPE = {"id": 0}      # a plain global, NOT thread-local: backward passes run on autograd's worker thread and must see the scope
+_SCOPE = {"id": 0, "concurrent": 0}      # a plain global, NOT thread-local: backward passes run on autograd's worker thread and must see the scope
 
 
 @contextlib.contextmanager
@@ -44,10 +44,12 @@ def workspace_scope(scope_id: int):
     that scope's buffers."""
     prev = _SCOPE["id"]
     _SCOPE["id"] = int(scope_id)
-    try:
+    _SCOPE["concurrent"] += 1            # kernels that wait for sibling CTAs (cooperative split-K fix-up) are not used here:
+    try:                                 # two such grids sharing the SMs could each hold what the other still needs
         yield
     finally:
         _SCOPE["id"] = prev
+        _SCOPE["concurrent"] -= 1
 
 
 def _workspace(device) -> dict:

@@ -29,7 +29,9 @@ _TILE_COUNTERS: dict = {}
 
 def _tile_counters(device: torch.device) -> torch.Tensor:
     """Zeroed per-(device, stream) tile counters of the in-kernel split-K fix-up (the kernel leaves them zero; launches on one
-    stream are ordered, so they can share the buffer)."""
+    stream are ordered, so they can share the buffer).  The fix-up makes the CTAs of a tile wait for each other, which is safe
+    for ONE such grid at a time (it is a single wave); code that runs GEMMs concurrently on several streams
+    (``ops.conv.workspace_scope``) gets the separate reduce kernel instead."""
     from .conv import _SCOPE                 # concurrent client slots (fl/server.py) each work inside their own scope
     key = (device.index, torch.cuda.current_stream(device).cuda_stream, _SCOPE["id"])
     t = _TILE_COUNTERS.get(key)
@@ -89,7 +91,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     if n_split > 1:
         scratch = torch.empty(n_split * G * M * N, device=a.device, dtype=torch.float32)
         # split-K partials are reduced inside the kernel by the last-arriving CTA of each tile (no splitk_reduce launch)
-        if L.ddl_gemm_tile_count(int(M), int(N), int(G)) <= MAX_FIXUP_TILES:
+        from .conv import _SCOPE
+        if L.ddl_gemm_tile_count(int(M), int(N), int(G)) <= MAX_FIXUP_TILES and not _SCOPE["concurrent"]:
             counters = _tile_counters(a.device)
     args = (_lib.p(A), _lib.i64(A.stride(1)), _lib.i64(A.stride(0)), int(a_mn),
             _lib.p(B), _lib.i64(B.stride(1)), _lib.i64(B.stride(0)), int(b_mn),
