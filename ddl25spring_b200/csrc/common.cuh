@@ -82,6 +82,24 @@ inline cudaError_t ddl_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 bloc
   cfg.numAttrs = 1;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
+
+// Cooperative launch: for grids whose CTAs wait for one another (the split-K fix-up of gemm_tcgen05.cu).  The runtime either
+// makes every CTA of the grid co-resident or fails the launch - a spin on a sibling CTA can then never wait for a block
+// that has not been scheduled.
+template <typename... KArgs, typename... Args>
+inline cudaError_t ddl_launch_coop(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 #endif
 
 #ifdef __CUDACC__

@@ -758,7 +758,10 @@ int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const Epilogue& ep
     configured.done();
   }
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, G * n_split);
-  DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kThreads), Plan::TOTAL, st, ta, tb, epi, M, N, K, kb_per_split));
+  if (epi.counters != nullptr)      // the split CTAs of a tile wait for each other: cooperative launch (all CTAs co-resident, or an error)
+    DDL_CUDA_CHECK(ddl_launch_coop(kern, grid, dim3(kThreads), Plan::TOTAL, st, ta, tb, epi, M, N, K, kb_per_split));
+  else
+    DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kThreads), Plan::TOTAL, st, ta, tb, epi, M, N, K, kb_per_split));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
