@@ -44,7 +44,9 @@ for (mangled, body), d in zip(funcs, dem):
     lines_out.append(f"{len(instr):6d} instr  {flags:60s} {short}")
     fam = re.sub(r"<.*", "", short).replace("void ", "").strip()
     keep = cnt["UTCHMMA"] or cnt["UTMALDG"] or fam in ("symm_reduce_kernel", "symm_barrier_kernel", "nvls_allreduce_kernel",
-                                                       "weighted_sum_kernel", "bn_stats_kernel", "bn_apply_kernel", "krum_select_kernel")
+                                                       "weighted_sum_kernel", "bn_stats_kernel", "bn_apply_kernel", "krum_select_kernel",
+                                                       "rank_select_mean_kernel", "causal_softmax_kernel", "attn_ds_kernel",
+                                                       "attn_bwd_prep_kernel", "softmax_xent_wide_kernel", "embedding_bwd_kernel")
     if fam not in seen and keep:        # full listings for the tensor-core / TMA / cross-GPU kernels; the rest is in SUMMARY.txt
         seen.add(fam)
         with open(os.path.join(out_dir, fam + ".sass"), "w") as f:
