@@ -203,6 +203,7 @@ def section_dp(rank: int, world: int, steps: int, warmup: int, arena) -> dict:
     import torch.nn.functional as F
 
     from ddl25spring_b200.models.resnet_nhwc import resnet18_nhwc
+    from ddl25spring_b200.ops.nn import kernel_classification_loss
     from ddl25spring_b200.parallel.dp import DataParallel
     from ddl25spring_b200.utils.timing import max_over_ranks
 
@@ -212,7 +213,7 @@ def section_dp(rank: int, world: int, steps: int, warmup: int, arena) -> dict:
     y = torch.randint(0, 10, (batch,), generator=g).cuda()
 
     def loss_fn(m, xb, yb):
-        return F.cross_entropy(m(xb), yb)
+        return kernel_classification_loss(m(xb), yb)
 
     out = {"model": "ResNet-18 (11 181 642 params), NHWC tcgen05 convolution stack", "per_gpu_batch": batch,
            "global_batch": batch * world, "optimizer": "SGD lr 0.05", "steps": steps, "warmup": warmup,
@@ -286,6 +287,7 @@ def section_robust(rank: int, world: int, flusher, coll_arena) -> dict:
     from ddl25spring_b200.fl.attacks import SignFlip, choose_malicious
     from ddl25spring_b200.fl.server import FedAvgServer
     from ddl25spring_b200.models.resnet_nhwc import resnet18_nhwc
+    from ddl25spring_b200.ops.nn import kernel_classification_loss
     from ddl25spring_b200.utils.timing import max_over_ranks
 
     samples, batch, rounds = 256, 64, 3
@@ -297,7 +299,7 @@ def section_robust(rank: int, world: int, flusher, coll_arena) -> dict:
     peaks = _peaks()
     hbm = peaks.get("hbm_gbs", 6551.0) * 1e9
     srv = FedAvgServer(0.05, batch, subsets, 1.0, 1, 10, model_fn=resnet18_nhwc, test_set=ds.test, device="cuda",
-                       loss_fn=F.cross_entropy, include_buffers=True, graph=True, attack=SignFlip(4.0), malicious=mal,
+                       loss_fn=kernel_classification_loss, include_buffers=True, graph=True, attack=SignFlip(4.0), malicious=mal,
                        test_batch_size=1000, concurrent_clients=CLIENTS_PER_GPU)
     D = srv.arena.size
     coll = None

@@ -15,6 +15,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import torch.distributed as dist
 import torch.nn.functional as F
+from ddl25spring_b200.ops.nn import kernel_classification_loss
 
 
 def main():
@@ -38,7 +39,7 @@ def main():
     g = torch.Generator().manual_seed(rank)
     x = torch.randn(a.batch, 3, 32, 32, generator=g).cuda()
     y = torch.randint(0, 10, (a.batch,), generator=g).cuda()
-    loss_fn = lambda m, xb, yb: F.cross_entropy(m(xb), yb)
+    loss_fn = lambda m, xb, yb: kernel_classification_loss(m(xb), yb)
     out = {"world": world, "per_gpu_batch": a.batch, "model": "ResNet-18 (11.18M params)", "convs": a.model, "graph": a.graph,
            "samples_per_s": {}, "ms_per_step": {}}
 

@@ -13,6 +13,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import torch.distributed as dist
 import torch.nn.functional as F
+from ddl25spring_b200.ops.nn import kernel_classification_loss
 
 
 def main():
@@ -46,7 +47,7 @@ def main():
     for name in a.aggregators.split(","):
         kw = dict(n_byzantine=int(mal.sum()), multi=K - 2 * int(mal.sum())) if name == "krum" else {}
         srv = FedAvgServer(0.05, a.batch, subsets, 1.0, 1, 10, model_fn=resnet18, test_set=ds.test, device="cuda",
-                           loss_fn=F.cross_entropy, include_buffers=True, graph=not a.no_graph,
+                           loss_fn=kernel_classification_loss, include_buffers=True, graph=not a.no_graph,
                            aggregator=make_aggregator(name, **kw), attack=SignFlip(4.0), malicious=mal, test_batch_size=1000)
         if world > 1:
             if coll is None:

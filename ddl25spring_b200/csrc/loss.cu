@@ -147,6 +147,24 @@ __global__ void __launch_bounds__(256) eval_top1_kernel(const float* __restrict_
   if (lane == 0 && cnt) atomicAdd(correct, cnt);
 }
 
+// Binary cross-entropy on logits against a CONSTANT target t (the DCGAN losses: real = 1, fake = 0): one block,
+// *loss += scale * sum_i [max(x,0) - x t + log(1 + exp(-|x|))],  grad_i = scale * (sigmoid(x_i) - t).
+// Replaces (reference / north star): F.binary_cross_entropy_with_logits in the federated DCGAN local step.
+__global__ void __launch_bounds__(256) bce_logits_const_kernel(const float* __restrict__ x, int64_t n, float target, float scale,
+                                                               float* __restrict__ loss, float* __restrict__ grad) {
+  pdl_launch_dependents();
+  pdl_wait();
+  __shared__ float red[32];
+  float acc = 0.f;
+  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
+    const float v = x[i];
+    acc += fmaxf(v, 0.f) - v * target + log1pf(__expf(-fabsf(v)));
+    if (grad) grad[i] = scale * (1.f / (1.f + __expf(-v)) - target);
+  }
+  acc = ddl::block_sum(acc, red);
+  if (threadIdx.x == 0) atomicAdd(loss, acc * scale);
+}
+
 // VAE loss: MSE(sum)(xr, x) - 1/2 sum(1 + lv - mu^2 - exp(lv)); gradients written when non-null.
 __global__ void __launch_bounds__(256) vae_loss_kernel(const float* __restrict__ xr, const float* __restrict__ x,
                                                        int64_t nx, const float* __restrict__ mu,
@@ -201,6 +219,14 @@ int ddl_softmax_xent(const float* logits, int64_t ld, const int64_t* target_idx,
   DDL_CUDA_CHECK(ddl_launch_pdl(softmax_xent_kernel, dim3(warp_grid(N)), dim3(256), 0, (cudaStream_t)stream, logits, ld, target_idx, target_stride, target_prob,
                                                                        grad, loss_sum, n_valid, N, C, loss_scale,
                                                                        grad_scale, ignore_index));
+  DDL_LAUNCH_CHECK();
+  return DDL_OK;
+}
+
+int ddl_bce_logits_const(const float* logits, int64_t n, float target, float scale, float* loss_accum, float* grad, void* stream) {
+  DDL_REQUIRE(n >= 0 && loss_accum != nullptr, "bad bce arguments");
+  if (n == 0) return DDL_OK;
+  DDL_CUDA_CHECK(ddl_launch_pdl(bce_logits_const_kernel, dim3(1), dim3(256), 0, (cudaStream_t)stream, logits, n, target, scale, loss_accum, grad));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

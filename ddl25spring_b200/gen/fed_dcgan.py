@@ -14,6 +14,7 @@ import torch.distributed as dist
 import torch.nn.functional as F
 
 from .. import ops
+from ..ops.nn import kernel_bce_logits
 from ..core.arena import FlatArena
 from ..core.seeds import clients_per_round
 from ..models.dcgan import Discriminator, Generator
@@ -49,13 +50,12 @@ def dcgan_local_steps(pair: DCGANPair, images: torch.Tensor, steps: int, batch: 
         # --- D step
         pair.da.grad.zero_()
         fake = G(z)
-        d_loss = F.binary_cross_entropy_with_logits(D(real), torch.ones(batch, device=dev)) + \
-            F.binary_cross_entropy_with_logits(D(fake.detach()), torch.zeros(batch, device=dev))
+        d_loss = kernel_bce_logits(D(real), 1.0) + kernel_bce_logits(D(fake.detach()), 0.0)
         d_loss.backward()
         ops.adam_step(pair.da.flat[:_pad4(pd)], pair.da.grad[:_pad4(pd)], m_d, v_d, step0 + s + 1, lr, beta1, 0.999)
         # --- G step
         pair.ga.grad.zero_()
-        g_loss = F.binary_cross_entropy_with_logits(D(fake), torch.ones(batch, device=dev))
+        g_loss = kernel_bce_logits(D(fake), 1.0)
         g_loss.backward()
         ops.adam_step(pair.ga.flat[:_pad4(pg)], pair.ga.grad[:_pad4(pg)], m_g, v_g, step0 + s + 1, lr, beta1, 0.999)
     return float(d_loss.detach()), float(g_loss.detach())
@@ -82,11 +82,11 @@ class GraphedDCGANStep:
             self.step_t.add_(1)
             pair.da.grad.zero_()
             fake = G(zz)
-            d_loss = F.binary_cross_entropy_with_logits(D(real), ones) + F.binary_cross_entropy_with_logits(D(fake.detach()), zeros)
+            d_loss = kernel_bce_logits(D(real), 1.0) + kernel_bce_logits(D(fake.detach()), 0.0)
             d_loss.backward()
             ops.adam_step(pair.da.flat[:self.pd4], pair.da.grad[:self.pd4], self.m_d, self.v_d, self.step_t, lr, beta1, 0.999)
             pair.ga.grad.zero_()
-            g_loss = F.binary_cross_entropy_with_logits(D(fake), ones)
+            g_loss = kernel_bce_logits(D(fake), 1.0)
             g_loss.backward()
             ops.adam_step(pair.ga.flat[:self.pg4], pair.ga.grad[:self.pg4], self.m_g, self.v_g, self.step_t, lr, beta1, 0.999)
             return torch.stack([d_loss.detach(), g_loss.detach()])

@@ -137,6 +137,12 @@ def kernel_cross_entropy(logits: torch.Tensor, target: torch.Tensor, ignore_inde
     return _XentFn.apply(logits.contiguous(), target.contiguous(), ignore_index, n_valid)
 
 
+def kernel_classification_loss(logits: torch.Tensor, target: torch.Tensor):
+    """Mean cross-entropy of a classifier batch in which every row counts (no ignore_index): the fused kernel alone - no
+    device-side count of valid rows.  The ``loss_fn`` of the ResNet-18 DP / federated runs."""
+    return kernel_cross_entropy(logits, target, n_valid=target.numel())
+
+
 class _SoftXentFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, logits, target):
@@ -157,6 +163,33 @@ def kernel_soft_cross_entropy(logits: torch.Tensor, target: torch.Tensor):
     if not logits.is_cuda or logits.dtype != torch.float32:
         return F.cross_entropy(logits, target)
     return _SoftXentFn.apply(logits.contiguous(), target.contiguous().float())
+
+
+class _BceConstFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target):
+        x = logits.contiguous().view(-1)
+        n = x.numel()
+        loss = torch.zeros((), device=x.device, dtype=torch.float32)
+        grad = torch.empty_like(x)
+        _lib.check(_lib.lib().ddl_bce_logits_const(_lib.p(x), _lib.i64(n), _lib.f32(target), _lib.f32(1.0 / max(n, 1)), _lib.p(loss),
+                                                   _lib.p(grad), _lib.stream()), "ddl_bce_logits_const")
+        ctx.save_for_backward(grad)
+        ctx.shape = logits.shape
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (grad,) = ctx.saved_tensors
+        return (grad * g).view(ctx.shape), None
+
+
+def kernel_bce_logits(logits: torch.Tensor, target: float):
+    """``F.binary_cross_entropy_with_logits(logits, full_like(logits, target))`` (mean) - value and gradient from one launch;
+    the DCGAN discriminator / generator losses (real = 1.0, fake = 0.0)."""
+    if not logits.is_cuda or logits.dtype != torch.float32:
+        return F.binary_cross_entropy_with_logits(logits, torch.full_like(logits, float(target)))
+    return _BceConstFn.apply(logits, float(target))
 
 
 class KernelSoftCrossEntropy(nn.Module):

@@ -11,6 +11,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import torch.distributed as dist
 import torch.nn.functional as F
+from ddl25spring_b200.ops.nn import kernel_classification_loss
 
 from ddl25spring_b200.core.data import SyntheticCIFAR, split
 from ddl25spring_b200.fl.aggregators import make_aggregator
@@ -41,7 +42,7 @@ def main(argv=None):
     n_byz = int(mal.sum())
     kw = dict(n_byzantine=n_byz, multi=max(1, a.clients - 2 * n_byz)) if "krum" in a.aggregator else {}
     srv = FedAvgServer(0.05, a.batch, subsets, 1.0, 1, 10, model_fn=resnet18_nhwc, test_set=ds.test, device="cuda" if cuda else "cpu",
-                       loss_fn=F.cross_entropy, include_buffers=True, graph=cuda and not a.no_graph,
+                       loss_fn=kernel_classification_loss, include_buffers=True, graph=cuda and not a.no_graph,
                        aggregator=make_aggregator(a.aggregator, **kw), attack=SignFlip(a.scale) if n_byz else None, malicious=mal,
                        test_batch_size=min(1000, len(ds.test)))
     if dist.is_initialized() and dist.get_world_size() > 1 and cuda:

@@ -91,6 +91,9 @@ int ddl_adam_step_dev(float* params, const float* grads, float* exp_avg, float* 
 int ddl_softmax_xent(const float* logits, int64_t ld, const int64_t* target_idx, int64_t target_stride,
                      const float* target_prob, float* grad, float* loss_sum, float* n_valid, int64_t N, int C,
                      float loss_scale, float grad_scale, int64_t ignore_index, void* stream);
+/* binary cross-entropy on n logits against one constant target (DCGAN: real = 1, fake = 0) [north star]:
+ * *loss_accum += scale * sum_i bce(x_i, target) (caller zeroes it); grad (may be NULL)_i = scale * (sigmoid(x_i) - target). */
+int ddl_bce_logits_const(const float* logits, int64_t n, float target, float scale, float* loss_accum, float* grad, void* stream);
 /* ---- K17: *correct += #rows whose argmax equals target (ref: hfl_complete.py:172-183) ---------- */
 int ddl_eval_top1(const float* logits, int64_t ld, const int64_t* target, int64_t N, int C, int* correct,
                   void* stream);

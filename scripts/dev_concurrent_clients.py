@@ -10,7 +10,7 @@ K = 8
 ds = SyntheticCIFAR(n_train=K * 128, n_test=500, seed=0)
 subsets = split(ds.train, K, True, 1)
 rows = {}
-for cc in (1, 4):
+for cc in (1, 4, 8):
     srv = FedAvgServer(0.05, 64, subsets, 1.0, 1, 10, model_fn=resnet18_nhwc, test_set=ds.test, device="cuda", loss_fn=F.cross_entropy,
                        include_buffers=True, graph=True, concurrent_clients=cc, test_batch_size=500)
     g = srv.arena.flat.detach().clone()
@@ -25,7 +25,7 @@ for cc in (1, 4):
     t1.record(); torch.cuda.synchronize()
     print("concurrent", cc, "ms per round of local training", t0.elapsed_time(t1) / 3)
 for rnd in range(2):
-    a, b = rows[(1, rnd)], rows[(4, rnd)]
+    a, b = rows[(1, rnd)], rows[(8, rnd)]
     print("round", rnd, "max abs diff per row", [(float((a[i] - b[i]).abs().max())) for i in range(K)], "finite", bool(torch.isfinite(b).all()))
     print("  delta norms seq", [round(float((a[i] - g).norm()), 4) for i in range(K)])
     print("  delta norms con", [round(float((b[i] - g).norm()), 4) for i in range(K)])

@@ -223,3 +223,15 @@ def test_vfl_network_runs_on_kernels(cuda_lib):
     assert hist[-1] < hist[0]
     acc, loss = net.test(tab.x[640:840], tab.y[640:840])
     assert float(acc) > 0.5
+
+
+def test_kernel_bce_logits_matches_torch(cuda_lib):
+    torch.manual_seed(0)
+    for target in (0.0, 1.0):
+        x = (3 * torch.randn(64, 1, 1, 1, device=DEV)).requires_grad_()
+        ref = F.binary_cross_entropy_with_logits(x, torch.full_like(x, target))
+        (g0,) = torch.autograd.grad(ref, x)
+        out = knn.kernel_bce_logits(x, target)
+        (g1,) = torch.autograd.grad(out * 2.0, x)
+        torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(g1, 2.0 * g0, rtol=1e-5, atol=1e-7)
