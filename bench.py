@@ -153,7 +153,7 @@ def timed_rounds(server, steps: int, warmup: int, device, flusher, sampler=None)
     for _ in range(warmup):
         server.run(1)
     barrier_sync(device)
-    total = 0.0
+    total = test_total = 0.0
     accs = []
     if sampler is not None:
         sampler.__enter__()
@@ -162,10 +162,12 @@ def timed_rounds(server, steps: int, warmup: int, device, flusher, sampler=None)
         torch.cuda.synchronize()
         res = server.run(1)              # run() brackets the round with CUDA events on the launching stream
         total += res.device_time_ms[0]
+        test_total += getattr(server, "test_ms_last_round", 0.0)
         accs.append(res.test_accuracy[0])
     barrier_sync(device)
     if sampler is not None:
         sampler.__exit__(None, None, None)
+    timed_rounds.last_test_ms = max_over_ranks(test_total, device) / max(steps, 1)
     return max_over_ranks(total, device), accs
 
 
@@ -437,6 +439,7 @@ def run_ours(args):
         server.run(1)
     ops.reset_launch_count()
     ms_total, accs = timed_rounds(server, args.steps, 0, device, flusher, sampler)
+    test_ms = timed_rounds.last_test_ms
     launches = ops.launch_count()
     del server
     torch.cuda.empty_cache()
@@ -465,6 +468,9 @@ def run_ours(args):
                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4,
                    "api": "PackedFedAvgServer(...).run(1) with data_on_device=False"},
            "gpu_launches": int(launches),
+           "round_breakdown_ms": {"train_and_aggregate": ms - test_ms, "test": test_ms,
+                                  "note": "training + aggregation is weak-scaled (8 clients per GPU); the 10 000-sample test() of "
+                                          "the reference's round is sharded over the ranks, so its share shrinks with N"},
            "config": cfg,
            "notes": {"timing": "CUDA events per round on the launching stream, summed, max over ranks",
                      "collective": "fused peer-memory kernels (parallel/symm_impl.py)" if collective is not None else "single GPU"}}

@@ -97,6 +97,7 @@ class PackedFedAvgServer:
                 self._norm = (MNIST_MEAN, MNIST_STD)
             self.X_all, self.Y_all = X.pin_memory(), Y.pin_memory()
         self.h2d_bytes_last_round = 0
+        self.test_ms_last_round = 0.0
 
         self._engines: dict[int, PackedMnistEngine] = {}
         self._bufs: dict[int, tuple] = {}
@@ -288,9 +289,15 @@ class PackedFedAvgServer:
                 W_local = torch.empty(0, P, device=self.device)
             with torch.no_grad(), span("server/aggregate"):
                 self._aggregate(W_local, mine_pos, weights)
+            ev_t = None
+            if self.device.type == "cuda":
+                ev_t = torch.cuda.Event(enable_timing=True)
+                ev_t.record()
             with span("server/test"):
                 acc = self.test()
             res.device_time_ms.append(timer.stop_ms())
+            if ev_t is not None:                     # share of the round spent in the (rank-sharded) evaluation
+                self.test_ms_last_round = ev_t.elapsed_time(timer.e1)
             if self.collective is not None and self.world > 1:
                 self.collective.arena.check()          # the host is synchronised here anyway: a peer time-out raises instead of
                                                        # silently leaving a stale global model
