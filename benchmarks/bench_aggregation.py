@@ -89,6 +89,20 @@ def main():
             t[name + "_fused"] = timeit(lambda: coll.aggregate(agg, rows_t, mine_pos, w, g), fl)
             if isinstance(agg, Krum):
                 sel[name] = sorted(agg.last_selected.cpu().tolist())
+        coll.two_phase_select = True                  # gather (float4 peer loads) + local selection + peer stores
+        for name in ("median", "trimmed_mean"):
+            t[name + "_two_phase_fused"] = timeit(lambda: coll.aggregate(rules[name], rows_t, mine_pos, w, g), fl)
+        coll.two_phase_select = False
+        # stages of the Krum path, timed separately (each is a collective: every rank runs the same sequence)
+        from ddl25spring_b200.ops.gemm import gram_tcgen05
+        from ddl25spring_b200.parallel.symm_impl import shard_bounds
+        d0, d1 = shard_bounds(DP, world, rank)
+        shard = d1 - d0
+        pad = (-shard) % 32
+        Ub = torch.zeros(K, shard + pad, device="cuda")
+        ptrs_k = [coll.row_ptrs[k % world] + (k // world) * DP * 4 for k in range(K)]
+        t["stage_gather_shard"] = timeit(lambda: coll.arena.reduce(2, ptrs_k, [1.0] * K, [Ub.data_ptr()], d0, d1, base=g, rank_lo=pad // 4), fl)
+        t["stage_gram_local_tf32"] = timeit(lambda: gram_tcgen05(Ub), fl)
         coll.arena.check()
         allrows = torch.empty(world, G_, DP, device="cuda")
 
@@ -122,6 +136,8 @@ def main():
         out["roofline_ms"] = round(roof, 4)
         out["roofline"] = "max(8 local rows read once from HBM at the measured copy bandwidth, (W-1)/W of them over NVLink at 900 GB/s)"
         out["frac_of_roofline"] = {k: round(roof / v, 3) for k, v in out["ms"].items() if k.endswith("_fused")}
+        out["frac_of_measured_nvlink_770"] = {k: round((world - 1) / world * local_bytes / 770e9 * 1e3 / v, 3)
+                                              for k, v in out["ms"].items() if k.endswith("_fused") or k.startswith("stage_gather")}
         out["krum_selected"] = sel
         out["krum_selection_agrees"] = sel.get("krum") == sel.get("krum_torch_fp32") == sel.get("krum_fused_gather")
     if rank == 0:

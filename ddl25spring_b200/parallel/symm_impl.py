@@ -148,8 +148,9 @@ class SymmetricAggregator:
     gathers the rows it needs with peer copies and scores locally)."""
 
     def __init__(self, arena: SymmetricArena | None = None, max_rows_per_rank: int = 16, row_elems: int = 1_200_000,
-                 use_nvls: bool = False, tag: str = ""):
+                 use_nvls: bool = False, tag: str = "", two_phase_select: bool = False):
         self.arena = arena or SymmetricArena()
+        self.two_phase_select = two_phase_select     # median / trimmed mean as gather + local selection + peer stores
         self.tag = tag                     # several aggregators may share one arena: buffer names carry the tag
         self.nvls = None
         if use_nvls:                       # in-switch reduction of the per-GPU partial sums (falls back when unsupported)
@@ -206,7 +207,24 @@ class SymmetricAggregator:
             else:
                 t = aggregator.trim_count(K)
                 lo, hi = t, K - t
-            a.reduce(1, ptrs, w, self.res_ptrs, d0, d1, rank_lo=lo, rank_hi=hi)
+            if self.two_phase_select and d1 > d0:
+                # Two phases: (1) the coordinate-sharded exchange as 128-bit peer loads into a local [K, shard] matrix (the same
+                # gather kernel Krum uses), (2) the selection network over LOCAL memory whose result rows are stored straight
+                # into every replica (peer stores), (3) a GPU-side barrier.  The one-kernel form reads 4 bytes per thread per
+                # row from the peers; here the NVLink side moves float4s and the sort never waits on a remote load.
+                shard = d1 - d0
+                pad = (-shard) % 32
+                Us = getattr(self, "_Usel", None)
+                if Us is None or Us.shape != (K, shard + pad):
+                    Us = self._Usel = torch.zeros(K, shard + pad, device="cuda")
+                a.reduce(2, ptrs, w, [Us.data_ptr()], d0, d1, rank_lo=pad // 4)
+                lptrs = [Us.data_ptr() + (k * Us.stride(0) - d0) * 4 for k in range(K)]
+                _lib.check(a.L.ddl_rank_select_mean_rows(_lib.host_ptrs(lptrs), K, int(lo), int(hi), _lib.host_ptrs(self.res_ptrs),
+                                                         len(self.res_ptrs), _lib.i64(d0), _lib.i64(d1), _lib.stream()),
+                           "ddl_rank_select_mean_rows")
+                a.barrier()
+            else:
+                a.reduce(1, ptrs, w, self.res_ptrs, d0, d1, rank_lo=lo, rank_hi=hi)
         else:
             # Krum: coordinate-sharded.  One fused kernel pulls THIS GPU's slice of every client's update delta
             # over NVLink into a local [K, shard] matrix; the tcgen05 Gram GEMM (K3) runs on that slice; the

@@ -191,9 +191,9 @@ def _fedavg_worker(rank, world, agg_name):
     subsets = split(ds.train, 12, True, 3)
     kw = dict(n_byzantine=1) if agg_name == "krum" else {}
     outs = {}
-    for name, coll in (("fused", make_collective()), ("nccl", None)):
+    for name, coll in (("fused", make_collective(two_phase_select=(agg_name == "median2"))), ("nccl", None)):
         srv = PackedFedAvgServer(0.05, 50, subsets, 0.5, 1, 3, test_set=ds.test, device="cuda", p_drop1=0.0, p_drop2=0.0,
-                                 aggregator=make_aggregator(agg_name, **kw), collective=coll)
+                                 aggregator=make_aggregator(agg_name.rstrip("2"), **kw), collective=coll)
         res = srv.run(2)
         torch.cuda.synchronize()
         outs[name] = (srv.arena.flat.clone().cpu(), res.test_accuracy)
@@ -201,7 +201,7 @@ def _fedavg_worker(rank, world, agg_name):
 
 
 @pytest.mark.timeout(400)
-@pytest.mark.parametrize("agg_name", ["mean", "median", "krum"])
+@pytest.mark.parametrize("agg_name", ["mean", "median", "median2", "krum"])
 def test_packed_fedavg_fused_equals_nccl_path(agg_name):
     world = min(torch.cuda.device_count(), 8)
     outs = run_distributed(_fedavg_worker, world, (agg_name,), timeout=300, backend="nccl")
