@@ -94,14 +94,14 @@ __global__ void __launch_bounds__(256) weighted_sum_kernel(RowTable tab, int K, 
 // ------------------------------------------------------------------------------------------
 template <int KP, bool MEDIAN>
 __global__ void __launch_bounds__(128) rank_select_mean_kernel(RowTable tab, int K, int lo, int hi, OutTable ot,
-                                                               int n_out, int64_t d0, int64_t d1) {
+                                                               int n_out, int64_t d0, int64_t d1, int one) {
   const int64_t d = d0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (d >= d1) return;
   float a[KP];
 #pragma unroll
   for (int k = 0; k < KP; ++k)
     a[k] = (k < K) ? __ldcg(tab.rows[k] + d) : (MEDIAN ? ddl::median_pad(k, K, KP) : __int_as_float(0x7f800000));
-  const float r = MEDIAN ? ddl::median_of<KP>(a, hi - lo == 2) : ddl::window_mean<KP>(a, lo, hi);
+  const float r = MEDIAN ? ddl::median_of<KP>(a, hi - lo == 2, one) : ddl::window_mean<KP>(a, lo, hi, one);
   for (int o = 0; o < n_out; ++o) ot.outs[o][d] = r;
 }
 
@@ -198,8 +198,8 @@ int launch_rank_select(const RowTable& tab, int K, int lo, int hi, const OutTabl
   const int block = 128;
   const int64_t grid = (n + block - 1) / block;
   const bool med = (lo == (K - 1) / 2 && hi == lo + 1) || (K % 2 == 0 && lo == K / 2 - 1 && hi == K / 2 + 1);
-  if (med) rank_select_mean_kernel<KP, true><<<(unsigned)grid, block, 0, st>>>(tab, K, lo, hi, ot, n_out, d0, d1);
-  else rank_select_mean_kernel<KP, false><<<(unsigned)grid, block, 0, st>>>(tab, K, lo, hi, ot, n_out, d0, d1);
+  if (med) rank_select_mean_kernel<KP, true><<<(unsigned)grid, block, 0, st>>>(tab, K, lo, hi, ot, n_out, d0, d1, 1);
+  else rank_select_mean_kernel<KP, false><<<(unsigned)grid, block, 0, st>>>(tab, K, lo, hi, ot, n_out, d0, d1, 1);
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

@@ -11,8 +11,10 @@
 //    SYMMETRICALLY (-inf below, +inf above) so that the median always sits at the centre ranks.
 //  * window_mean<KP>: full sort, then the mean of ranks [lo, hi) (trimmed mean, general rank windows).
 //
-// Non-finite inputs: fminf / fmaxf return the non-NaN operand, so a NaN never propagates - it is overwritten by a copy of a
-// neighbouring value as it moves through the network.  A minority of NaN rows therefore cannot poison a coordinate.
+// Pipe balance: a compare-exchange written as two FMNMX keeps only the ALU pipe busy (64 lanes/clk/SM; ncu showed it 97 %
+// active), so three of every four exchanges compute the max from the min with two exact integer IMADs on the FMA pipe
+// (DDL_CB in select_nets.cuh).
+// Non-finite inputs: a NaN behaves like +inf (it moves to the top ranks); a minority of NaN rows cannot poison a coordinate.
 #pragma once
 #include <cuda_runtime.h>
 #include "select_nets.cuh"   // generated straight-line networks (scripts/gen_select_nets.py)
@@ -20,9 +22,10 @@
 namespace ddl {
 
 // a[] padded symmetrically to KP entries.  pair != 0: mean of the two centre ranks (even K); else the lower centre rank.
+// `one` must be the integer 1 passed as a RUN-TIME value (a kernel argument): see DDL_CB in select_nets.cuh.
 template <int KP>
-__device__ __forceinline__ float median_of(float (&a)[KP], int pair) {
-  median_net<KP>(a);
+__device__ __forceinline__ float median_of(float (&a)[KP], int pair, int one) {
+  median_net<KP>(a, one, -one);
   const float m0 = a[KP / 2 - 1], m1 = a[KP / 2];
   return pair ? 0.5f * (m0 + m1) : m0;
 }
@@ -37,8 +40,8 @@ __device__ __forceinline__ float median_pad(int k, int K, int KP) {
 
 // a[] padded with +inf above K.  Mean of sorted ranks [lo, hi).
 template <int KP>
-__device__ __forceinline__ float window_mean(float (&a)[KP], int lo, int hi) {
-  sort_net<KP>(a);
+__device__ __forceinline__ float window_mean(float (&a)[KP], int lo, int hi, int one) {
+  sort_net<KP>(a, one, -one);
   float s = 0.f;
 #pragma unroll
   for (int k = 0; k < KP; ++k) s += (k >= lo && k < hi) ? a[k] : 0.f;

@@ -103,6 +103,7 @@ struct ReduceArgs {
   int rank, world;
   int* state;                // device-local channel state: [0] go flag, [1] finished blocks, [2] epoch
   int* err;
+  int one;                   // the integer 1 as a run-time value (selection networks: DDL_CB in select_nets.cuh)
   const float* mc_in;        // NVLS: multicast address of the summed buffer (nullptr = peer loads through the row table)
   float* mc_out;             // NVLS: multicast address of the destination (nullptr = peer stores through the out table)
   ddl_opt_args opt;
@@ -254,7 +255,7 @@ __global__ void __launch_bounds__(256) symm_reduce_kernel(RowTable tab, OutTable
         c[k] = MODE == 3 ? ddl::median_pad(k, a.K, KP) : INFINITY;
         if (k < a.K) asm volatile("ld.global.relaxed.sys.f32 %0, [%1];" : "=f"(c[k]) : "l"(tab.rows[k] + d) : "memory");
       }
-      const float s = MODE == 3 ? ddl::median_of<KP>(c, a.rank_hi - a.rank_lo == 2) : ddl::window_mean<KP>(c, a.rank_lo, a.rank_hi);
+      const float s = MODE == 3 ? ddl::median_of<KP>(c, a.rank_hi - a.rank_lo == 2, a.one) : ddl::window_mean<KP>(c, a.rank_lo, a.rank_hi, a.one);
       for (int o = 0; o < a.n_out; ++o) ot.outs[o][d] = s;
     }
   }
@@ -358,7 +359,7 @@ int ddl_symm_reduce(int mode, const float* const* rows, const float* weights, co
   ReduceArgs a;
   a.K = K; a.n_out = n_out; a.v0 = d0 / 4; a.v1 = d1 / 4; a.base = base; a.dev_w = dev_weights; a.alpha = alpha; a.beta = beta;
   a.rank_lo = rank_lo; a.rank_hi = rank_hi; a.rank = rank; a.world = world; a.state = state; a.err = err;
-  a.mc_in = mc_in; a.mc_out = mc_out;
+  a.mc_in = mc_in; a.mc_out = mc_out; a.one = 1;
   memset(&a.opt, 0, sizeof(a.opt));
   if (opt != nullptr && opt->kind != 0) {
     DDL_REQUIRE(mode == 0 && base != nullptr, "the optimizer epilogue needs mode 0 and base = the local parameters");
