@@ -137,45 +137,55 @@ __global__ void __launch_bounds__(256) attack_perturb_kernel(const float* __rest
 //   dist_ij = G_ii + G_jj - 2 G_ij ; score_i = sum of the (K - f - 2) smallest dist_ij, j != i
 //   sel[0..multi) = indices of the `multi` smallest scores (stable), and the FedAvg-style
 //   selection weights w[i] = 1/multi for selected rows, 0 otherwise.
-// One block; thread i owns row i (K <= 128).
+// One block of 32 warps; a warp owns a row at a time (K <= 128).
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) krum_select_kernel(const float* __restrict__ G, int ldg, int K, int f, int multi,
-                                                          float* __restrict__ scores, int* __restrict__ sel,
-                                                          float* __restrict__ selw) {
+__global__ void __launch_bounds__(1024) krum_select_kernel(const float* __restrict__ G, int ldg, int K, int f, int multi,
+                                                           float* __restrict__ scores, int* __restrict__ sel,
+                                                           float* __restrict__ selw) {
+  // One warp per row i (32 warps take rows w, w + 32, ...): the K - 1 distances of the row go to shared memory, every lane
+  // ranks its distances against the whole row (ties by index) and the m = K - f - 2 smallest are summed with a fixed-order
+  // warp reduction.  (The first version kept an insertion-sorted list per THREAD in local memory: 118 us at K = 64.)
   __shared__ float s_score[128];
   __shared__ float s_diag[128];
-  const int i = threadIdx.x;
-  if (i < K) s_diag[i] = G[(int64_t)i * ldg + i];
+  __shared__ float s_d[32][128];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int t = threadIdx.x; t < 128; t += blockDim.x) {
+    s_diag[t] = t < K ? G[(int64_t)t * ldg + t] : 0.f;
+    s_score[t] = __int_as_float(0x7f800000);
+  }
   __syncthreads();
-  float sc = __int_as_float(0x7f800000);
-  if (i < K) {
-    const int m = K - f - 2;
-    // insertion-select of the m smallest distances (K is small; local array lives in registers/L1)
-    float best[128];
-    int nb = 0;
-    for (int j = 0; j < K; ++j) {
-      if (j == i) continue;
+  const int m = K - f - 2;
+  const float inf = __int_as_float(0x7f800000);
+  for (int i = w; i < K; i += 32) {
+    for (int j = lane; j < K; j += 32) {
       // a non-finite distance (NaN / Inf rows, or a Gram entry that overflowed fp32) must count as "infinitely far":
       // fmaxf alone would turn NaN into 0 and make the poisoned row the best candidate
       float dj = s_diag[i] + s_diag[j] - 2.f * G[(int64_t)i * ldg + j];
-      dj = (dj == dj && fabsf(dj) <= 3.0e38f) ? fmaxf(dj, 0.f) : __int_as_float(0x7f800000);
-      int p = nb < m ? nb++ : m;   // position one past the kept range when full
-      if (p == m) {
-        if (dj >= best[m - 1]) continue;
-        p = m - 1;
-      }
-      while (p > 0 && best[p - 1] > dj) { best[p] = best[p - 1]; --p; }
-      best[p] = dj;
+      dj = (dj == dj && fabsf(dj) <= 3.0e38f) ? fmaxf(dj, 0.f) : inf;
+      s_d[w][j] = (j == i) ? inf : dj;
     }
-    sc = 0.f;
-    for (int j = 0; j < nb; ++j) sc += best[j];
-    if (!(s_diag[i] == s_diag[i]) || fabsf(s_diag[i]) > 3.0e38f) sc = __int_as_float(0x7f800000);   // a non-finite row is never selected
-    scores[i] = sc;
+    __syncwarp();
+    float acc = 0.f;
+    for (int j = lane; j < K; j += 32) {
+      if (j == i) continue;
+      const float dj = s_d[w][j];
+      int rank = 0;
+      for (int l = 0; l < K; ++l) {
+        const float dl = s_d[w][l];
+        rank += (l != i) && ((dl < dj) || (dl == dj && l < j));
+      }
+      if (rank < m) acc += dj;
+    }
+    acc = ddl::warp_sum(acc);
+    if (!(s_diag[i] == s_diag[i]) || fabsf(s_diag[i]) > 3.0e38f) acc = inf;   // a non-finite row is never selected
+    if (lane == 0) { s_score[i] = acc; scores[i] = acc; }
+    __syncwarp();
   }
-  s_score[i] = sc;
   __syncthreads();
+  const int i = threadIdx.x;
   if (i < K) {
     // rank of row i among the scores (stable: ties broken by index)
+    const float sc = s_score[i];
     int rank = 0;
     for (int j = 0; j < K; ++j) rank += (s_score[j] < sc) || (s_score[j] == sc && j < i);
     if (rank < multi) sel[rank] = i;
@@ -317,7 +327,7 @@ int ddl_krum_select(const float* gram, int ldg, int K, int n_byzantine, int mult
   DDL_REQUIRE(K >= 1 && K <= 128, "Krum select supports K <= 128, got %d", K);
   DDL_REQUIRE(K - n_byzantine - 2 >= 1, "Krum needs K >= f + 3 (K=%d, f=%d)", K, n_byzantine);
   DDL_REQUIRE(multi >= 1 && multi <= K, "multi=%d outside [1, K]", multi);
-  krum_select_kernel<<<1, 128, 0, (cudaStream_t)stream>>>(gram, ldg, K, n_byzantine, multi, scores, sel, selw);
+  krum_select_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(gram, ldg, K, n_byzantine, multi, scores, sel, selw);
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
