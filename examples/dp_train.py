@@ -46,7 +46,11 @@ def main():
             loss = dp.train_step(loss_fn, x)
             print(itr, float(loss), flush=True)
     else:
-        wa = WeightAveraging(net, torch.optim.Adam(net.parameters(), lr=8e-4))
+        averager = None
+        if a.fused and cuda:            # the replicas' weights are averaged in place by ONE peer-memory kernel per rank (K2b)
+            from ddl25spring_b200.parallel.symm_impl import SymmetricArena, SymmetricWeightAverager
+            averager = SymmetricWeightAverager(SymmetricArena(), sum(p.numel() for p in net.parameters()) + 4096)
+        wa = WeightAveraging(net, torch.optim.Adam(net.parameters(), lr=8e-4), averager=averager)
         for itr in range(a.iters):
             x = next(ds).to(dev)
             loss = loss_fn(net, x)
