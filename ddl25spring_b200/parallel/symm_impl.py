@@ -148,9 +148,12 @@ class SymmetricAggregator:
     gathers the rows it needs with peer copies and scores locally)."""
 
     def __init__(self, arena: SymmetricArena | None = None, max_rows_per_rank: int = 16, row_elems: int = 1_200_000,
-                 use_nvls: bool = False, tag: str = "", two_phase_select: bool = False):
+                 use_nvls: bool = False, tag: str = "", two_phase_select: bool | None = None):
         self.arena = arena or SymmetricArena()
-        self.two_phase_select = two_phase_select     # median / trimmed mean as gather + local selection + peer stores
+        # median / trimmed mean as gather + local selection + peer stores instead of the one-kernel form.  Measured with 8 rows
+        # of 11.2 M floats per GPU: 2 GPUs 0.46 vs 0.40 ms (one kernel wins), 8 GPUs 0.82 vs 0.96 ms (two phases win) - the
+        # default follows the group size.
+        self.two_phase_select = (self.arena.world >= 8) if two_phase_select is None else two_phase_select
         self.tag = tag                     # several aggregators may share one arena: buffer names carry the tag
         self.nvls = None
         if use_nvls:                       # in-switch reduction of the per-GPU partial sums (falls back when unsupported)
