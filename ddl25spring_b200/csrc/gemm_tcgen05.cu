@@ -19,6 +19,7 @@
 //
 // Replaces (reference): every nn.Linear and, via ops/gemm.py: gram(), the
 // pairwise-distance computation of Krum [north star].
+#include <cstdlib>
 #include "common.cuh"
 #include "ddl25_kernels.h"
 #include "tc05.cuh"
@@ -758,8 +759,9 @@ int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const Epilogue& ep
     configured.done();
   }
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, G * n_split);
-  if (epi.counters != nullptr)      // the split CTAs of a tile wait for each other: cooperative launch (all CTAs co-resident, or an error)
-    DDL_CUDA_CHECK(ddl_launch_coop(kern, grid, dim3(kThreads), Plan::TOTAL, st, ta, tb, epi, M, N, K, kb_per_split));
+  static const int fix_mode = getenv("DDL_FIXUP_LAUNCH") ? atoi(getenv("DDL_FIXUP_LAUNCH")) : 0;
+  if (epi.counters != nullptr && fix_mode < 2)   // the split CTAs of a tile wait for each other: cooperative launch (all CTAs co-resident, or an error)
+    DDL_CUDA_CHECK(ddl_launch_coop(kern, grid, dim3(kThreads), Plan::TOTAL, st, fix_mode == 1, ta, tb, epi, M, N, K, kb_per_split));
   else
     DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kThreads), Plan::TOTAL, st, ta, tb, epi, M, N, K, kb_per_split));
   DDL_LAUNCH_CHECK();

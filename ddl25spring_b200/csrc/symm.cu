@@ -109,26 +109,21 @@ struct ReduceArgs {
   ddl_opt_args opt;
 };
 
-// One optimizer update of 4 coordinates: g = summed gradient (already scaled by beta = 1/W), p = parameters.
-__device__ __forceinline__ float4 opt_apply(const ddl_opt_args& o, float4 p, float4 g, int64_t v, float bc1, float bc2_rsqrt) {
+// One optimizer update of 4 coordinates: g = summed gradient (already scaled by beta = 1/W), p = parameters, mb / vb = the
+// moments of these coordinates (loaded by the caller ahead of the peer loads, stored by the caller afterwards).
+__device__ __forceinline__ float4 opt_apply(const ddl_opt_args& o, float4 p, float4 g, float4& mb, float4& vb, float bc1, float bc2_rsqrt) {
   float* pp = &p.x;
   float* gg = &g.x;
+  float* m4 = &mb.x;
+  float* v4 = &vb.x;
   if (o.kind == 1) {                                   // SGD (+ weight decay, + momentum)
-    float4 mb = make_float4(0.f, 0.f, 0.f, 0.f);
-    float* m4 = &mb.x;
-    if (o.m != nullptr) mb = reinterpret_cast<const float4*>(o.m)[v - o.state_off4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       float d = fmaf(o.weight_decay, pp[i], gg[i]);
       if (o.m != nullptr) { m4[i] = fmaf(o.momentum, m4[i], d); d = m4[i]; }
       pp[i] = fmaf(-o.lr, d, pp[i]);
     }
-    if (o.m != nullptr) reinterpret_cast<float4*>(o.m)[v - o.state_off4] = mb;
   } else {                                             // 2 = Adam (L2 in the gradient), 3 = AdamW (decoupled decay)
-    float4 mb = reinterpret_cast<const float4*>(o.m)[v - o.state_off4];
-    float4 vb = reinterpret_cast<const float4*>(o.v)[v - o.state_off4];
-    float* m4 = &mb.x;
-    float* v4 = &vb.x;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       float d = gg[i];
@@ -138,8 +133,6 @@ __device__ __forceinline__ float4 opt_apply(const ddl_opt_args& o, float4 p, flo
       v4[i] = fmaf(o.beta2, v4[i], (1.f - o.beta2) * d * d);
       pp[i] -= (o.lr / bc1) * (m4[i] / (sqrtf(v4[i]) * bc2_rsqrt + o.eps));
     }
-    reinterpret_cast<float4*>(o.m)[v - o.state_off4] = mb;
-    reinterpret_cast<float4*>(o.v)[v - o.state_off4] = vb;
   }
   return p;
 }
@@ -148,7 +141,7 @@ __device__ __forceinline__ float4 opt_apply(const ddl_opt_args& o, float4 p, flo
 // (one coordinate per thread, KP rows), MODE 3: the same for a window that is exactly the median (pruned network).
 // MODE 2: gather of this GPU's coordinate shard of every row.
 template <int MODE, int KP>
-__global__ void __launch_bounds__(256) symm_reduce_kernel(RowTable tab, OutTable ot, PeerPads pp, ReduceArgs a) {
+__global__ void __launch_bounds__(256, MODE == 0 ? 1 : 2) symm_reduce_kernel(RowTable tab, OutTable ot, PeerPads pp, ReduceArgs a) {
   // the channel's epoch is advanced by the LAST block of the previous collective, i.e. it is stable for the whole launch
   const int epoch = ld_acquire_gpu(a.state + 2) + 1;
   // ---- 1. entry barrier
@@ -176,47 +169,74 @@ __global__ void __launch_bounds__(256) symm_reduce_kernel(RowTable tab, OutTable
       bc1 = 1.f - powf(a.opt.beta1, step);
       bc2_rsqrt = 1.f / sqrtf(1.f - powf(a.opt.beta2, step));
     }
-    for (int64_t v = a.v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; healthy && v < a.v1; v += stride) {
-      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    // U coordinates x KC rows in flight per thread: an NVLink round trip is ~2 us, and a bucket kernel runs on few CTAs so
+    // that it can overlap the backward pass - with one coordinate per thread in flight it moved ~10 GB/s per CTA.
+    constexpr int U = 4, KC = 4;
+    const bool has_m = a.opt.kind >= 2 || (a.opt.kind == 1 && a.opt.m != nullptr);
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t v = a.v0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; healthy && v < a.v1; v += stride * U) {
+      float4 acc[U], pb[U], mb[U], vb[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {                    // local operands first: their loads overlap the peer round trip
+        const int64_t vv = v + u * stride;
+        acc[u] = pb[u] = mb[u] = vb[u] = zero4;
+        if (vv < a.v1) {
+          if (a.base != nullptr) pb[u] = reinterpret_cast<const float4*>(a.base)[vv];
+          if (has_m) mb[u] = reinterpret_cast<const float4*>(a.opt.m)[vv - a.opt.state_off4];
+          if (a.opt.kind >= 2) vb[u] = reinterpret_cast<const float4*>(a.opt.v)[vv - a.opt.state_off4];
+        }
+      }
       if (a.mc_in != nullptr) {
-        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
-                     : "=f"(acc.x), "=f"(acc.y), "=f"(acc.z), "=f"(acc.w) : "l"(a.mc_in + 4 * v) : "memory");
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int64_t vv = v + u * stride;
+          if (vv < a.v1)
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                         : "=f"(acc[u].x), "=f"(acc[u].y), "=f"(acc[u].z), "=f"(acc[u].w) : "l"(a.mc_in + 4 * vv) : "memory");
+        }
       } else {
         // zero-weight rows are neither loaded nor accumulated (Krum: only the selected rows cross NVLink; a rejected
-        // row may hold NaN / Inf, which 0 * x would turn into NaN)
-        int k = 0;
-        for (; k + 8 <= a.K; k += 8) {
-          float4 x[8];
-          float w[8];
+        // row may hold NaN / Inf, which 0 * x would turn into NaN).  Rows are accumulated in ascending order.
+        for (int k = 0; k < a.K; k += KC) {
+          float4 x[KC][U];
+          float w[KC];
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            w[u] = a.dev_w ? __ldg(a.dev_w + k + u) : tab.w[k + u];
-            x[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (w[u] != 0.f) x[u] = ld_peer(reinterpret_cast<const float4*>(tab.rows[k + u]) + v);
+          for (int c = 0; c < KC; ++c) {
+            w[c] = 0.f;
+            if (k + c < a.K) w[c] = a.dev_w ? __ldg(a.dev_w + k + c) : tab.w[k + c];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+              const int64_t vv = v + u * stride;
+              x[c][u] = zero4;
+              if (w[c] != 0.f && vv < a.v1) x[c][u] = ld_peer(reinterpret_cast<const float4*>(tab.rows[k + c]) + vv);
+            }
           }
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            acc.x = fmaf(w[u], x[u].x, acc.x); acc.y = fmaf(w[u], x[u].y, acc.y); acc.z = fmaf(w[u], x[u].z, acc.z); acc.w = fmaf(w[u], x[u].w, acc.w);
-          }
-        }
-        for (; k < a.K; ++k) {
-          const float w = a.dev_w ? __ldg(a.dev_w + k) : tab.w[k];
-          if (w == 0.f) continue;
-          const float4 x = ld_peer(reinterpret_cast<const float4*>(tab.rows[k]) + v);
-          acc.x = fmaf(w, x.x, acc.x); acc.y = fmaf(w, x.y, acc.y); acc.z = fmaf(w, x.z, acc.z); acc.w = fmaf(w, x.w, acc.w);
+          for (int c = 0; c < KC; ++c)
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+              acc[u].x = fmaf(w[c], x[c][u].x, acc[u].x); acc[u].y = fmaf(w[c], x[c][u].y, acc[u].y);
+              acc[u].z = fmaf(w[c], x[c][u].z, acc[u].z); acc[u].w = fmaf(w[c], x[c][u].w, acc[u].w);
+            }
         }
       }
-      float4 r = make_float4(a.beta * acc.x, a.beta * acc.y, a.beta * acc.z, a.beta * acc.w);
-      if (a.opt.kind != 0) {
-        r = opt_apply(a.opt, reinterpret_cast<const float4*>(a.base)[v], r, v, bc1, bc2_rsqrt);
-      } else if (a.base != nullptr) {
-        const float4 b = reinterpret_cast<const float4*>(a.base)[v];
-        r.x = fmaf(a.alpha, b.x, r.x); r.y = fmaf(a.alpha, b.y, r.y); r.z = fmaf(a.alpha, b.z, r.z); r.w = fmaf(a.alpha, b.w, r.w);
-      }
-      if (a.mc_out != nullptr) {
-        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(a.mc_out + 4 * v), "f"(r.x), "f"(r.y), "f"(r.z), "f"(r.w) : "memory");
-      } else {
-        for (int o = 0; o < a.n_out; ++o) reinterpret_cast<float4*>(ot.outs[o])[v] = r;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t vv = v + u * stride;
+        if (vv >= a.v1) continue;
+        float4 r = make_float4(a.beta * acc[u].x, a.beta * acc[u].y, a.beta * acc[u].z, a.beta * acc[u].w);
+        if (a.opt.kind != 0) {
+          r = opt_apply(a.opt, pb[u], r, mb[u], vb[u], bc1, bc2_rsqrt);
+          if (has_m) reinterpret_cast<float4*>(a.opt.m)[vv - a.opt.state_off4] = mb[u];
+          if (a.opt.kind >= 2) reinterpret_cast<float4*>(a.opt.v)[vv - a.opt.state_off4] = vb[u];
+        } else if (a.base != nullptr) {
+          r.x = fmaf(a.alpha, pb[u].x, r.x); r.y = fmaf(a.alpha, pb[u].y, r.y); r.z = fmaf(a.alpha, pb[u].z, r.z); r.w = fmaf(a.alpha, pb[u].w, r.w);
+        }
+        if (a.mc_out != nullptr) {
+          asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(a.mc_out + 4 * vv), "f"(r.x), "f"(r.y), "f"(r.z), "f"(r.w) : "memory");
+        } else {
+          for (int o = 0; o < a.n_out; ++o) reinterpret_cast<float4*>(ot.outs[o])[vv] = r;
+        }
       }
     }
   }

@@ -17,6 +17,8 @@ Reference call sites replaced: every ``nn.Linear`` listed in SURVEY §2.5.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import _lib
@@ -24,6 +26,10 @@ from . import _lib
 ACT = {"none": 0, None: 0, "relu": 1, "leaky_relu": 2}
 PRECISE_CHAIN = 1024
 MAX_FIXUP_TILES = 8192
+# In-kernel split-K fix-up (the split CTAs of a tile meet at a counter and each reduces its share of the rows; cooperative
+# launch).  Opt-in: on the LLaMA step the separate reduce kernel behind a programmatic dependent launch measured faster
+# (2.74 ms vs 3.30 ms cooperative / 3.20 ms programmatic launch of the fix-up), see profiles/r2_llama_fixup_modes.txt.
+USE_FIXUP = os.environ.get("DDL_GEMM_FIXUP", "0") == "1"
 _TILE_COUNTERS: dict = {}
 
 
@@ -90,9 +96,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     scratch = counters = None
     if n_split > 1:
         scratch = torch.empty(n_split * G * M * N, device=a.device, dtype=torch.float32)
-        # split-K partials are reduced inside the kernel by the last-arriving CTA of each tile (no splitk_reduce launch)
         from .conv import _SCOPE
-        if L.ddl_gemm_tile_count(int(M), int(N), int(G)) <= MAX_FIXUP_TILES and not _SCOPE["concurrent"]:
+        if USE_FIXUP and L.ddl_gemm_tile_count(int(M), int(N), int(G)) <= MAX_FIXUP_TILES and not _SCOPE["concurrent"]:
             counters = _tile_counters(a.device)
     args = (_lib.p(A), _lib.i64(A.stride(1)), _lib.i64(A.stride(0)), int(a_mn),
             _lib.p(B), _lib.i64(B.stride(1)), _lib.i64(B.stride(0)), int(b_mn),

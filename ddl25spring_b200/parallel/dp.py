@@ -140,7 +140,10 @@ class DataParallel:
         b = self.buckets[bi]
         view = self.arena.grad[b.lo:b.hi]
         if self.reducer is not None:
-            b.work = self.reducer(view, b.lo, b.hi)
+            if hasattr(self.reducer, "tail_ctas"):   # the step's last bucket overlaps nothing: the reducer may use the whole GPU for it
+                b.work = self.reducer(view, b.lo, b.hi, last=len(self._launched) == len(self.buckets) - 1)
+            else:
+                b.work = self.reducer(view, b.lo, b.hi)
         else:
             b.work = dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
         self._launched.append(bi)
@@ -199,6 +202,7 @@ class DataParallel:
                 from ..utils.graphs import GraphedStep
 
                 def fwd_bwd(*b):
+                    self._launched = []
                     loss = loss_fn(self.module, *b)
                     loss.backward()                      # accumulates in place into the (static) flat gradient arena
                     if in_graph:

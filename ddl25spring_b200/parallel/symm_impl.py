@@ -317,8 +317,11 @@ class SymmetricGradReducer:
     capturable = True
 
     def __init__(self, arena: SymmetricArena, n_elems: int, max_ctas: int = 32, fuse_optimizer: bool = True,
-                 use_nvls: bool = False, tag: str = ""):
+                 use_nvls: bool = False, tag: str = "", tail_ctas: int = 148):
         self.arena = arena
+        # buckets reduced WHILE the backward pass still runs take `max_ctas` CTAs (they share the SMs with its GEMMs); the
+        # step's last bucket has nothing left to overlap with and takes `tail_ctas` (LLaMA DP, 2 GPUs: 3.11 -> 2.87 ms / step)
+        self.tail_ctas = tail_ctas
         n = (n_elems + 127) // 128 * 128
         self.n = n
         self.mc_grad = self.mc_param = 0
@@ -396,21 +399,22 @@ class SymmetricGradReducer:
                 self.step_dev.add_(1)
 
     # ---- reducer protocol
-    def __call__(self, view: torch.Tensor, lo: int, hi: int):
+    def __call__(self, view: torch.Tensor, lo: int, hi: int, last: bool = False):
         a = self.arena
         ready = torch.cuda.Event()
         ready.record()
         s0, s1 = shard_bounds(hi - lo, a.world, a.rank)
         fused = self.fuses_optimizer and self._opt is not None
+        ctas = max(self.max_ctas, self.tail_ctas) if last else self.max_ctas
         with torch.cuda.stream(self.stream):
             self.stream.wait_event(ready)
             if fused:
                 a.reduce(0, self.ptrs, [1.0] * a.world, self.param_ptrs, lo + s0, lo + s1, base=self.param, beta=1.0 / a.world,
-                         max_ctas=self.max_ctas, channel=self.channel, opt=self._opt_args(lo, hi, s0, s1),
+                         max_ctas=ctas, channel=self.channel, opt=self._opt_args(lo, hi, s0, s1),
                          mc_in=self.mc_grad, mc_out=self.mc_param)
                 view.zero_()          # every peer has read this bucket (exit barrier): ready for the next backward
             else:
-                a.reduce(0, self.ptrs, [1.0] * a.world, self.ptrs, lo + s0, lo + s1, max_ctas=self.max_ctas, channel=self.channel,
+                a.reduce(0, self.ptrs, [1.0] * a.world, self.ptrs, lo + s0, lo + s1, max_ctas=ctas, channel=self.channel,
                          mc_in=self.mc_grad, mc_out=self.mc_grad)
             done = torch.cuda.Event()
             done.record()

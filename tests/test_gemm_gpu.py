@@ -36,7 +36,9 @@ def test_gemm_mn_major_operands(cuda_lib, precise):
     assert _rel_err(dw, dy.double().T @ x.double()) < tol
 
 
-def test_gemm_grouped_and_splitk(cuda_lib):
+@pytest.mark.parametrize("fixup", [False, True])
+def test_gemm_grouped_and_splitk(cuda_lib, fixup, monkeypatch):
+    monkeypatch.setattr(G, "USE_FIXUP", fixup)      # separate reduce kernel / in-kernel cooperative fix-up
     Gn, M, N, K = 8, 100, 128, 1024
     a, b = torch.randn(Gn, M, K, device=DEV), torch.randn(Gn, N, K, device=DEV)
     bias = torch.randn(Gn, N, device=DEV)
