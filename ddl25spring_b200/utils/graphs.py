@@ -11,6 +11,7 @@ on every call.  On CPU (or with ``enabled=False``) it just calls ``fn``.
 """
 from __future__ import annotations
 
+import gc
 from typing import Callable, Sequence
 
 import torch
@@ -34,8 +35,18 @@ class GraphedStep:
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
-            self.static_out = fn(*self.static_in)
+        # A dead reference cycle that still owns an earlier CUDAGraph (a previous model's step) must not be collected WHILE
+        # this capture runs: destroying a graph is not a capturable call and invalidates the capture.  torch.cuda.graph no
+        # longer collects on entry, so collect now and keep the cyclic collector off until the capture has ended.
+        gc.collect()
+        gc_was_on = gc.isenabled()
+        gc.disable()
+        try:
+            with torch.cuda.graph(self.graph):
+                self.static_out = fn(*self.static_in)
+        finally:
+            if gc_was_on:
+                gc.enable()
 
     def __call__(self, *inputs):
         if not self.enabled:

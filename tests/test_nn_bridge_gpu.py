@@ -235,3 +235,36 @@ def test_kernel_bce_logits_matches_torch(cuda_lib):
         (g1,) = torch.autograd.grad(out * 2.0, x)
         torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-6)
         torch.testing.assert_close(g1, 2.0 * g0, rtol=1e-5, atol=1e-7)
+
+
+def test_second_graph_capture_survives_a_dead_cycle_owning_the_first_graph(cuda_lib):
+    """A finished model's step graph kept alive only by a reference cycle must not be collected in the middle of the next
+    capture (destroying a CUDA graph there invalidates it): GraphedStep collects first and holds the collector off."""
+    import gc
+    from ddl25spring_b200.utils.graphs import GraphedStep
+
+    class Holder:
+        pass
+
+    def make():
+        lin = torch.nn.Linear(64, 64).to(DEV)
+        h = Holder()
+
+        def step(x):
+            h.n = getattr(h, "n", 0) + 1                 # closure -> holder -> graphed step -> closure: a cycle
+            y = knn.kernel_linear(x, lin.weight, lin.bias)
+            junk = [[] for _ in range(2000)]             # enough container allocations to trigger automatic collections
+            for j in junk:
+                j.append(junk)
+            return y.sum()
+
+        h.g = GraphedStep(step, (torch.randn(32, 64, device=DEV),))
+        return h
+
+    gc.collect()
+    h1 = make()
+    del h1                                               # dead cycle, first graph still alive inside it
+    h2 = make()
+    out = h2.g(torch.ones(32, 64, device=DEV))
+    assert torch.isfinite(out).item()
+    assert gc.isenabled()
