@@ -83,6 +83,41 @@ __global__ void __launch_bounds__(256) swiglu_bwd_kernel(const float4* __restric
   }
 }
 
+// Gate and up projections computed by ONE GEMM against the stacked weight [Wg; Wu]: gu is [M, 2F] with the gate in columns
+// [0, F) and the up projection in [F, 2F) of every row.  h = silu(gate) * up is [M, F]; the backward writes d(gu) in the same
+// layout so that ONE dgrad GEMM and ONE wgrad GEMM serve both projections.
+__global__ void __launch_bounds__(256) swiglu_gu_fwd_kernel(const float4* __restrict__ gu, float4* __restrict__ h, int64_t M, int F4) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int64_t n4 = M * F4;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t m = i / F4;
+    const int f = (int)(i - m * F4);
+    const float4 a = gu[m * 2 * F4 + f], b = gu[m * 2 * F4 + F4 + f];
+    float4 o;
+    o.x = a.x / (1.f + __expf(-a.x)) * b.x; o.y = a.y / (1.f + __expf(-a.y)) * b.y;
+    o.z = a.z / (1.f + __expf(-a.z)) * b.z; o.w = a.w / (1.f + __expf(-a.w)) * b.w;
+    h[i] = o;
+  }
+}
+
+__global__ void __launch_bounds__(256) swiglu_gu_bwd_kernel(const float4* __restrict__ gu, const float4* __restrict__ dh,
+                                                            float4* __restrict__ dgu, int64_t M, int F4) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int64_t n4 = M * F4;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t m = i / F4;
+    const int f = (int)(i - m * F4);
+    const float4 a = gu[m * 2 * F4 + f], b = gu[m * 2 * F4 + F4 + f], d = dh[i];
+    float4 x, y;
+    swiglu_grad(a.x, b.x, d.x, x.x, y.x); swiglu_grad(a.y, b.y, d.y, x.y, y.y);
+    swiglu_grad(a.z, b.z, d.z, x.z, y.z); swiglu_grad(a.w, b.w, d.w, x.w, y.w);
+    dgu[m * 2 * F4 + f] = x;
+    dgu[m * 2 * F4 + F4 + f] = y;
+  }
+}
+
 int blocks_for(int64_t work) {
   int64_t b = (work + 255) / 256;
   if (b > kNumSMs * 16) b = kNumSMs * 16;
@@ -122,6 +157,22 @@ int ddl_swiglu_bwd(const float* g, const float* u, const float* dh, float* dg, f
   DDL_CUDA_CHECK(ddl_launch_pdl(swiglu_bwd_kernel, dim3(blocks_for(n / 4)), dim3(256), 0, (cudaStream_t)stream,
                                 reinterpret_cast<const float4*>(g), reinterpret_cast<const float4*>(u), reinterpret_cast<const float4*>(dh),
                                 reinterpret_cast<float4*>(dg), reinterpret_cast<float4*>(du), n / 4));
+  DDL_LAUNCH_CHECK();
+  return DDL_OK;
+}
+
+int ddl_swiglu_gu_fwd(const float* gu, float* h, int64_t M, int F, void* stream) {
+  DDL_REQUIRE(M > 0 && F > 0 && F % 4 == 0, "swiglu_gu: F=%d must be a positive multiple of 4", F);
+  DDL_CUDA_CHECK(ddl_launch_pdl(swiglu_gu_fwd_kernel, dim3(blocks_for(M * (F / 4))), dim3(256), 0, (cudaStream_t)stream,
+                                reinterpret_cast<const float4*>(gu), reinterpret_cast<float4*>(h), M, F / 4));
+  DDL_LAUNCH_CHECK();
+  return DDL_OK;
+}
+
+int ddl_swiglu_gu_bwd(const float* gu, const float* dh, float* dgu, int64_t M, int F, void* stream) {
+  DDL_REQUIRE(M > 0 && F > 0 && F % 4 == 0, "swiglu_gu: F=%d must be a positive multiple of 4", F);
+  DDL_CUDA_CHECK(ddl_launch_pdl(swiglu_gu_bwd_kernel, dim3(blocks_for(M * (F / 4))), dim3(256), 0, (cudaStream_t)stream,
+                                reinterpret_cast<const float4*>(gu), reinterpret_cast<const float4*>(dh), reinterpret_cast<float4*>(dgu), M, F / 4));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }

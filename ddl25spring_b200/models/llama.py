@@ -73,9 +73,12 @@ class GatedMLP(nn.Module):
         self.w_gate = nn.Linear(dmodel, hidden, bias=False)
         self.w_up = nn.Linear(dmodel, hidden, bias=False)
         self.w_down = nn.Linear(hidden, dmodel, bias=False)
-        self.act_fn = None         # ops.nn.use_kernels() installs the fused SwiGLU here
+        self.act_fn = None         # ops.nn.use_kernels() installs the fused SwiGLU here ...
+        self.gate_up_fn = None     # ... and the one-GEMM gate + up projection over the stacked weight [w_gate; w_up]
 
     def forward(self, x):
+        if self.gate_up_fn is not None:
+            return self.w_down(self.gate_up_fn(x, self.w_gate.weight, self.w_up.weight))
         if self.act_fn is not None:
             return self.w_down(self.act_fn(self.w_gate(x), self.w_up(x)))
         return self.w_down(F.silu(self.w_gate(x)) * self.w_up(x))

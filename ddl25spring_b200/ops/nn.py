@@ -438,6 +438,76 @@ def kernel_swiglu(g, u):
     return _SwiGluFn.apply(g, u)
 
 
+def _stacked(wg: torch.Tensor, wu: torch.Tensor) -> bool:
+    """True when ``wu`` starts where ``wg`` ends in the same storage, i.e. [wg; wu] is one contiguous [2F, D] matrix (adjacent
+    views of a flat arena, or the pair laid out by :func:`stack_gate_up`)."""
+    return (wg.shape == wu.shape and wg.is_contiguous() and wu.is_contiguous()
+            and wg.untyped_storage().data_ptr() == wu.untyped_storage().data_ptr()
+            and wu.storage_offset() == wg.storage_offset() + wg.numel())
+
+
+def stack_gate_up(mlp) -> None:
+    """Lay ``mlp.w_gate.weight`` and ``mlp.w_up.weight`` out back to back in one buffer (values kept, Parameters kept: only
+    their ``.data`` moves).  core.arena.FlatArena packs parameters in registration order, which keeps the pair adjacent."""
+    wg, wu = mlp.w_gate.weight, mlp.w_up.weight
+    if _stacked(wg.data, wu.data) or wg.shape != wu.shape:
+        return
+    buf = torch.cat([wg.data.reshape(-1), wu.data.reshape(-1)])
+    n = wg.numel()
+    wg.data, wu.data = buf[:n].view_as(wg), buf[n:].view_as(wu)
+
+
+class _GateUpSwiGluFn(torch.autograd.Function):
+    """``silu(x Wg^T) * (x Wu^T)`` with the two projections as ONE GEMM against the stacked weight [Wg; Wu] (N = 2F), a SwiGLU
+    kernel on the stacked [M, 2F] result, and a backward of ONE dgrad GEMM (K = 2F) + ONE wgrad GEMM instead of two each plus
+    the add of the two input gradients.  Replaces (reference): simplellm's gated MLP inside every LLaMA block
+    (lab/tutorial_1b/primer/intro.py:17 via ``LLama``)."""
+
+    @staticmethod
+    def forward(ctx, x, wg, wu, precise):
+        Fh, D = wg.shape
+        x2 = x.reshape(-1, D)
+        if x2.stride(1) != 1 or x2.stride(0) != D:
+            x2 = x2.contiguous()
+        M = x2.shape[0]
+        w2 = torch.as_strided(wg, (2 * Fh, D), (D, 1))
+        gu = gemm(x2, w2, precise=precise)
+        h = torch.empty(M, Fh, device=x.device, dtype=torch.float32)
+        _lib.check(_lib.lib().ddl_swiglu_gu_fwd(_lib.p(gu), _lib.p(h), _lib.i64(M), int(Fh), _lib.stream()), "ddl_swiglu_gu_fwd")
+        ctx.save_for_backward(x2, wg, gu)
+        ctx.precise, ctx.shape = precise, x.shape
+        return h.view(*x.shape[:-1], Fh)
+
+    @staticmethod
+    def backward(ctx, dh):
+        x2, wg, gu = ctx.saved_tensors
+        Fh, D = wg.shape
+        M = x2.shape[0]
+        dh2 = dh.reshape(M, Fh)
+        if not dh2.is_contiguous():
+            dh2 = dh2.contiguous()
+        dgu = torch.empty_like(gu)
+        _lib.check(_lib.lib().ddl_swiglu_gu_bwd(_lib.p(gu), _lib.p(dh2), _lib.p(dgu), _lib.i64(M), int(Fh), _lib.stream()), "ddl_swiglu_gu_bwd")
+        w2 = torch.as_strided(wg, (2 * Fh, D), (D, 1))
+        gx = gwg = gwu = None
+        if ctx.needs_input_grad[0]:
+            gx = gemm(dgu, w2, b_mn=True, precise=ctx.precise).view(ctx.shape)
+        if ctx.needs_input_grad[1] or ctx.needs_input_grad[2]:
+            gw2 = gemm(dgu, x2, a_mn=True, b_mn=True, precise=ctx.precise)           # [2F, D]
+            gwg, gwu = gw2[:Fh], gw2[Fh:]
+        return gx, gwg, gwu, None
+
+
+def kernel_gate_up_swiglu(x, wg, wu, precise: bool = True):
+    """The gated MLP's first half.  Stacked weights (see :func:`stack_gate_up`) take the one-GEMM path; anything else the
+    two-GEMM path through :func:`kernel_linear` and :func:`kernel_swiglu`."""
+    Fh, D = wg.shape
+    if (x.is_cuda and x.dtype == torch.float32 and wg.dtype == torch.float32 and x.numel() and D % 32 == 0 and Fh % 32 == 0
+            and _stacked(wg, wu)):
+        return _GateUpSwiGluFn.apply(x, wg, wu, precise)
+    return kernel_swiglu(kernel_linear(x, wg, None, precise), kernel_linear(x, wu, None, precise))
+
+
 class _EmbeddingFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, tokens, weight, padding_idx):
@@ -490,4 +560,7 @@ def use_kernels(model: nn.Module, precise: bool = True) -> nn.Module:
             mod.qkv_fn = kernel_rope_qkv
         elif isinstance(mod, GatedMLP):
             mod.act_fn = kernel_swiglu
+            if mod.w_gate.bias is None and mod.w_up.bias is None:
+                stack_gate_up(mod)
+                mod.gate_up_fn = (lambda pr: (lambda x, wg, wu: kernel_gate_up_swiglu(x, wg, wu, pr)))(precise)
     return model

@@ -322,6 +322,9 @@ int ddl_embedding_bwd(const float* grad_out, const int64_t* tokens, float* dW_ac
                       int64_t padding_idx, void* stream);
 int ddl_swiglu_fwd(const float* g, const float* u, float* h, int64_t n, void* stream);               /* h = silu(g) * u */
 int ddl_swiglu_bwd(const float* g, const float* u, const float* dh, float* dg, float* du, int64_t n, void* stream);
+/* stacked layout: gu = [M, 2F] (gate | up per row, the output of ONE GEMM against [Wg; Wu]); h, dh = [M, F]; dgu = [M, 2F] */
+int ddl_swiglu_gu_fwd(const float* gu, float* h, int64_t M, int F, void* stream);
+int ddl_swiglu_gu_bwd(const float* gu, const float* dh, float* dgu, int64_t M, int F, void* stream);
 
 /* ---- K9 general: NHWC / OHWI convolutions as tap GEMMs on tcgen05 (csrc/conv_tcgen05.cu) -------------------------------
  * (ref: nn.Conv2d via ATen/cuDNN, lab/tutorial_1a/hfl_complete.py:51,53; ResNet-18 / DCGAN convs of the north star.)

@@ -268,3 +268,24 @@ def test_second_graph_capture_survives_a_dead_cycle_owning_the_first_graph(cuda_
     out = h2.g(torch.ones(32, 64, device=DEV))
     assert torch.isfinite(out).item()
     assert gc.isenabled()
+
+
+def test_stacked_gate_up_swiglu_matches_torch(cuda_lib):
+    """One GEMM against [Wg; Wu] + stacked SwiGLU kernel, forward and all three gradients, vs fp32 torch autograd."""
+    from ddl25spring_b200.models.llama import GatedMLP
+    torch.manual_seed(3)
+    mlp = GatedMLP(96, 160).to(DEV)
+    x = torch.randn(5, 40, 96, device=DEV, requires_grad=True)
+    y0 = mlp(x); y0.square().sum().backward()
+    g0 = [x.grad.clone()] + [p.grad.clone() for p in mlp.parameters()]
+    x.grad = None; mlp.zero_grad()
+    knn.use_kernels(mlp)
+    assert mlp.gate_up_fn is not None and knn._stacked(mlp.w_gate.weight, mlp.w_up.weight)
+    y1 = mlp(x); y1.square().sum().backward()
+    torch.testing.assert_close(y1, y0, rtol=1e-4, atol=1e-4)
+    for a, b in zip([x.grad] + [p.grad for p in mlp.parameters()], g0):
+        torch.testing.assert_close(a, b, rtol=2e-4, atol=2e-3)
+    # weights that are NOT back to back in memory take the two-GEMM path and give the same answer
+    mlp.w_up.weight.data = mlp.w_up.weight.data.clone()
+    assert not knn._stacked(mlp.w_gate.weight, mlp.w_up.weight)
+    torch.testing.assert_close(mlp(x), y1, rtol=1e-5, atol=1e-5)
