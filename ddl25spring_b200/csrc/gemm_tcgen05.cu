@@ -32,7 +32,19 @@ using namespace tc05;
 constexpr int BM = 128;
 constexpr int ROW_BYTES = 128;          // one swizzle row: 32 tf32 or 64 bf16 along the contiguous dim
 constexpr int kEpiWarps = 4;
-constexpr int kThreads = 32 * (2 + kEpiWarps);
+constexpr int kThreads = 32 * (2 + kEpiWarps);           // gram_packed_kernel
+// Splitter warps of the general GEMM body (3xTF32 hi / lo split): warps 2 .. 2 + kSplitWarps; the first kEpiWarps of them
+// then drain the accumulator.  Measured on B200 (768 x 864 x 288, scripts/dev/gemm_kloop_cost.py): 8 splitter warps are no
+// faster than 4 - the 3xTF32 k-loop is bound by shared-memory bandwidth (12 MMAs x 8 KB of operands + 32 KB of TMA writes
+// + the splitter's traffic per k-block, at 128 B/clk), which is why not rewriting the hi tile (Epilogue::keep_hi) pays.
+constexpr int kSplitWarps = 4;
+constexpr int kGemmThreads = 32 * (2 + kSplitWarps);
+
+// 3xTF32: 1 = use the staged fp32 tile as the hi operand without rewriting it (DDL_GEMM_KEEP_HI overrides)
+inline int keep_hi_default() {
+  static const int v = getenv("DDL_GEMM_KEEP_HI") ? atoi(getenv("DDL_GEMM_KEEP_HI")) : 1;
+  return v;
+}
 
 struct Epilogue {
   float* C;             // output (or partials scratch when n_split > 1)
@@ -52,6 +64,7 @@ struct Epilogue {
   float alpha;
   float beta;           // direct (n_split == 1) path only: C = act(alpha*acc + beta*C_old + bias)
   int n_split;          // > 1: write raw partial tiles to C = scratch[split][g][M][N] (ldc = N)
+  int keep_hi;          // SPLIT3: the staged fp32 tile serves as the hi operand as it is (the tensor core truncates to TF32)
   int same_ab;          // A and B are the same matrix (Gram / SYRK): stage each tile once, use it as both operands
   const float* center;  // SPLIT3 only, may be null: K-vector subtracted from every row of the staged tiles before the hi/lo
                         // split (Krum scores update DELTAS u_k - global; re-centring in shared memory means the K x D delta
@@ -140,7 +153,7 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
-      mbar_init(&split_bar[s], kEpiWarps);
+      mbar_init(&split_bar[s], kSplitWarps);
     }
     mbar_init(accum_bar, 1);
     mbar_fence_init();
@@ -248,15 +261,14 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
     }
   } else {
     // ===================== splitter (PRECISE) + epilogue warps =====================
-    const int ew = warp - 2;                 // 0..3
-    const int et = ew * 32 + lane;           // 0..127
+    const int et = (warp - 2) * 32 + lane;   // index among the splitter threads; 0..127 are the epilogue threads
     if constexpr (SPLIT3) {
       uint32_t phase = 0;
       int s = 0;
       constexpr int NV = (Plan::A_BYTES + Plan::B_BYTES) / 16;   // float4 count of A|B (contiguous)
       const int nv = epi.same_ab ? Plan::A_BYTES / 16 : NV;      // SYRK: only the A tile was staged
       // Re-centring: float4 i of a K-major 128B-swizzled tile is row i/8, physical 16-byte chunk i%8, i.e. logical
-      // columns 4*((i%8) ^ (row%8)) .. +3.  With 128 splitter threads striding by 128, a thread's chunk and row%8 never
+      // columns 4*((i%8) ^ (row%8)) .. +3.  With 32 * kSplitWarps splitter threads striding by as many, a thread's chunk and row%8 never
       // change, so it needs ONE float4 of the centre vector per k-block, fetched before the wait on the TMA bytes.
       const int cchunk = ((et & 7) ^ ((et >> 3) & 7)) * 4;
       for (int kb = 0; kb < num_kb; ++kb) {
@@ -273,15 +285,18 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
         mbar_wait(&full_bar[s], phase);
         float4* hi = reinterpret_cast<float4*>(stage_base + s * Plan::STAGE_BYTES);
         float4* lo = hi + NV;
+        // The tensor core reads the top 19 bits of an fp32 operand, i.e. the staged tile already IS the hi part; it is
+        // rewritten only when the centre was subtracted.  (epi.keep_hi: leave the staged values in place.)
+        const bool rewrite_hi = (epi.center != nullptr) || !epi.keep_hi;
 #pragma unroll 4
-        for (int i = et; i < nv; i += 32 * kEpiWarps) {
+        for (int i = et; i < nv; i += 32 * kSplitWarps) {
           float4 x = hi[i], h, l;
           x.x -= cv.x; x.y -= cv.y; x.z -= cv.z; x.w -= cv.w;
           h.x = __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u); l.x = x.x - h.x;
           h.y = __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u); l.y = x.y - h.y;
           h.z = __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u); l.z = x.z - h.z;
           h.w = __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u); l.w = x.w - h.w;
-          hi[i] = h;
+          if (rewrite_hi) hi[i] = h;
           lo[i] = l;
         }
         fence_proxy_async_smem();            // make the generic-proxy stores visible to the tensor core
@@ -290,7 +305,8 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
         if (++s == STAGES) { s = 0; phase ^= 1; }
       }
     }
-    // ---- epilogue: TMEM -> registers -> global
+    // ---- epilogue: TMEM -> registers -> global (warps 2..5; the split-only warps 6..9 are done)
+    if (warp < 2 + kEpiWarps) {
     const int quarter = warp & 3;            // TMEM lane quarter this warp may read
     if (num_kb > 0) {
       mbar_wait(accum_bar, 0);
@@ -445,6 +461,7 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
       if (et == 0 && atomicAdd(cnt, 1) == 2 * n_split - 1) *cnt = 0;   // last one out re-arms the counter for the next launch
     }
     fence_before_thread_sync();
+    }
   }
   __syncthreads();
   if (warp == 2) {
@@ -454,21 +471,21 @@ __device__ __forceinline__ void gemm_tcgen05_body(const CUtensorMap& tma_a, cons
 }
 
 template <int BN, int EB, bool A_MN, bool B_MN, bool SPLIT3>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                     const Epilogue epi, const int M, const int N, const int K, const int kblocks_per_split) {
   gemm_tcgen05_body<BN, EB, A_MN, B_MN, SPLIT3, false>(tma_a, tma_b, nullptr, epi, M, N, K, kblocks_per_split);
 }
 
 template <int BN, bool A_MN, bool B_MN, bool SPLIT3>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kGemmThreads, 2)
 gemm_tcgen05_short_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                           const Epilogue epi, const int M, const int N, const int K, const int kblocks_per_split) {
   gemm_tcgen05_body<BN, 4, A_MN, B_MN, SPLIT3, false, true>(tma_a, tma_b, nullptr, epi, M, N, K, kblocks_per_split);
 }
 
 template <int BN, bool SPLIT3>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kGemmThreads, 1)
 gather_gemm_tcgen05_kernel(const __grid_constant__ GatherMaps gm, const __grid_constant__ CUtensorMap tma_b,
                            const Epilogue epi, const int M, const int N, const int K, const int kblocks_per_split) {
   gemm_tcgen05_body<BN, 4, false, false, SPLIT3, true>(tma_b, tma_b, &gm, epi, M, N, K, kblocks_per_split);
@@ -761,9 +778,9 @@ int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const Epilogue& ep
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, G * n_split);
   static const int fix_mode = getenv("DDL_FIXUP_LAUNCH") ? atoi(getenv("DDL_FIXUP_LAUNCH")) : 0;
   if (epi.counters != nullptr && fix_mode < 2)   // the split CTAs of a tile wait for each other: cooperative launch (all CTAs co-resident, or an error)
-    DDL_CUDA_CHECK(ddl_launch_coop(kern, grid, dim3(kThreads), Plan::TOTAL, st, fix_mode == 1, ta, tb, epi, M, N, K, kb_per_split));
+    DDL_CUDA_CHECK(ddl_launch_coop(kern, grid, dim3(kGemmThreads), Plan::TOTAL, st, fix_mode == 1, ta, tb, epi, M, N, K, kb_per_split));
   else
-    DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kThreads), Plan::TOTAL, st, ta, tb, epi, M, N, K, kb_per_split));
+    DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kGemmThreads), Plan::TOTAL, st, ta, tb, epi, M, N, K, kb_per_split));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -778,7 +795,7 @@ int launch_gemm_short(const CUtensorMap& ta, const CUtensorMap& tb, const Epilog
     configured.done();
   }
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, G);
-  DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kThreads), Plan::TOTAL, st, ta, tb, epi, M, N, K, (K + 31) / 32));
+  DDL_CUDA_CHECK(ddl_launch_pdl(kern, grid, dim3(kGemmThreads), Plan::TOTAL, st, ta, tb, epi, M, N, K, (K + 31) / 32));
   DDL_LAUNCH_CHECK();
   return DDL_OK;
 }
@@ -857,6 +874,7 @@ static int gemm_impl(const void* A, int64_t lda, int64_t a_group_stride, int a_m
   if (int e = make_operand_map(&tb, ob, K, G, BN, eb)) return e;
 
   Epilogue epi;
+  epi.keep_hi = keep_hi_default();
   epi.C = n_split > 1 ? scratch : C;
   epi.ldc = ldc; epi.c_group_stride = c_group_stride;
   // the cooperative fix-up needs all CTAs of the grid co-resident: one wave of one CTA per SM
@@ -974,6 +992,7 @@ int ddl_gather_gemm_tcgen05(const float* const* parts, const int* part_dims, con
   OperandDesc ob{W, N, ldw, 0, 0};
   if (int e = make_operand_map(&tb, ob, Ktot, 1, BN, 4)) return e;
   Epilogue epi;
+  epi.keep_hi = keep_hi_default();
   epi.C = n_split > 1 ? scratch : C;
   epi.ldc = ldc; epi.c_group_stride = 0; epi.bias = bias; epi.bias_group_stride = 0;
   epi.act = act; epi.slope = slope; epi.alpha = 1.f; epi.beta = 0.f; epi.n_split = n_split; epi.same_ab = 0;
@@ -986,7 +1005,7 @@ int ddl_gather_gemm_tcgen05(const float* const* parts, const int* part_dims, con
     auto kern = gather_gemm_tcgen05_kernel<BN_, P_>;                                                           \
     using Plan = SmemPlan<BN_, 4, P_>;                                                                         \
     DDL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Plan::TOTAL));      \
-    kern<<<grid, kThreads, Plan::TOTAL, st>>>(gm, tb, epi, M, N, 0, kbps);                                     \
+    kern<<<grid, kGemmThreads, Plan::TOTAL, st>>>(gm, tb, epi, M, N, 0, kbps);                                     \
   }
   if (BN == 32) { if (precise) DDL_GATHER_CASE(32, true) else DDL_GATHER_CASE(32, false) }
   else if (BN == 64) { if (precise) DDL_GATHER_CASE(64, true) else DDL_GATHER_CASE(64, false) }
@@ -1030,6 +1049,7 @@ int ddl_gram_rowgather_tcgen05(const float* const* part_ptrs, int n_parts, int r
   n_split = (total_kb + kbps - 1) / kbps;
   const int BN = Kc <= 32 ? 32 : (Kc <= 64 ? 64 : 128);
   Epilogue epi;
+  epi.keep_hi = keep_hi_default();
   epi.C = n_split > 1 ? scratch : gram;
   epi.ldc = ldg; epi.c_group_stride = 0; epi.bias = nullptr; epi.bias_group_stride = 0;
   epi.act = 0; epi.slope = 0.f; epi.alpha = 1.f; epi.beta = 0.f; epi.n_split = n_split; epi.same_ab = 1;
@@ -1043,7 +1063,7 @@ int ddl_gram_rowgather_tcgen05(const float* const* part_ptrs, int n_parts, int r
     auto kern = gather_gemm_tcgen05_kernel<BN_, P_>;                                                           \
     using Plan = SmemPlan<BN_, 4, P_>;                                                                         \
     DDL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Plan::TOTAL));      \
-    kern<<<grid, kThreads, Plan::TOTAL, st>>>(gm, gm.maps[0], epi, Kc, Kc, Kdim, kbps);                        \
+    kern<<<grid, kGemmThreads, Plan::TOTAL, st>>>(gm, gm.maps[0], epi, Kc, Kc, Kdim, kbps);                        \
   }
 #define DDL_ROWG_CASE(BN_) { if (precise) DDL_ROWG_CASE2(BN_, true) else DDL_ROWG_CASE2(BN_, false) }
   if (BN == 32) DDL_ROWG_CASE(32) else if (BN == 64) DDL_ROWG_CASE(64) else DDL_ROWG_CASE(128)

@@ -30,6 +30,7 @@ MAX_FIXUP_TILES = 8192
 # launch).  Opt-in: on the LLaMA step the separate reduce kernel behind a programmatic dependent launch measured faster
 # (2.74 ms vs 3.30 ms cooperative / 3.20 ms programmatic launch of the fix-up), see profiles/r2_llama_fixup_modes.txt.
 USE_FIXUP = os.environ.get("DDL_GEMM_FIXUP", "0") == "1"
+AUTO_SPLIT = True           # spread the K loop of small grids over more SMs (see gemm()); benchmarks switch it off to isolate it
 _TILE_COUNTERS: dict = {}
 
 
@@ -84,7 +85,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         # grows ~linearly in K (measured on B200: 2e-6 at K=128, 8e-5 at K=9216).  Cap each
         # accumulation chain at PRECISE_CHAIN products and finish the sum in fp32 on the CUDA cores.
         n_split = max(n_split, -(-K // PRECISE_CHAIN))
-    if n_split == 1 and beta == 0.0 and eb == 4:
+    if AUTO_SPLIT and n_split == 1 and beta == 0.0 and eb == 4:
         # a grid that covers less than half the SMs with a long K loop (LLaMA's 768-wide projections on 768 tokens: 18 tiles x
         # 24 k-blocks, or 42 tiles x 9 k-blocks: 17.8 us at 26 % tensor-pipe activity under ncu) is latency-bound per CTA: spread the reduction over more SMs, partials summed in a fixed order
         bn = 32 if N <= 32 else (64 if N <= 64 else 128)
