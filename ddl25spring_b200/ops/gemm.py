@@ -80,19 +80,23 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.shape[-1] == N
         bias_stride = bias.stride(0) if bias.dim() == 2 else 0
+    chain_min = 1
     if precise and beta == 0.0:
         # The tensor core's fp32 accumulator truncates on every add, so the error of a K-long chain
         # grows ~linearly in K (measured on B200: 2e-6 at K=128, 8e-5 at K=9216).  Cap each
         # accumulation chain at PRECISE_CHAIN products and finish the sum in fp32 on the CUDA cores.
-        n_split = max(n_split, -(-K // PRECISE_CHAIN))
+        chain_min = -(-K // PRECISE_CHAIN)
     if AUTO_SPLIT and n_split == 1 and beta == 0.0 and eb == 4:
-        # a grid that covers less than half the SMs with a long K loop (LLaMA's 768-wide projections on 768 tokens: 18 tiles x
-        # 24 k-blocks, or 42 tiles x 9 k-blocks: 17.8 us at 26 % tensor-pipe activity under ncu) is latency-bound per CTA: spread the reduction over more SMs, partials summed in a fixed order
+        # A grid that covers less than half the SMs with a long K loop is latency-bound per CTA: spread the reduction over more
+        # SMs, partials summed in a fixed order by splitk_reduce_kernel.  Tuned inside a CUDA graph on the LLaMA lab's shapes
+        # (scripts/dev/gemm_split_tune.py, profiles/r2_gemm_split_tune.txt): a k-block costs ~0.75 us (3xTF32), the extra
+        # reduce launch 3-5 us depending on the output size, so 9 k-blocks are only worth splitting on very small grids.
         bn = 32 if N <= 32 else (64 if N <= 64 else 128)
         ctas = -(-M // 128) * -(-N // bn) * G
         kb = -(-K // 32)
-        if 2 * ctas <= 148 and kb >= 8:
+        if 2 * ctas <= 148 and (kb >= 16 or (kb >= 8 and ctas <= 20)):
             n_split = max(1, min(kb // 3, 148 // ctas))
+    n_split = max(n_split, chain_min)
     L = _lib.lib()
     scratch = counters = None
     if n_split > 1:
