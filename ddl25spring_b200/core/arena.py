@@ -126,7 +126,11 @@ class FlatArena:
             for s in self.specs:
                 if s.is_buffer:
                     continue
-                params[s.name].grad = self.grad[s.offset:s.offset + s.numel].view(s.shape)
+                p = params[s.name]
+                p.grad = self.grad[s.offset:s.offset + s.numel].view(s.shape)
+                # ops.nn: a weight-gradient GEMM may accumulate straight into this slot (C = A B + C in the epilogue) instead
+                # of handing a temporary to autograd's add kernel; post-accumulate-grad hooks are still run
+                p._ddl_direct_grad = True
         return self.grad
 
     # ------------------------------------------------------------------ access

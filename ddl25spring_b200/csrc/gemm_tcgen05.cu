@@ -62,7 +62,7 @@ struct Epilogue {
   int act;              // 0 none, 1 relu, 2 leaky relu
   float slope;
   float alpha;
-  float beta;           // direct (n_split == 1) path only: C = act(alpha*acc + beta*C_old + bias)
+  float beta;           // C = act(alpha*acc + beta*C_old + bias): in the epilogue when n_split == 1, else in splitk_reduce_kernel
   int n_split;          // > 1: write raw partial tiles to C = scratch[split][g][M][N] (ldc = N)
   int keep_hi;          // SPLIT3: the staged fp32 tile serves as the hi operand as it is (the tensor core truncates to TF32)
   int same_ab;          // A and B are the same matrix (Gram / SYRK): stage each tile once, use it as both operands
@@ -495,7 +495,7 @@ gather_gemm_tcgen05_kernel(const __grid_constant__ GatherMaps gm, const __grid_c
 __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ part, int n_split,
                                                             int64_t group_elems /*M*N*/, int G, int N, float* __restrict__ C,
                                                             int64_t ldc, int64_t c_group_stride, const float* __restrict__ bias,
-                                                            int64_t bias_group_stride, int act, float slope) {
+                                                            int64_t bias_group_stride, int act, float slope, float beta) {
   pdl_launch_dependents();
   pdl_wait();
   const int64_t total = group_elems * G;
@@ -506,8 +506,10 @@ __global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restr
     const int64_t r = i % group_elems;
     const int64_t m = r / N;
     const int n = (int)(r % N);
+    float* dst = C + (int64_t)g * c_group_stride + m * ldc + n;
+    if (beta != 0.f) acc = fmaf(beta, *dst, acc);          // C = act(alpha * A B + beta * C + bias), as on the direct path
     if (bias) acc += bias[(int64_t)g * bias_group_stride + n];
-    C[(int64_t)g * c_group_stride + m * ldc + n] = apply_act(acc, act, slope);
+    *dst = apply_act(acc, act, slope);
   }
 }
 
@@ -733,7 +735,7 @@ int launch_gram_packed(const float* U, int64_t ld, int K, int64_t D, const float
   if (!direct) {
     const int64_t ge = (int64_t)K * K;
     DDL_CUDA_CHECK(ddl_launch_pdl(splitk_reduce_kernel, dim3((unsigned)((ge + 255) / 256)), dim3(256), 0, st, (const float*)scratch, n_split, ge,
-                                  1, K, gram, ldg, (int64_t)0, (const float*)nullptr, (int64_t)0, 0, 0.f));
+                                  1, K, gram, ldg, (int64_t)0, (const float*)nullptr, (int64_t)0, 0, 0.f, 0.f));
     DDL_LAUNCH_CHECK();
   }
   return DDL_OK;
@@ -854,7 +856,7 @@ static int gemm_impl(const void* A, int64_t lda, int64_t a_group_stride, int a_m
   if (n_split < 1) n_split = 1;
   const int total_kb = (K + bk - 1) / bk;
   if (n_split > total_kb) n_split = total_kb;
-  DDL_REQUIRE(n_split == 1 || beta == 0.f, "beta (accumulate into C) is only supported without split-K");
+  if (beta != 0.f) tile_counters = nullptr;      // accumulate into C with split-K: the separate reduce kernel applies beta
   DDL_REQUIRE(n_split == 1 || scratch != nullptr, "split-K needs a scratch buffer of ddl_gemm_scratch_floats() floats");
   const int kbps = (total_kb + n_split - 1) / n_split;
   n_split = (total_kb + kbps - 1) / kbps;
@@ -911,7 +913,7 @@ static int gemm_impl(const void* A, int64_t lda, int64_t a_group_stride, int a_m
     int64_t blocks = (ge * G + 255) / 256;
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
     DDL_CUDA_CHECK(ddl_launch_pdl(splitk_reduce_kernel, dim3((unsigned)blocks), dim3(256), 0, st, scratch, n_split, ge, G, N, C, ldc,
-                                  c_group_stride, bias, bias_group_stride, act, slope));
+                                  c_group_stride, bias, bias_group_stride, act, slope, beta));
     DDL_LAUNCH_CHECK();
   }
   return DDL_OK;
@@ -1016,7 +1018,7 @@ int ddl_gather_gemm_tcgen05(const float* const* parts, const int* part_dims, con
     const int64_t ge = (int64_t)M * N;
     int64_t blocks = (ge + 255) / 256;
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    splitk_reduce_kernel<<<(int)blocks, 256, 0, st>>>(scratch, n_split, ge, 1, N, C, ldc, 0, bias, 0, act, slope);
+    splitk_reduce_kernel<<<(int)blocks, 256, 0, st>>>(scratch, n_split, ge, 1, N, C, ldc, 0, bias, 0, act, slope, 0.f);
     DDL_LAUNCH_CHECK();
   }
   return DDL_OK;
@@ -1073,7 +1075,7 @@ int ddl_gram_rowgather_tcgen05(const float* const* part_ptrs, int n_parts, int r
   if (n_split > 1) {
     const int64_t ge = (int64_t)Kc * Kc;
     int64_t blocks = (ge + 255) / 256;
-    splitk_reduce_kernel<<<(int)blocks, 256, 0, st>>>(scratch, n_split, ge, 1, Kc, gram, ldg, 0, nullptr, 0, 0, 0.f);
+    splitk_reduce_kernel<<<(int)blocks, 256, 0, st>>>(scratch, n_split, ge, 1, Kc, gram, ldg, 0, nullptr, 0, 0, 0.f, 0.f);
     DDL_LAUNCH_CHECK();
   }
   return DDL_OK;

@@ -81,12 +81,12 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         assert bias.dtype == torch.float32 and bias.shape[-1] == N
         bias_stride = bias.stride(0) if bias.dim() == 2 else 0
     chain_min = 1
-    if precise and beta == 0.0:
+    if precise:
         # The tensor core's fp32 accumulator truncates on every add, so the error of a K-long chain
         # grows ~linearly in K (measured on B200: 2e-6 at K=128, 8e-5 at K=9216).  Cap each
         # accumulation chain at PRECISE_CHAIN products and finish the sum in fp32 on the CUDA cores.
         chain_min = -(-K // PRECISE_CHAIN)
-    if AUTO_SPLIT and n_split == 1 and beta == 0.0 and eb == 4:
+    if AUTO_SPLIT and n_split == 1 and eb == 4:
         # A grid that covers less than half the SMs with a long K loop is latency-bound per CTA: spread the reduction over more
         # SMs, partials summed in a fixed order by splitk_reduce_kernel.  Tuned inside a CUDA graph on the LLaMA lab's shapes
         # (scripts/dev/gemm_split_tune.py, profiles/r2_gemm_split_tune.txt): a k-block costs ~0.75 us (3xTF32), the extra
@@ -102,7 +102,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     if n_split > 1:
         scratch = torch.empty(n_split * G * M * N, device=a.device, dtype=torch.float32)
         from .conv import _SCOPE
-        if USE_FIXUP and L.ddl_gemm_tile_count(int(M), int(N), int(G)) <= MAX_FIXUP_TILES and not _SCOPE["concurrent"]:
+        if USE_FIXUP and beta == 0.0 and L.ddl_gemm_tile_count(int(M), int(N), int(G)) <= MAX_FIXUP_TILES and not _SCOPE["concurrent"]:
             counters = _tile_counters(a.device)
     args = (_lib.p(A), _lib.i64(A.stride(1)), _lib.i64(A.stride(0)), int(a_mn),
             _lib.p(B), _lib.i64(B.stride(1)), _lib.i64(B.stride(0)), int(b_mn),

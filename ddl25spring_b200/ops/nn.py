@@ -40,6 +40,21 @@ def col_sum(x: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def _direct_grad_slot(w: torch.Tensor):
+    """The gradient slot of a parameter bound to a flat gradient arena (``core.arena.FlatArena.bind_grads`` marks them), when a
+    backward kernel may accumulate straight into it: the weight-gradient GEMM then runs as ``C = A B + C`` on the slot - no
+    temporary and no autograd add kernel per parameter per step (45 launches and two 37 MB read-modify-write passes of the
+    LLaMA lab step).  The backward then returns no gradient for the parameter; autograd still runs the parameter's
+    post-accumulate-grad hooks (DataParallel's bucket launches) - checked by tests/test_nn_bridge_gpu.py.
+    ``None`` -> return the gradient to autograd as usual (no slot yet, or a double-backward graph)."""
+    if not getattr(w, "_ddl_direct_grad", False) or torch.is_grad_enabled():
+        return None
+    g = w.grad
+    if g is None or g.dtype != torch.float32 or not g.is_contiguous() or g.shape != w.shape or g.data_ptr() % 16:
+        return None
+    return g
+
+
 class _LinearFn(torch.autograd.Function):
     """nn.Linear on the tcgen05 GEMM, forward + both gradients, for ANY layer width.
 
@@ -81,7 +96,11 @@ class _LinearFn(torch.autograd.Function):
             if ctx.needs_input_grad[0]:
                 gx = gemm(g2, w, b_mn=True, precise=ctx.precise).view(ctx.shape)
             if ctx.needs_input_grad[1]:
-                gw = gemm(g2, x2, a_mn=True, b_mn=True, precise=ctx.precise)
+                slot = _direct_grad_slot(w)
+                if slot is not None:
+                    gemm(g2, x2, a_mn=True, b_mn=True, precise=ctx.precise, out=slot, beta=1.0)
+                else:
+                    gw = gemm(g2, x2, a_mn=True, b_mn=True, precise=ctx.precise)
             if ctx.has_bias and ctx.needs_input_grad[2]:
                 gb = col_sum(g2)
             return gx, gw, gb, None
@@ -475,6 +494,7 @@ class _GateUpSwiGluFn(torch.autograd.Function):
         h = torch.empty(M, Fh, device=x.device, dtype=torch.float32)
         _lib.check(_lib.lib().ddl_swiglu_gu_fwd(_lib.p(gu), _lib.p(h), _lib.i64(M), int(Fh), _lib.stream()), "ddl_swiglu_gu_fwd")
         ctx.save_for_backward(x2, wg, gu)
+        ctx.wu = wu                      # only its gradient slot is needed in the backward
         ctx.precise, ctx.shape = precise, x.shape
         return h.view(*x.shape[:-1], Fh)
 
@@ -493,8 +513,13 @@ class _GateUpSwiGluFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             gx = gemm(dgu, w2, b_mn=True, precise=ctx.precise).view(ctx.shape)
         if ctx.needs_input_grad[1] or ctx.needs_input_grad[2]:
-            gw2 = gemm(dgu, x2, a_mn=True, b_mn=True, precise=ctx.precise)           # [2F, D]
-            gwg, gwu = gw2[:Fh], gw2[Fh:]
+            wu = ctx.wu
+            sg, su = _direct_grad_slot(wg), _direct_grad_slot(wu)
+            if sg is not None and su is not None and _stacked(sg, su):       # the two slots are back to back like the weights
+                gemm(dgu, x2, a_mn=True, b_mn=True, precise=ctx.precise, out=torch.as_strided(sg, (2 * Fh, D), (D, 1)), beta=1.0)
+            else:
+                gw2 = gemm(dgu, x2, a_mn=True, b_mn=True, precise=ctx.precise)       # [2F, D]
+                gwg, gwu = gw2[:Fh], gw2[Fh:]
         return gx, gwg, gwu, None
 
 
@@ -516,20 +541,23 @@ class _EmbeddingFn(torch.autograd.Function):
         out = torch.empty(tok.numel(), d, device=weight.device, dtype=torch.float32)
         _lib.check(_lib.lib().ddl_embedding_fwd(_lib.p(weight), _lib.p(tok), _lib.p(out), _lib.i64(tok.numel()), int(d), _lib.i64(V),
                                                 _lib.stream()), "ddl_embedding_fwd")
-        ctx.save_for_backward(tok)
+        ctx.save_for_backward(tok, weight)
         ctx.shape, ctx.pad = (V, d), -1 if padding_idx is None else int(padding_idx)
         return out.view(*tokens.shape, d)
 
     @staticmethod
     def backward(ctx, g):
-        (tok,) = ctx.saved_tensors
+        tok, weight = ctx.saved_tensors
         V, d = ctx.shape
         g2 = g.reshape(-1, d)
         if g2.stride(1) != 1 or g2.stride(0) != d:
             g2 = g2.contiguous()
-        dW = torch.zeros(V, d, device=g.device, dtype=torch.float32)
+        slot = _direct_grad_slot(weight)         # the scatter-add goes straight into the arena slot: no V x d temporary
+        dW = slot if slot is not None else torch.zeros(V, d, device=g.device, dtype=torch.float32)
         _lib.check(_lib.lib().ddl_embedding_bwd(_lib.p(g2), _lib.p(tok), _lib.p(dW), _lib.i64(tok.numel()), int(d), _lib.i64(V),
                                                 _lib.i64(ctx.pad), _lib.stream()), "ddl_embedding_bwd")
+        if slot is not None:
+            return None, None, None
         return None, dW, None
 
 

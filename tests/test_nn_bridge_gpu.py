@@ -289,3 +289,30 @@ def test_stacked_gate_up_swiglu_matches_torch(cuda_lib):
     mlp.w_up.weight.data = mlp.w_up.weight.data.clone()
     assert not knn._stacked(mlp.w_gate.weight, mlp.w_up.weight)
     torch.testing.assert_close(mlp(x), y1, rtol=1e-5, atol=1e-5)
+
+
+def test_weight_gradients_accumulate_straight_into_arena_slots(cuda_lib):
+    """Parameters bound to a flat gradient arena get their weight gradient from the GEMM epilogue (C = A B + C): same values as
+    autograd's own accumulation over two backward passes, post-accumulate-grad hooks run once per parameter and pass."""
+    from ddl25spring_b200.core.arena import FlatArena
+    from ddl25spring_b200.models.llama import LLama
+    torch.manual_seed(5)
+    V = 512
+    ref = LLama(None, V, 96, 2, DEV, 2, 64)
+    net = LLama(None, V, 96, 2, DEV, 2, 64)
+    net.load_state_dict(ref.state_dict())
+    knn.use_kernels(net)
+    arena = FlatArena.from_module(net, with_grad=True)
+    fired = {}
+    for name, p in net.named_parameters():
+        assert p._ddl_direct_grad
+        p.register_post_accumulate_grad_hook((lambda n: (lambda _p: fired.__setitem__(n, fired.get(n, 0) + 1)))(name))
+    tok = torch.randint(0, V, (2, 64), device=DEV)
+    for _ in range(2):                                   # gradients of two passes add up in both models
+        knn.kernel_causal_lm_loss(net(tok), tok).backward()
+        F.cross_entropy(ref(tok)[:, :-1].reshape(-1, V), tok[:, 1:].reshape(-1)).backward()
+    names = [n for n, _ in net.named_parameters()]
+    assert {n: fired.get(n, 0) for n in names} == {n: 2 for n in names}
+    for (name, p), q in zip(net.named_parameters(), ref.parameters()):
+        assert p.grad.data_ptr() >= arena.grad.data_ptr() and p.grad.data_ptr() < arena.grad.data_ptr() + arena.grad.numel() * 4, name
+        torch.testing.assert_close(p.grad, q.grad, rtol=2e-3, atol=2e-4, msg=name)
