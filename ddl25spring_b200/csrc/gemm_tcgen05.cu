@@ -813,6 +813,278 @@ int dispatch_short(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMa
   return launch_gemm_short<BN, true, true, SPLIT3>(ta, tb, epi, M, N, K, G, st);
 }
 
+
+// ------------------------------------------------------------------------------------------ persistent GEMM (many tiles)
+// A grid of several waves of one-tile CTAs pays the fixed cost of a CTA (~6 us: first TMA round trip, accumulator drain,
+// epilogue) once per tile and runs nothing else on the SM meanwhile: the 768 x 32 000 x 288 vocabulary projection of the LLaMA
+// lab took 145 us for ten waves of 9-k-block tiles.  Here ONE CTA per SM walks the tile list: the TMA producer, the splitter
+// warps and the MMA issuer run ahead across tile boundaries through the operand ring, and the accumulator is DOUBLE-BUFFERED in
+// TMEM (2 x 128 columns) so that the four epilogue warps drain tile i while the tensor core fills tile i + 1.  Tiles are
+// numbered so that the CTAs running at the same time share operand slabs through L2 (see n_fast).
+// fp32 operands (TF32 or 3xTF32), BN = 128, one group, no split-K.
+constexpr int kPersistThreads = 32 * (2 + kEpiWarps + 4);   // TMA, MMA, 4 epilogue warps, 4 splitter warps
+
+template <bool SPLIT3>
+struct PersistPlan {
+  static constexpr int BN = 128;
+  static constexpr int A_BYTES = BM * ROW_BYTES, B_BYTES = BN * ROW_BYTES;
+  static constexpr int STAGE_BYTES = (A_BYTES + B_BYTES) * (SPLIT3 ? 2 : 1);
+  static constexpr int STAGES = SPLIT3 ? 3 : 6;              // 192 KB of operand ring
+  static constexpr int EPI_PITCH = 36;                       // floats; see the epilogue of gemm_tcgen05_body
+  static constexpr int EPI_BYTES = kEpiWarps * 32 * EPI_PITCH * 4;
+  static constexpr int BAR_BYTES = 1024;
+  static constexpr int TOTAL = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024 /*alignment slack*/;
+  static_assert(TOTAL <= 227 * 1024, "persistent GEMM plan exceeds the shared memory of an SM");
+};
+
+template <bool A_MN, bool B_MN, bool SPLIT3>
+__global__ void __launch_bounds__(kPersistThreads, 1)
+gemm_persist_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const Epilogue epi,
+                    const int M, const int N, const int K) {
+  using Plan = PersistPlan<SPLIT3>;
+  constexpr int BN = Plan::BN, STAGES = Plan::STAGES, BK = 32, UMMA_K = 8, KSTEPS = 4;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* stage_base = smem;
+  float* epi_smem = reinterpret_cast<float*>(smem + STAGES * Plan::STAGE_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Plan::STAGE_BYTES + Plan::EPI_BYTES);
+  uint64_t* full_bar = bars;                    // TMA bytes landed
+  uint64_t* empty_bar = bars + STAGES;          // MMAs that read the stage have completed
+  uint64_t* split_bar = bars + 2 * STAGES;      // hi/lo split written (SPLIT3 only)
+  uint64_t* acc_full = bars + 3 * STAGES;       // [2] accumulator buffer complete
+  uint64_t* acc_empty = bars + 3 * STAGES + 2;  // [2] accumulator buffer drained by the epilogue warps
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m_tiles = (M + BM - 1) / BM, n_tiles = (N + BN - 1) / BN;
+  const int total_tiles = m_tiles * n_tiles;
+  const int num_kb = (K + BK - 1) / BK;
+  // consecutive tiles (= the tiles in flight on neighbouring SMs) share the slab of the operand with MORE slabs' counterpart:
+  // few row tiles -> m fastest (they share a B slab); few column tiles -> n fastest (they share an A slab)
+  const bool n_fast = m_tiles > n_tiles;
+  auto tile_m0 = [&](int t) { return (n_fast ? t / n_tiles : t % m_tiles) * BM; };
+  auto tile_n0 = [&](int t) { return (n_fast ? t % n_tiles : t / m_tiles) * BN; };
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+      mbar_init(&split_bar[s], 4);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&acc_full[b], 1);
+      mbar_init(&acc_empty[b], kEpiWarps);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc<2 * BN>(tmem_slot);
+  fence_before_thread_sync();
+  __syncthreads();
+  fence_after_thread_sync();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_launch_dependents();
+  pdl_wait();
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      uint32_t phase = 0;
+      int s = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int m0 = tile_m0(t), n0 = tile_n0(t);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[s], phase ^ 1);
+          uint8_t* a_dst = stage_base + s * Plan::STAGE_BYTES;
+          uint8_t* b_dst = a_dst + Plan::A_BYTES;
+          mbar_arrive_expect_tx(&full_bar[s], Plan::A_BYTES + Plan::B_BYTES);
+          const int k0 = kb * BK;
+          if constexpr (A_MN) tma_load_4d(a_dst, &tma_a, &full_bar[s], 0, k0, m0 / BK, 0);
+          else tma_load_3d(a_dst, &tma_a, &full_bar[s], k0, m0, 0);
+          if constexpr (B_MN) tma_load_4d(b_dst, &tma_b, &full_bar[s], 0, k0, n0 / BK, 0);
+          else tma_load_3d(b_dst, &tma_b, &full_bar[s], k0, n0, 0);
+          if (++s == STAGES) { s = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = make_idesc(FMT_TF32, BM, BN, A_MN, B_MN);
+    constexpr uint32_t a_lay = A_MN ? LAYOUT_SW128_BASE32B : LAYOUT_SW128, b_lay = B_MN ? LAYOUT_SW128_BASE32B : LAYOUT_SW128;
+    constexpr uint32_t a_sbo = A_MN ? 512 : 1024, b_sbo = B_MN ? 512 : 1024;
+    constexpr uint32_t a_lbo = A_MN ? BK * ROW_BYTES : 16, b_lbo = B_MN ? BK * ROW_BYTES : 16;
+    constexpr uint32_t a_step = A_MN ? UMMA_K * ROW_BYTES : 32, b_step = B_MN ? UMMA_K * ROW_BYTES : 32;
+    constexpr uint32_t LO_OFF = Plan::A_BYTES + Plan::B_BYTES;
+    uint32_t phase = 0, acc_phase = 0;
+    int s = 0, buf = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      mbar_wait(&acc_empty[buf], acc_phase ^ 1);          // the epilogue has drained this buffer (tile t - 2)
+      fence_after_thread_sync();
+      const uint32_t tmem_acc = tmem_base + (uint32_t)(buf * BN);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(SPLIT3 ? &split_bar[s] : &full_bar[s], phase);
+        fence_after_thread_sync();
+        if (elect_one()) {
+          const uint32_t a_hi = smem_u32(stage_base + s * Plan::STAGE_BYTES);
+          const uint64_t da_hi0 = smem_desc_sw128(a_hi, a_lbo, a_sbo, a_lay);
+          const uint64_t db_hi0 = smem_desc_sw128(a_hi + Plan::A_BYTES, b_lbo, b_sbo, b_lay);
+#pragma unroll
+          for (int kk = 0; kk < KSTEPS; ++kk) {
+            const bool acc = (kb > 0) || (kk > 0);
+            const uint64_t da_hi = desc_advance(da_hi0, kk * a_step), db_hi = desc_advance(db_hi0, kk * b_step);
+            if constexpr (SPLIT3) {
+              const uint64_t da_lo = desc_advance(da_hi, LO_OFF), db_lo = desc_advance(db_hi, LO_OFF);
+              mma_tf32(tmem_acc, da_lo, db_hi, idesc, acc);
+              mma_tf32(tmem_acc, da_hi, db_lo, idesc, true);
+              mma_tf32(tmem_acc, da_hi, db_hi, idesc, true);
+            } else {
+              mma_tf32(tmem_acc, da_hi, db_hi, idesc, acc);
+            }
+          }
+          mma_commit(&empty_bar[s]);
+          if (kb == num_kb - 1) mma_commit(&acc_full[buf]);
+        }
+        __syncwarp();
+        if (++s == STAGES) { s = 0; phase ^= 1; }
+      }
+      if (++buf == 2) { buf = 0; acc_phase ^= 1; }
+    }
+  } else if (warp >= 2 + kEpiWarps) {
+    // ===================== splitter warps (3xTF32): lo = x - trunc_tf32(x); the staged tile is the hi operand =====================
+    if constexpr (SPLIT3) {
+      const int st = (warp - 2 - kEpiWarps) * 32 + lane;     // 0..127
+      constexpr int NV = (Plan::A_BYTES + Plan::B_BYTES) / 16;
+      uint32_t phase = 0;
+      int s = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[s], phase);
+          const float4* hi = reinterpret_cast<const float4*>(stage_base + s * Plan::STAGE_BYTES);
+          float4* lo = reinterpret_cast<float4*>(stage_base + s * Plan::STAGE_BYTES) + NV;
+#pragma unroll 4
+          for (int i = st; i < NV; i += 128) {
+            const float4 x = hi[i];
+            float4 l;
+            l.x = x.x - __uint_as_float(__float_as_uint(x.x) & 0xFFFFE000u);
+            l.y = x.y - __uint_as_float(__float_as_uint(x.y) & 0xFFFFE000u);
+            l.z = x.z - __uint_as_float(__float_as_uint(x.z) & 0xFFFFE000u);
+            l.w = x.w - __uint_as_float(__float_as_uint(x.w) & 0xFFFFE000u);
+            lo[i] = l;
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&split_bar[s]);
+          if (++s == STAGES) { s = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue warps: TMEM -> registers -> shared transpose -> global =====================
+    const int quarter = warp & 3;
+    constexpr int WP = Plan::EPI_PITCH;
+    float* wsm = epi_smem + (warp - 2) * (32 * WP);
+    float* Cg = epi.C;
+    const int64_t ldc = epi.ldc;
+    const float* bias = epi.bias;
+    const bool vec_ok = (ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(Cg) & 15) == 0) && (N % 4 == 0);
+    const int lr = lane >> 3, lc = (lane & 7) * 4;
+    uint32_t acc_phase = 0;
+    int buf = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int m0 = tile_m0(t), n0 = tile_n0(t);
+      const int mrow0 = m0 + quarter * 32;
+      mbar_wait(&acc_full[buf], acc_phase);
+      fence_after_thread_sync();
+      const uint32_t tmem_acc = tmem_base + (uint32_t)(buf * BN) + ((uint32_t)(quarter * 32) << 16);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        if (n0 + c0 >= N) break;
+        float v[32];
+        tmem_ld_32x32(tmem_acc + (uint32_t)c0, v);
+#pragma unroll
+        for (int i = 0; i < 32; i += 4)
+          *reinterpret_cast<float4*>(wsm + lane * WP + i) =
+              make_float4(v[i] * epi.alpha, v[i + 1] * epi.alpha, v[i + 2] * epi.alpha, v[i + 3] * epi.alpha);
+        __syncwarp();
+        if (vec_ok) {
+          const int n = n0 + c0 + lc;
+          const bool nok = n < N;
+          float4 bn4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (bias && nok) bn4 = *reinterpret_cast<const float4*>(bias + n);
+#pragma unroll
+          for (int it = 0; it < 8; ++it) {
+            const int r = it * 4 + lr, m = mrow0 + r;
+            float4 x = *reinterpret_cast<const float4*>(wsm + r * WP + lc);
+            if (nok && m < M) {
+              float4* dst = reinterpret_cast<float4*>(Cg + (int64_t)m * ldc + n);
+              if (epi.beta != 0.f) {
+                const float4 old = *dst;
+                x.x = fmaf(epi.beta, old.x, x.x); x.y = fmaf(epi.beta, old.y, x.y);
+                x.z = fmaf(epi.beta, old.z, x.z); x.w = fmaf(epi.beta, old.w, x.w);
+              }
+              x.x = apply_act(x.x + bn4.x, epi.act, epi.slope); x.y = apply_act(x.y + bn4.y, epi.act, epi.slope);
+              x.z = apply_act(x.z + bn4.z, epi.act, epi.slope); x.w = apply_act(x.w + bn4.w, epi.act, epi.slope);
+              *dst = x;
+            }
+          }
+        } else {
+          const int nn = n0 + c0 + lane;
+          const bool ncol_ok = nn < N;
+          const float bn = (bias && ncol_ok) ? bias[nn] : 0.f;
+          float* cbase = Cg + (int64_t)mrow0 * ldc + nn;
+#pragma unroll 4
+          for (int rr = 0; rr < 32; ++rr) {
+            float x = wsm[rr * WP + lane];
+            if (ncol_ok && mrow0 + rr < M) {
+              if (epi.beta != 0.f) x = fmaf(epi.beta, cbase[(int64_t)rr * ldc], x);
+              cbase[(int64_t)rr * ldc] = apply_act(x + bn, epi.act, epi.slope);
+            }
+          }
+        }
+        __syncwarp();
+      }
+      fence_before_thread_sync();                   // this warp's tcgen05.ld of the buffer are complete ...
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);  // ... the tensor core may overwrite it (tile t + 2)
+      if (++buf == 2) { buf = 0; acc_phase ^= 1; }
+    }
+  }
+  fence_before_thread_sync();
+  __syncthreads();
+  if (warp == 2) {
+    fence_after_thread_sync();
+    tmem_dealloc<2 * PersistPlan<SPLIT3>::BN>(tmem_base);
+  }
+}
+
+template <bool A_MN, bool B_MN, bool SPLIT3>
+int launch_gemm_persist(const CUtensorMap& ta, const CUtensorMap& tb, const Epilogue& epi, int M, int N, int K, cudaStream_t st) {
+  using Plan = PersistPlan<SPLIT3>;
+  auto kern = gemm_persist_kernel<A_MN, B_MN, SPLIT3>;
+  static DdlOncePerDevice configured;
+  if (configured.need()) {
+    DDL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Plan::TOTAL));
+    configured.done();
+  }
+  const int tiles = ((M + BM - 1) / BM) * ((N + Plan::BN - 1) / Plan::BN);
+  const int grid = tiles < kNumSMs ? tiles : kNumSMs;
+  DDL_CUDA_CHECK(ddl_launch_pdl(kern, dim3(grid), dim3(kPersistThreads), Plan::TOTAL, st, ta, tb, epi, M, N, K));
+  DDL_LAUNCH_CHECK();
+  return DDL_OK;
+}
+
+template <bool SPLIT3>
+int dispatch_persist(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const Epilogue& epi, int M, int N, int K,
+                     cudaStream_t st) {
+  if (!a_mn && !b_mn) return launch_gemm_persist<false, false, SPLIT3>(ta, tb, epi, M, N, K, st);
+  if (!a_mn && b_mn) return launch_gemm_persist<false, true, SPLIT3>(ta, tb, epi, M, N, K, st);
+  if (a_mn && !b_mn) return launch_gemm_persist<true, false, SPLIT3>(ta, tb, epi, M, N, K, st);
+  return launch_gemm_persist<true, true, SPLIT3>(ta, tb, epi, M, N, K, st);
+}
+
 template <int BN, int EB, bool SPLIT3>
 int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const Epilogue& epi, int M,
                    int N, int K, int G, int n_split, int kbps, cudaStream_t st) {
@@ -894,6 +1166,12 @@ static int gemm_impl(const void* A, int64_t lda, int64_t a_group_stride, int a_m
   cudaStream_t st = (cudaStream_t)stream;
   int rc;
   const bool amn = a_mn_major != 0, bmn = b_mn_major != 0;
+  // many tiles, one split, fp32: the persistent kernel (accumulator double-buffered in TMEM, epilogue under the next main loop)
+  static const int persist_min_tiles = getenv("DDL_GEMM_PERSIST_MIN_TILES") ? atoi(getenv("DDL_GEMM_PERSIST_MIN_TILES")) : 2 * kNumSMs;
+  if (!use_short && eb == 4 && G == 1 && n_split == 1 && BN == 128 && center == nullptr && !epi.same_ab &&
+      (int64_t)((M + BM - 1) / BM) * ((N + 127) / 128) >= persist_min_tiles) {
+    return precise ? dispatch_persist<true>(amn, bmn, ta, tb, epi, M, N, K, st) : dispatch_persist<false>(amn, bmn, ta, tb, epi, M, N, K, st);
+  }
   if (use_short) {
     DDL_REQUIRE(center == nullptr, "re-centring is not available on the short-K path");
     epi.same_ab = 0;

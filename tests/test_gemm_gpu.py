@@ -104,3 +104,27 @@ def test_gather_gemm_local_parts(cuda_lib, dims):
     cat = torch.cat([p[:, :d] for p, d in zip(parts, dims)], 1).double()
     exp = torch.nn.functional.leaky_relu(cat @ W.double().T + b.double(), 0.01)
     assert _rel_err(got, exp) < 1e-5
+
+
+@pytest.mark.parametrize("precise", [False, True])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+def test_persistent_gemm_many_tiles(cuda_lib, precise, a_mn, b_mn):
+    """Grids of >= 2 x 148 tiles run the persistent kernel (one CTA per SM walks the tiles, accumulator double-buffered in
+    TMEM): every operand layout, a ragged last tile in both dimensions, bias + ReLU, and accumulation into C."""
+    torch.manual_seed(11)
+    M, N, K = 128 * 9 + 32, 128 * 40 + 96, 288            # 10 x 41 = 410 tiles
+    a = torch.randn((K, M) if a_mn else (M, K), device=DEV)
+    b = torch.randn((K, N) if b_mn else (N, K), device=DEV)
+    bias = torch.randn(N, device=DEV)
+    A = a.double().T if a_mn else a.double()
+    B = b.double() if b_mn else b.double().T
+    tol = 1e-5 if precise else 3e-3
+    exp = torch.relu(A @ B + bias.double())
+    got = G.gemm(a, b, a_mn=a_mn, b_mn=b_mn, bias=bias, act="relu", precise=precise)
+    assert _rel_err(got, exp) < tol
+    c0 = torch.randn(M, N, device=DEV)
+    out = c0.clone()
+    G.gemm(a, b, a_mn=a_mn, b_mn=b_mn, precise=precise, out=out, alpha=0.5, beta=1.0)
+    assert _rel_err(out, 0.5 * (A @ B) + c0.double()) < tol
+    again = G.gemm(a, b, a_mn=a_mn, b_mn=b_mn, bias=bias, act="relu", precise=precise)
+    assert torch.equal(got, again)
