@@ -1,6 +1,6 @@
 """Small single-GPU drivers for `ncu --set full` captures of the round-2 kernels.
 
-  python scripts/profile_r2_kernels.py gram8 | gram64 | median64 | linear | attention
+  python scripts/profile_r2_kernels.py gram8 | gram64 | median64 | linear | attention | persist
 """
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -40,3 +40,11 @@ elif which == "attention":
         o.sum().backward()
     torch.cuda.synchronize()
     print(which, float(o[0, 0, 0, 0]))
+elif which == "persist":
+    # the LLaMA lab's vocabulary projection: 768 x 32 000 x 288, 3xTF32 -> 1 500 tiles on the persistent kernel
+    x = torch.randn(768, 288, device="cuda")
+    w = torch.randn(32000, 288, device="cuda")
+    for _ in range(4):
+        y = G.gemm(x, w, precise=True)
+    torch.cuda.synchronize()
+    print(which, float(y[0, 0]))
