@@ -17,6 +17,10 @@ None of this framework's kernels, arenas or graphs runs here - only stock PyTorc
 * ``vfl``     lab/tutorial_2b/vfl.py:36-37,79-82 - party embeddings ``all_gather``-ed, ``torch.cat``, ``nn.Linear`` top model,
               autograd backward, AdamW.
 
+The pipeline baseline (``dist.isend`` / ``irecv`` of CUDA tensors between plain-PyTorch LLaMA stages, lab/tutorial_1b/PP/1F1B/
+intro_PP_1F1B_MB.py) is the ``torch`` arm of ``benchmarks/bench_pp_llama.py``; the DCGAN ``dist.all_reduce`` baseline is the
+``nccl`` arm of ``benchmarks/bench_fed_dcgan.py``.
+
 Timing: CUDA events around the timed iterations on every rank, max over ranks; rank 0 prints one JSON object whose rows are
 the "reference build on NCCL" columns of BASELINE.md section 4.
 """
