@@ -8,6 +8,8 @@ pair.  On CPU tensors every function falls back to the plain PyTorch statement o
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.nn.functional as F
 from torch import nn
@@ -38,6 +40,22 @@ def col_sum(x: torch.Tensor) -> torch.Tensor:
     _lib.check(_lib.lib().ddl_col_sum(_lib.p(x), _lib.i64(x.stride(0)), int(x.shape[0]), int(x.shape[1]), _lib.p(out), _lib.f32(1.0),
                                       _lib.f32(0.0), _lib.stream()), "ddl_col_sum")
     return out
+
+
+# Input and weight gradient of a linear layer only share inputs: with CONCURRENT_WGRAD the weight-gradient GEMM runs on the
+# side stream of the current workspace scope (a parallel branch inside a captured step), as ops/conv.py does for convolutions.
+CONCURRENT_WGRAD = os.environ.get("DDL_CONCURRENT_WGRAD", "1") == "1"
+
+
+def _side_and_main(side_fn, main_fn):
+    from .conv import _workspace
+    main, side = torch.cuda.current_stream(), _workspace(torch.device("cuda", torch.cuda.current_device()))["side"]
+    side.wait_stream(main)
+    with torch.cuda.stream(side):
+        a = side_fn()
+    b = main_fn()
+    main.wait_stream(side)
+    return a, b
 
 
 def _direct_grad_slot(w: torch.Tensor):
@@ -93,14 +111,20 @@ class _LinearFn(torch.autograd.Function):
         if ctx.aligned:
             x2, w = ctx.saved_tensors
             g2 = g2.contiguous()
-            if ctx.needs_input_grad[0]:
-                gx = gemm(g2, w, b_mn=True, precise=ctx.precise).view(ctx.shape)
-            if ctx.needs_input_grad[1]:
+            def wgrad():
                 slot = _direct_grad_slot(w)
                 if slot is not None:
                     gemm(g2, x2, a_mn=True, b_mn=True, precise=ctx.precise, out=slot, beta=1.0)
-                else:
-                    gw = gemm(g2, x2, a_mn=True, b_mn=True, precise=ctx.precise)
+                    return None
+                return gemm(g2, x2, a_mn=True, b_mn=True, precise=ctx.precise)
+
+            if ctx.needs_input_grad[0] and ctx.needs_input_grad[1] and CONCURRENT_WGRAD:
+                gw, gx = _side_and_main(wgrad, lambda: gemm(g2, w, b_mn=True, precise=ctx.precise).view(ctx.shape))
+            else:
+                if ctx.needs_input_grad[0]:
+                    gx = gemm(g2, w, b_mn=True, precise=ctx.precise).view(ctx.shape)
+                if ctx.needs_input_grad[1]:
+                    gw = wgrad()
             if ctx.has_bias and ctx.needs_input_grad[2]:
                 gb = col_sum(g2)
             return gx, gw, gb, None
@@ -510,16 +534,24 @@ class _GateUpSwiGluFn(torch.autograd.Function):
         _lib.check(_lib.lib().ddl_swiglu_gu_bwd(_lib.p(gu), _lib.p(dh2), _lib.p(dgu), _lib.i64(M), int(Fh), _lib.stream()), "ddl_swiglu_gu_bwd")
         w2 = torch.as_strided(wg, (2 * Fh, D), (D, 1))
         gx = gwg = gwu = None
-        if ctx.needs_input_grad[0]:
-            gx = gemm(dgu, w2, b_mn=True, precise=ctx.precise).view(ctx.shape)
-        if ctx.needs_input_grad[1] or ctx.needs_input_grad[2]:
+
+        def wgrad():
             wu = ctx.wu
             sg, su = _direct_grad_slot(wg), _direct_grad_slot(wu)
             if sg is not None and su is not None and _stacked(sg, su):       # the two slots are back to back like the weights
                 gemm(dgu, x2, a_mn=True, b_mn=True, precise=ctx.precise, out=torch.as_strided(sg, (2 * Fh, D), (D, 1)), beta=1.0)
-            else:
-                gw2 = gemm(dgu, x2, a_mn=True, b_mn=True, precise=ctx.precise)       # [2F, D]
-                gwg, gwu = gw2[:Fh], gw2[Fh:]
+                return None, None
+            gw2 = gemm(dgu, x2, a_mn=True, b_mn=True, precise=ctx.precise)           # [2F, D]
+            return gw2[:Fh], gw2[Fh:]
+
+        need_w = ctx.needs_input_grad[1] or ctx.needs_input_grad[2]
+        if ctx.needs_input_grad[0] and need_w and CONCURRENT_WGRAD:
+            (gwg, gwu), gx = _side_and_main(wgrad, lambda: gemm(dgu, w2, b_mn=True, precise=ctx.precise).view(ctx.shape))
+        else:
+            if ctx.needs_input_grad[0]:
+                gx = gemm(dgu, w2, b_mn=True, precise=ctx.precise).view(ctx.shape)
+            if need_w:
+                gwg, gwu = wgrad()
         return gx, gwg, gwu, None
 
 
