@@ -388,12 +388,30 @@ class _CausalAttnGemmFn(torch.autograd.Function):
         _lib.check(L.ddl_attn_bwd_prep(_lib.p(go), _lib.i64(go.stride(0)), _lib.i64(go.stride(1)), _lib.i64(go.stride(2)), _lib.p(op),
                                        _lib.p(dop), _lib.p(delta), int(B), int(H), int(T), int(hd), int(HP), _lib.stream()),
                    "ddl_attn_bwd_prep")
-        dS = gemm(dop, vp, precise=True)                                              # dP = dO V^T
-        _lib.check(L.ddl_attn_ds(_lib.p(P), _lib.p(dS), _lib.p(delta), _lib.i64(G * T), int(T), _lib.f32(ctx.scale), _lib.stream()),
-                   "ddl_attn_ds")
-        dv = gemm(P, dop, a_mn=True, b_mn=True, precise=True)                         # P^T dO
-        dq = gemm(dS, kp, b_mn=True, precise=True)                                    # dS K
-        dk = gemm(dS, qp, a_mn=True, b_mn=True, precise=True)                         # dS^T Q
+        if CONCURRENT_WGRAD:
+            # dV only needs P and dO, dK only dS and Q: both leave the critical path prep -> dP -> dS -> dQ and run on the side
+            # stream of the workspace scope (parallel branches of a captured step); outputs are allocated before the fork
+            from .conv import _workspace
+            main, side = torch.cuda.current_stream(), _workspace(go.device)["side"]
+            dv, dk = torch.empty_like(dop), torch.empty_like(dop)
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                gemm(P, dop, a_mn=True, b_mn=True, precise=True, out=dv)              # P^T dO
+            dS = gemm(dop, vp, precise=True)                                          # dP = dO V^T
+            _lib.check(L.ddl_attn_ds(_lib.p(P), _lib.p(dS), _lib.p(delta), _lib.i64(G * T), int(T), _lib.f32(ctx.scale), _lib.stream()),
+                       "ddl_attn_ds")
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                gemm(dS, qp, a_mn=True, b_mn=True, precise=True, out=dk)              # dS^T Q
+            dq = gemm(dS, kp, b_mn=True, precise=True)                                # dS K
+            main.wait_stream(side)
+        else:
+            dS = gemm(dop, vp, precise=True)                                          # dP = dO V^T
+            _lib.check(L.ddl_attn_ds(_lib.p(P), _lib.p(dS), _lib.p(delta), _lib.i64(G * T), int(T), _lib.f32(ctx.scale), _lib.stream()),
+                       "ddl_attn_ds")
+            dv = gemm(P, dop, a_mn=True, b_mn=True, precise=True)                     # P^T dO
+            dq = gemm(dS, kp, b_mn=True, precise=True)                                # dS K
+            dk = gemm(dS, qp, a_mn=True, b_mn=True, precise=True)                     # dS^T Q
         view = lambda t: t.view(B, H, T, HP)[..., :hd]
         return view(dq), view(dk), view(dv), None
 
