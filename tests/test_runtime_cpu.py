@@ -52,3 +52,31 @@ def test_u8_normalize_and_adam_tensor_step_host_paths():
     ops.adam_step(p1, g, m1, v1, 3, 1e-2)
     ops.adam_step(p2, g, m2, v2, torch.tensor(3, dtype=torch.int32), 1e-2)
     assert torch.equal(p1, p2)
+
+
+def test_gate_up_weights_are_stacked_and_stay_stacked_in_a_flat_arena():
+    """use_kernels lays w_gate / w_up out back to back (one GEMM over [Wg; Wu] on the GPU); values, Parameters and state_dict
+    keys are untouched, a FlatArena keeps the pair adjacent (also in the gradient arena), and CPU forward is unchanged."""
+    import torch
+    from ddl25spring_b200.core.arena import FlatArena
+    from ddl25spring_b200.models.llama import LLama
+    from ddl25spring_b200.ops.nn import _direct_grad_slot, _stacked, use_kernels
+    torch.manual_seed(0)
+    net = LLama(None, 64, 32, 2, "cpu", 2, 8)
+    tok = torch.randint(0, 64, (2, 8))
+    before = {k: v.clone() for k, v in net.state_dict().items()}
+    y0 = net(tok)
+    use_kernels(net)
+    mlps = [m for m in net.modules() if hasattr(m, "w_gate")]
+    assert mlps and all(_stacked(m.w_gate.weight.data, m.w_up.weight.data) for m in mlps)
+    assert all(torch.equal(before[k], v) for k, v in net.state_dict().items())
+    arena = FlatArena.from_module(net, with_grad=True)
+    for m in mlps:
+        assert _stacked(m.w_gate.weight.data, m.w_up.weight.data) and _stacked(m.w_gate.weight.grad, m.w_up.weight.grad)
+        assert m.w_gate.weight._ddl_direct_grad
+        with torch.no_grad():
+            assert _direct_grad_slot(m.w_gate.weight) is m.w_gate.weight.grad      # backward runs with grad mode off
+        assert _direct_grad_slot(m.w_gate.weight) is None                          # ... never while a graph is being built
+    torch.testing.assert_close(net(tok), y0)
+    net(tok).sum().backward()
+    assert float(arena.grad.abs().sum()) > 0
