@@ -76,7 +76,7 @@ def test_robust_resnet_fl_example_runs_on_cpu():
     assert len(res.test_accuracy) == 1 and res.test_accuracy[0] == res.test_accuracy[0]
 
 
-@pytest.mark.parametrize("name", ["horizontal_federated_learning", "vertical_federated_learning"])
+@pytest.mark.parametrize("name", ["horizontal_federated_learning", "vertical_federated_learning", "data_and_pipeline_parallel"])
 def test_tutorial_notebooks_execute(name):
     """The tutorial notebooks (counterparts of the reference's lab notebooks) are stored clean and their code cells run."""
     import json
